@@ -1,0 +1,144 @@
+/* kmb200.h -- C ABI of libkmeans_b200.so: a B200-native (sm_100a) K-means Lloyd iteration that
+ * drops in behind OAP MLlib's org.apache.spark.ml.clustering.KMeans.fit() path.
+ *
+ * Every entry point replaces a piece of the reference's JNI surface (reference =
+ * bobjiang82/oap-mllib, paths below are relative to mllib-dal/src/main/).  The JNI symbols the
+ * Scala side binds are thin wrappers over these functions (csrc/jni_shim.cpp).
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative
+ * kmb200_status; kmb200_last_error() gives the thread-local message.  No function falls back to a
+ * CPU implementation: without a usable sm_100 GPU every compute call fails with KMB200_ERR_DEVICE.
+ * Handles are not thread-safe; different handles may be used from different threads.
+ */
+#ifndef KMB200_H_
+#define KMB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    KMB200_OK = 0,
+    KMB200_ERR_ARG = -1,      /* bad argument (null, negative size, shape mismatch)            */
+    KMB200_ERR_DEVICE = -2,   /* no sm_100 device / CUDA runtime error                         */
+    KMB200_ERR_MEMORY = -3,   /* device or pinned-host allocation failed                       */
+    KMB200_ERR_COMM = -4,     /* NCCL unavailable or returned an error                         */
+    KMB200_ERR_EMPTY = -5,    /* more empty clusters than positive-distance candidate rows     */
+    KMB200_ERR_LIMIT = -6     /* size beyond a documented limit                                */
+} kmb200_status;
+
+typedef struct kmb200_table kmb200_table; /* one executor's row partition, FP32, resident in HBM */
+typedef struct kmb200_comm kmb200_comm;   /* one rank of the NCCL communicator                    */
+
+/* ---- platform gate ----------------------------------------------------------------------------
+ * Replaces Java_org_apache_spark_ml_util_OneDAL_00024_cCheckPlatformCompatibility
+ * (native/OneDAL.cpp:96-102, "is this an Intel CPU") with "is there at least one sm_100 GPU".
+ * Returns 1 / 0 (never an error code). */
+int kmb200_device_ok(void);
+/* Number of visible CUDA devices (0 when the driver is absent). */
+int kmb200_device_count(void);
+/* Selects the CUDA device used by the calling thread for subsequent calls (one executor = one
+ * GPU = one rank; S/ml/clustering/KMeansDALImpl.scala:48-50 uses the partition index as rank). */
+int kmb200_set_device(int32_t ordinal);
+
+/* ---- data table ---------------------------------------------------------------------------------
+ * Replaces the oneDAL HomogenNumericTable<double> conversion: DALMatrix allocation
+ * (scala/.../ml/util/OneDAL.scala:125-127), one JNI cSetDoubleBatch per row (:135-139 ->
+ * native/OneDAL.cpp:50-60), RowMergedNumericTable + cAddNumericTable (:155-163 ->
+ * native/OneDAL.cpp:67-76).  Here: one device table of `rows` x `cols` FP32 (leading dimension
+ * padded to 32 floats), filled by BATCHED row uploads from host memory (pinned or pageable). */
+int kmb200_table_create(int64_t rows, int32_t cols, kmb200_table **out);
+/* Copies nrows x ncols row-major values to table rows [row0, row0+nrows).  ncols must equal the
+ * table's cols.  f64 input is rounded to FP32 on the device (the reference's own test accepts FP32
+ * input at abs 1e-6: IntelKMeansSuite.scala:204-218). */
+int kmb200_table_append_f64(kmb200_table *t, int64_t row0, const double *rows, int64_t nrows, int32_t ncols);
+int kmb200_table_append_f32(kmb200_table *t, int64_t row0, const float *rows, int64_t nrows, int32_t ncols);
+/* Reads rows back as FP32 (diagnostics / tests; the reference has numericTableToVectors,
+ * OneDAL.scala:37-52, for the same purpose). */
+int kmb200_table_read_rows(const kmb200_table *t, int64_t row0, int64_t nrows, float *out);
+int64_t kmb200_table_rows(const kmb200_table *t);
+int32_t kmb200_table_cols(const kmb200_table *t);
+/* Benchmark utility (no reference counterpart): fills rows [0, rows) with synthetic Gaussian
+ * blobs ON THE DEVICE: row i belongs to blob hash(seed, row_offset+i) mod k_true and equals
+ * centres[blob] + N(0,1)^cols (counter-based RNG).  centres is k_true x cols FP32 on the host. */
+int kmb200_table_fill_blobs(kmb200_table *t, const float *centres, int32_t k_true, uint64_t seed,
+                            int64_t row_offset);
+/* Replaces cFreeDataMemory (native/OneDAL.cpp:83-89) / OneDAL.releaseNumericTables
+ * (OneDAL.scala:81-90). */
+int kmb200_table_free(kmb200_table *t);
+
+/* ---- communicator -------------------------------------------------------------------------------
+ * Replaces the oneCCL KVS rendezvous: OneCCL.init -> c_init (native/OneCCL.cpp:47-86), cleanup
+ * (:93-99), isRoot / rankID (:106-120), and drops the ip/port probing (c_getAvailPort :207-247).
+ * The Spark driver (or rank 0) calls kmb200_comm_unique_id once; the 128 bytes travel inside the
+ * task closure; each executor calls kmb200_comm_init(world, rank, id). */
+#define KMB200_UNIQUE_ID_BYTES 128
+int kmb200_comm_unique_id(uint8_t id[KMB200_UNIQUE_ID_BYTES]);
+int kmb200_comm_init(int32_t world, int32_t rank, const uint8_t id[KMB200_UNIQUE_ID_BYTES], kmb200_comm **out);
+int32_t kmb200_comm_rank(const kmb200_comm *c);
+int32_t kmb200_comm_size(const kmb200_comm *c);
+int kmb200_comm_destroy(kmb200_comm *c);
+
+/* ---- the Lloyd driver ---------------------------------------------------------------------------
+ * Replaces Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansDALComputeWithInitCenters
+ * (native/KMeansDALImpl.cpp:175-249): the loop `for (it = 0; it < maxIter && !converged; it++)`,
+ * oneDAL step1Local (:70-77), the gather + step2Master merge/finalize (:80-130, here ONE in-place
+ * ncclAllReduce of [k*d sums | k counts | cost]), and the convergence test (:135-168).
+ *
+ *   table        this rank's rows;  comm NULL => single GPU
+ *   init_centers k x d row-major FP64 (what OneDAL.makeNumericTable(centers) built, OneDAL.scala:62-79)
+ *   tol          absolute Euclidean distance per centre; every centre must move <= tol.
+ *                tol < 0 disables the test (exactly max_iter iterations; benchmark use).
+ *   out_centers  k x d FP64, written on EVERY rank (the reference returns them on rank 0 only)
+ *   out_cost     objective of the LAST executed assignment step (reference :125-127,:243)
+ *   out_iters    executed iterations (reference :241).  max_iter == 0 returns the initial centres
+ *                with cost 0.0 (the reference leaves the cost uninitialised, :195).
+ * Collective: every rank of comm must call it with the same k, d, tol, max_iter, init_centers. */
+int kmb200_fit(kmb200_table *table, kmb200_comm *comm, const double *init_centers, int32_t k, int32_t d,
+               double tol, int32_t max_iter, double *out_centers, double *out_cost, int32_t *out_iters);
+
+/* Post-fit assignment pass (replaces the JVM pass behind KMeansSummary:
+ * spark-3.1.1/ml/clustering/KMeans.scala:134-142,359-368).  labels_host (may be NULL) receives the
+ * cluster index of every local row; sizes_host (may be NULL, k entries) the cluster sizes summed
+ * over all ranks; cost_host (may be NULL) the summed squared distances. */
+int kmb200_assign(kmb200_table *table, kmb200_comm *comm, const double *centers, int32_t k, int32_t d,
+                  int32_t *labels_host, int64_t *sizes_host, double *cost_host);
+
+/* ---- instrumentation (replaces the integer-second prints at native/KMeansDALImpl.cpp:218-222) ---
+ * Device-side timings (CUDA events on the library's stream) of the last kmb200_fit /
+ * kmb200_assign on this thread, summed over iterations, in milliseconds. */
+typedef struct {
+    int32_t iterations;
+    int32_t kernel_launches;   /* kernels of this library launched                           */
+    int64_t rechecked_rows;    /* rows whose top-2 gap was inside the error bound (FP64 re-check) */
+    int32_t empty_cluster_events;
+    float total_ms;            /* first kernel of the first iteration -> end of the last         */
+    float assign_ms;           /* tcgen05 distance GEMM + argmin epilogue                        */
+    float recheck_ms;          /* FP64 re-evaluation of near-tie rows                            */
+    float bucket_ms;           /* label histogram + scan + row bucketing                         */
+    float accumulate_ms;       /* per-cluster FP64 sums / cost                                   */
+    float allreduce_ms;        /* NCCL all-reduce (0 for a single GPU)                           */
+    float finalize_ms;         /* centres, convergence flag, TF32 split of the new centres      */
+} kmb200_profile;
+int kmb200_get_profile(kmb200_profile *out);
+
+/* Tunables (process-wide; for experiments and tests).  name: "eps_scale" (multiplier on the
+ * near-tie error bound, default 1.0), "passes" (3 = 3xTF32 [default], 1 = single TF32 pass + wider
+ * re-check), "force_simt" (1 = use the CUDA-core FP32 assign kernel instead of tcgen05; debugging). */
+int kmb200_set_option(const char *name, double value);
+
+/* Test hook (no reference counterpart): raw tensor-core scores ||c_j||^2 - 2 x.c_j (FP32) of every
+ * row against every padded centre column (rows x kpad, row-major).  scores_host may be NULL to
+ * query kpad only.  Lets the tests measure the 3xTF32 error against FP64. */
+int kmb200_debug_scores(kmb200_table *table, const double *centers, int32_t k, int32_t d, float *scores_host,
+                        int32_t *kpad_out);
+
+const char *kmb200_last_error(void);
+const char *kmb200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KMB200_H_ */

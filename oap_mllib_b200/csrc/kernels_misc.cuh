@@ -1,0 +1,510 @@
+// CUDA-core kernels around the tensor-core assign step: ingest, centroid preparation, FP64 re-check
+// of near-tie rows, label bucketing, per-cluster FP64 accumulation, finalize / convergence, the
+// empty-cluster candidate search and the synthetic-blob generator.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+namespace kmb {
+
+constexpr int kSegChunk = 512;     // rows per accumulate work unit (one CTA)
+constexpr int kBucketRows = 8192;  // rows per CTA in the bucketing kernels
+constexpr int kHistSmemMax = 12288;  // largest k whose histogram is kept in shared memory
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ------------------------------------------------------------------ ingest
+// staging (dense nrows x d, T) -> table rows (leading dimension ld, FP32); padding stays zero.
+template <typename T>
+__global__ void convert_rows_kernel(const T *__restrict__ src, float *__restrict__ dst, int64_t nrows, int d,
+                                    int ld) {
+    const int64_t total = nrows * d;
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = e / d;
+        const int c = (int)(e - r * d);
+        dst[r * ld + c] = (float)src[e];
+    }
+}
+
+// ||x_i||^2 for rows [row0, row0 + nrows): G = min(32, ld/4) lanes per row, float4 loads.
+__global__ void rownorm_kernel(const float *__restrict__ X, float *__restrict__ xnorm, int64_t row0, int64_t nrows,
+                               int ld) {
+    const int vec = ld >> 2;
+    const int G = vec < 32 ? vec : 32;  // ld is a multiple of 32 -> vec is a multiple of 8
+    const int rows_per_warp = 32 / G;
+    const int lane = threadIdx.x & 31;
+    const int sub = lane / G, gl = lane % G;
+    const int64_t warp_global = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t rb = warp_global * rows_per_warp; rb < nrows; rb += nwarps * rows_per_warp) {
+        const int64_t r = rb + sub;
+        float acc = 0.f;
+        if (r < nrows) {
+            const float4 *p = reinterpret_cast<const float4 *>(X + (row0 + r) * ld);
+            for (int v = gl; v < vec; v += G) {
+                const float4 q = __ldg(p + v);
+                acc += q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+            }
+        }
+        for (int o = G >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (r < nrows && gl == 0) xnorm[row0 + r] = acc;
+    }
+}
+
+// ------------------------------------------------------------------ centroid preparation
+// One CTA per padded centroid row j.  For j < k: B_hi/B_lo = TF32 round-to-nearest split of -2*c_j,
+// cnorm = ||c_j||^2 (FP64 sum, rounded to FP32), cstats[0] = max ||c_j|| (atomicMax on the bits of
+// a non-negative float).  For j >= k: zero rows and cnorm = +inf so the column never wins.
+__global__ void split_centers_kernel(const double *__restrict__ cent, float *__restrict__ bhi,
+                                     float *__restrict__ blo, float *__restrict__ cnorm, float *cstats, int k,
+                                     int ld) {
+    const int j = blockIdx.x;
+    __shared__ double red[32];
+    double acc = 0.0;
+    for (int c = threadIdx.x; c < ld; c += blockDim.x) {
+        float h = 0.f, l = 0.f;
+        if (j < k) {
+            const double v = cent[(size_t)j * ld + c];
+            acc += v * v;
+            const float f = (float)(-2.0 * v);
+            uint32_t hb;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hb) : "f"(f));
+            h = __uint_as_float(hb);
+            const float rem = (float)(-2.0 * v - (double)h);
+            uint32_t lb;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lb) : "f"(rem));
+            l = __uint_as_float(lb);
+        }
+        bhi[(size_t)j * ld + c] = h;
+        blo[(size_t)j * ld + c] = l;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < (blockDim.x + 31) / 32; ++w) s += red[w];
+        if (j < k) {
+            cnorm[j] = (float)s;
+            // round the norm up a little so the bound stays an upper bound
+            const float nrm = (float)sqrt(s) * 1.000001f;
+            atomicMax(reinterpret_cast<int *>(cstats), __float_as_int(nrm));
+        } else {
+            cnorm[j] = __int_as_float(0x7f800000);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ exact (FP64) assignment
+// One warp per listed row (list == nullptr: every row).  score_j = ||c_j||^2 - 2 x.c_j in FP64,
+// first minimum wins.  Used (a) to re-evaluate rows whose tensor-core top-2 gap is inside the error
+// bound, (b) as the CUDA-core reference path for tests (option "force_simt").
+__global__ void recheck_kernel(const float *__restrict__ X, const double *__restrict__ cent,
+                               const int32_t *__restrict__ list, const int32_t *__restrict__ list_count,
+                               int32_t list_cap, int64_t n, int k, int ld, int32_t *__restrict__ labels) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp_global = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    int64_t count = n;
+    if (list) {
+        count = *list_count;
+        if (count > list_cap) count = list_cap;
+    }
+    const int per_lane = ld >> 5;  // ld is a multiple of 32
+    const bool cached = per_lane <= 16;  // rows up to 512 floats are held in registers
+    for (int64_t w = warp_global; w < count; w += nwarps) {
+        const int64_t row = list ? (int64_t)list[w] : w;
+        double xr[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            xr[i] = (cached && i < per_lane) ? (double)__ldg(X + row * ld + i * 32 + lane) : 0.0;
+        double best = INFINITY;
+        int bidx = 0;
+        for (int j = 0; j < k; ++j) {
+            const double *cj = cent + (size_t)j * ld;
+            double dot = 0.0, cn = 0.0;
+            if (cached) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    if (i < per_lane) {
+                        const double c = __ldg(cj + i * 32 + lane);
+                        dot = fma(xr[i], c, dot);
+                        cn = fma(c, c, cn);
+                    }
+                }
+            } else {
+                for (int c0 = lane; c0 < ld; c0 += 32) {
+                    const double c = __ldg(cj + c0);
+                    dot = fma((double)__ldg(X + row * ld + c0), c, dot);
+                    cn = fma(c, c, cn);
+                }
+            }
+            dot = warp_sum(dot);
+            cn = warp_sum(cn);
+            const double sc = cn - 2.0 * dot;
+            if (sc < best) {
+                best = sc;
+                bidx = j;
+            }
+        }
+        if (lane == 0) labels[row] = bidx;
+    }
+}
+
+// ------------------------------------------------------------------ bucketing rows by label
+// counts[j] = number of local rows with label j.
+__global__ void label_hist_kernel(const int32_t *__restrict__ labels, int64_t n, int k, int32_t *counts) {
+    extern __shared__ int32_t sh[];
+    const bool use_sh = k <= kHistSmemMax;
+    if (use_sh) {
+        for (int j = threadIdx.x; j < k; j += blockDim.x) sh[j] = 0;
+        __syncthreads();
+    }
+    const int64_t r0 = (int64_t)blockIdx.x * kBucketRows;
+    const int64_t r1 = min(n, r0 + kBucketRows);
+    for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
+        const int l = labels[r];
+        if (use_sh) atomicAdd(&sh[l], 1);
+        else atomicAdd(&counts[l], 1);
+    }
+    if (use_sh) {
+        __syncthreads();
+        for (int j = threadIdx.x; j < k; j += blockDim.x)
+            if (sh[j]) atomicAdd(&counts[j], sh[j]);
+    }
+}
+
+// Single CTA: offsets = exclusive scan of counts (k+1 entries), cursor = offsets, chunk_off =
+// exclusive scan of ceil(counts / kSegChunk) (k+1 entries).
+__global__ void scan_kernel(const int32_t *__restrict__ counts, int k, int32_t *offsets, int32_t *cursor,
+                            int32_t *chunk_off) {
+    __shared__ int32_t s_cnt[1024], s_chk[1024];
+    __shared__ int32_t base_cnt, base_chk;
+    if (threadIdx.x == 0) { base_cnt = 0; base_chk = 0; }
+    __syncthreads();
+    for (int j0 = 0; j0 < k; j0 += 1024) {
+        const int j = j0 + threadIdx.x;
+        const int c = j < k ? counts[j] : 0;
+        const int h = (c + kSegChunk - 1) / kSegChunk;
+        s_cnt[threadIdx.x] = c;
+        s_chk[threadIdx.x] = h;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {  // Hillis-Steele inclusive scan
+            int a = 0, b = 0;
+            if ((int)threadIdx.x >= o) { a = s_cnt[threadIdx.x - o]; b = s_chk[threadIdx.x - o]; }
+            __syncthreads();
+            s_cnt[threadIdx.x] += a;
+            s_chk[threadIdx.x] += b;
+            __syncthreads();
+        }
+        if (j < k) {
+            const int ex = base_cnt + s_cnt[threadIdx.x] - c;
+            offsets[j] = ex;
+            cursor[j] = ex;
+            chunk_off[j] = base_chk + s_chk[threadIdx.x] - h;
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) { base_cnt += s_cnt[1023]; base_chk += s_chk[1023]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { offsets[k] = base_cnt; chunk_off[k] = base_chk; }
+}
+
+// order[] = row indices grouped by label (order inside a group follows atomic arrival).
+__global__ void scatter_kernel(const int32_t *__restrict__ labels, int64_t n, int k, int32_t *cursor,
+                               int32_t *__restrict__ order) {
+    extern __shared__ int32_t sh[];  // [k] counts -> bases (only when k <= kHistSmemMax)
+    const bool use_sh = k <= kHistSmemMax;
+    const int64_t r0 = (int64_t)blockIdx.x * kBucketRows;
+    const int64_t r1 = min(n, r0 + kBucketRows);
+    if (!use_sh) {
+        for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
+            const int pos = atomicAdd(&cursor[labels[r]], 1);
+            order[pos] = (int32_t)r;
+        }
+        return;
+    }
+    for (int j = threadIdx.x; j < k; j += blockDim.x) sh[j] = 0;
+    __syncthreads();
+    for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x) atomicAdd(&sh[labels[r]], 1);
+    __syncthreads();
+    for (int j = threadIdx.x; j < k; j += blockDim.x) {
+        const int c = sh[j];
+        sh[j] = c ? atomicAdd(&cursor[j], c) : 0;  // reserve a contiguous range per (block, label)
+    }
+    __syncthreads();
+    for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
+        const int pos = atomicAdd(&sh[labels[r]], 1);
+        order[pos] = (int32_t)r;
+    }
+}
+
+// ------------------------------------------------------------------ per-cluster accumulation
+// One CTA per chunk (<= kSegChunk rows of ONE cluster, taken from the bucketed order[]).  Thread
+// layout: TPR = ld/4 threads per row (one float4 each), RPP = 256/TPR rows in flight per pass.
+// Sums and the direct-form cost sum ||x - c_j||^2 are accumulated in FP64 registers; no atomics.
+// part[chunk][ld] and cpart[chunk] receive the chunk partials.
+__global__ void __launch_bounds__(256)
+segment_sums_kernel(const float *__restrict__ X, const double *__restrict__ cent,
+                    const int32_t *__restrict__ order, const int32_t *__restrict__ offsets,
+                    const int32_t *__restrict__ chunk_off, int k, int ld, double *__restrict__ part,
+                    double *__restrict__ cpart) {
+    const int chunk = blockIdx.x;
+    if (chunk >= chunk_off[k]) return;
+    // binary search: largest j with chunk_off[j] <= chunk
+    int lo = 0, hi = k;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (chunk_off[mid] <= chunk) lo = mid; else hi = mid;
+    }
+    const int j = lo;
+    const int start = offsets[j] + (chunk - chunk_off[j]) * kSegChunk;
+    const int end = min(offsets[j + 1], start + kSegChunk);
+
+    extern __shared__ double sred[];  // [RPP][ld] for the cross-row reduction
+    const int vec = ld >> 2;
+    double cost = 0.0;
+    for (int v0 = 0; v0 < vec; v0 += 256) {  // ld <= 1024 per pass of 256 float4 lanes
+        const int tpr = min(vec - v0, 256);
+        const int rpp = 256 / tpr;
+        const int tv = threadIdx.x % tpr + v0;
+        const int tr = threadIdx.x / tpr;
+        double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+        if (tr < rpp) {
+            const double c0 = cent[(size_t)j * ld + 4 * tv + 0], c1 = cent[(size_t)j * ld + 4 * tv + 1];
+            const double c2 = cent[(size_t)j * ld + 4 * tv + 2], c3 = cent[(size_t)j * ld + 4 * tv + 3];
+            int i = start + tr;
+            // 4 rows in flight per thread
+            for (; i + 3 * rpp < end; i += 4 * rpp) {
+                const int ra = order[i], rb = order[i + rpp], rc = order[i + 2 * rpp], rd = order[i + 3 * rpp];
+                const float4 a = __ldg(reinterpret_cast<const float4 *>(X + (size_t)ra * ld) + tv);
+                const float4 b = __ldg(reinterpret_cast<const float4 *>(X + (size_t)rb * ld) + tv);
+                const float4 c = __ldg(reinterpret_cast<const float4 *>(X + (size_t)rc * ld) + tv);
+                const float4 d = __ldg(reinterpret_cast<const float4 *>(X + (size_t)rd * ld) + tv);
+#define KMB_ACC(q)                                                                  \
+    {                                                                               \
+        const double x0 = q.x, x1 = q.y, x2 = q.z, x3 = q.w;                        \
+        s0 += x0; s1 += x1; s2 += x2; s3 += x3;                                     \
+        const double e0 = x0 - c0, e1 = x1 - c1, e2 = x2 - c2, e3 = x3 - c3;        \
+        cost = fma(e0, e0, cost); cost = fma(e1, e1, cost);                         \
+        cost = fma(e2, e2, cost); cost = fma(e3, e3, cost);                         \
+    }
+                KMB_ACC(a) KMB_ACC(b) KMB_ACC(c) KMB_ACC(d)
+            }
+            for (; i < end; i += rpp) {
+                const float4 a = __ldg(reinterpret_cast<const float4 *>(X + (size_t)order[i] * ld) + tv);
+                KMB_ACC(a)
+            }
+#undef KMB_ACC
+        }
+        // reduce the rpp row-lanes that share a column group (fixed order -> deterministic per chunk)
+        if (tr < rpp) {
+            double *dst = sred + (size_t)tr * ld + 4 * tv;
+            dst[0] = s0; dst[1] = s1; dst[2] = s2; dst[3] = s3;
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < 4 * tpr; c += blockDim.x) {
+            double s = 0.0;
+            for (int r = 0; r < rpp; ++r) s += sred[(size_t)r * ld + 4 * v0 + c];
+            part[(size_t)chunk * ld + 4 * v0 + c] = s;
+        }
+        __syncthreads();
+    }
+    // cost: block reduction in a fixed tree
+    __shared__ double cred[8];
+    cost = warp_sum(cost);
+    if ((threadIdx.x & 31) == 0) cred[threadIdx.x >> 5] = cost;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < 8; ++w) s += cred[w];
+        cpart[chunk] = s;
+    }
+}
+
+// One CTA per cluster: red[j*ld + c] = sum over the cluster's chunks (in chunk order) of part;
+// red[k*ld + j] = count_j (as FP64, exact below 2^53); costj[j] = sum of the chunk costs.
+__global__ void segment_reduce_kernel(const double *__restrict__ part, const double *__restrict__ cpart,
+                                      const int32_t *__restrict__ offsets, const int32_t *__restrict__ chunk_off,
+                                      int k, int ld, double *__restrict__ red, double *__restrict__ costj) {
+    const int j = blockIdx.x;
+    const int c0 = chunk_off[j], c1 = chunk_off[j + 1];
+    for (int c = threadIdx.x; c < ld; c += blockDim.x) {
+        double s = 0.0;
+        for (int ch = c0; ch < c1; ++ch) s += part[(size_t)ch * ld + c];
+        red[(size_t)j * ld + c] = s;
+    }
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int ch = c0; ch < c1; ++ch) s += cpart[ch];
+        costj[j] = s;
+        red[(size_t)k * ld + j] = (double)(offsets[j + 1] - offsets[j]);
+    }
+}
+
+// Single CTA: red[k*ld + k] = sum_j costj[j] in a fixed order.
+__global__ void cost_sum_kernel(const double *__restrict__ costj, int k, int ld, double *__restrict__ red) {
+    __shared__ double sh[1024];
+    double s = 0.0;
+    for (int j = threadIdx.x; j < k; j += 1024) s += costj[j];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 512; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) red[(size_t)k * ld + k] = sh[0];
+}
+
+// ------------------------------------------------------------------ finalize + convergence
+// One CTA per cluster, after the all-reduce: c_new = sum * (1/count) (reciprocal multiply, as oneDAL
+// and Spark's scal(1/weightSum)); moved^2 = sequential sum_d (new-old)^2 (KMeansDALImpl.cpp:135-145);
+// flags[0] += 1 when the centre moved more than tol, flags[1] += 1 when the cluster is empty (its old
+// centre is copied; the host-driven candidate substitution replaces it).  The new centres go to a
+// second buffer so the old ones stay available for that substitution.
+__global__ void finalize_kernel(const double *__restrict__ red, const double *__restrict__ cent,
+                                double *__restrict__ cent_new, int k, int ld, int d, double tol, int32_t *flags) {
+    const int j = blockIdx.x;
+    extern __shared__ double sdiff[];
+    const double cnt = red[(size_t)k * ld + j];
+    if (cnt <= 0.0) {
+        for (int c = threadIdx.x; c < d; c += blockDim.x) cent_new[(size_t)j * ld + c] = cent[(size_t)j * ld + c];
+        if (threadIdx.x == 0) atomicAdd(&flags[1], 1);
+        return;
+    }
+    const double inv = 1.0 / cnt;
+    for (int c = threadIdx.x; c < d; c += blockDim.x) {
+        const double nv = red[(size_t)j * ld + c] * inv;
+        const double df = nv - cent[(size_t)j * ld + c];
+        sdiff[c] = df * df;
+        cent_new[(size_t)j * ld + c] = nv;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int c = 0; c < d; ++c) s += sdiff[c];
+        if (!(s <= tol * tol)) atomicAdd(&flags[0], 1);
+    }
+}
+
+// ------------------------------------------------------------------ empty-cluster candidates
+// dist[i] = ||x_i - c_label(i)||^2 in FP64, one warp per row.
+__global__ void rowdist_kernel(const float *__restrict__ X, const double *__restrict__ cent,
+                               const int32_t *__restrict__ labels, int64_t n, int ld, double *__restrict__ dist) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp_global = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = warp_global; row < n; row += nwarps) {
+        const double *cj = cent + (size_t)labels[row] * ld;
+        double s = 0.0;
+        for (int c = lane; c < ld; c += 32) {
+            const double e = (double)X[row * ld + c] - cj[c];
+            s = fma(e, e, s);
+        }
+        s = warp_sum(s);
+        if (lane == 0) dist[row] = s;
+    }
+}
+
+// Arg-max of dist over rows not in excl[0..nexcl): stage 1 per CTA, stage 2 single CTA (nblk1 == 0
+// means "reduce the nb stage-1 results").  Ties -> lowest row index.
+__global__ void argmax_kernel(const double *__restrict__ dist, int64_t n, const int32_t *__restrict__ excl,
+                              int nexcl, double *__restrict__ bval, int32_t *__restrict__ bidx, int stage2_nb) {
+    __shared__ double sv[256];
+    __shared__ int32_t si[256];
+    double v = -1.0;
+    int32_t idx = -1;
+    if (stage2_nb == 0) {
+        for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+            bool skip = false;
+            for (int e = 0; e < nexcl; ++e) skip |= (excl[e] == (int32_t)r);
+            const double dv = dist[r];
+            if (!skip && (dv > v || (dv == v && (int32_t)r < idx))) { v = dv; idx = (int32_t)r; }
+        }
+    } else {
+        for (int b = threadIdx.x; b < stage2_nb; b += blockDim.x) {
+            const double dv = bval[b];
+            const int32_t di = bidx[b];
+            if (di >= 0 && (dv > v || (dv == v && di < idx))) { v = dv; idx = di; }
+        }
+    }
+    sv[threadIdx.x] = v;
+    si[threadIdx.x] = idx;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            const double ov = sv[threadIdx.x + o];
+            const int32_t oi = si[threadIdx.x + o];
+            if (oi >= 0 && (ov > sv[threadIdx.x] || (ov == sv[threadIdx.x] && (si[threadIdx.x] < 0 || oi < si[threadIdx.x])))) {
+                sv[threadIdx.x] = ov;
+                si[threadIdx.x] = oi;
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const int out = stage2_nb == 0 ? blockIdx.x : stage2_nb;  // stage 2 writes slot [nb]
+        bval[out] = sv[0];
+        bidx[out] = si[0];
+    }
+}
+
+// ------------------------------------------------------------------ cluster sizes (kmb200_assign)
+__global__ void counts_to_i64_kernel(const int32_t *__restrict__ counts, int k, unsigned long long *out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < k) out[j] = (unsigned long long)counts[j];
+}
+
+// ------------------------------------------------------------------ synthetic Gaussian blobs
+__device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+// Row i (global index row_offset + i) belongs to blob splitmix64(seed ^ gi) mod k_true; each thread
+// produces 4 consecutive columns: two Box-Muller pairs from one 64-bit hash per pair.
+__global__ void blobs_kernel(float *__restrict__ X, int64_t nrows, int d, int ld, const float *__restrict__ centres,
+                             int k_true, uint64_t seed, int64_t row_offset) {
+    const int vec = ld >> 2;
+    const int64_t total = nrows * vec;
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = e / vec;
+        const int v = (int)(e - r * vec);
+        const uint64_t gi = (uint64_t)(row_offset + r);
+        const int blob = (int)(splitmix64(seed ^ (gi * 0x9E3779B97F4A7C15ull)) % (uint64_t)k_true);
+        float out[4];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint64_t bits = splitmix64(seed + 0x632BE59BD9B4E019ull * (gi * (uint64_t)vec * 2 + (uint64_t)(2 * v + h) + 1));
+            const float u1 = ((uint32_t)(bits >> 40) + 1u) * (1.0f / 16777217.0f);  // (0,1]
+            const float u2 = (uint32_t)(bits & 0xFFFFFFu) * (1.0f / 16777216.0f);   // [0,1)
+            const float rad = sqrtf(-2.0f * __logf(u1));
+            float sn, cs;
+            __sincosf(6.283185307179586f * u2, &sn, &cs);
+            out[2 * h] = rad * cs;
+            out[2 * h + 1] = rad * sn;
+        }
+        float4 q;
+        const int c = 4 * v;
+        q.x = c + 0 < d ? out[0] + centres[(size_t)blob * d + c + 0] : 0.f;
+        q.y = c + 1 < d ? out[1] + centres[(size_t)blob * d + c + 1] : 0.f;
+        q.z = c + 2 < d ? out[2] + centres[(size_t)blob * d + c + 2] : 0.f;
+        q.w = c + 3 < d ? out[3] + centres[(size_t)blob * d + c + 3] : 0.f;
+        reinterpret_cast<float4 *>(X + r * ld)[v] = q;
+    }
+}
+
+}  // namespace kmb

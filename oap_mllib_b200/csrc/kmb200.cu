@@ -1,0 +1,899 @@
+// libkmeans_b200.so -- host side of the C ABI declared in include/kmb200.h.
+// Table ingest (host -> HBM), NCCL rendezvous, and the Lloyd driver that replaces the loop in the
+// reference's mllib-dal/src/main/native/KMeansDALImpl.cpp:175-249.  There is no CPU fallback: every
+// compute entry point fails with KMB200_ERR_DEVICE when no sm_100 GPU is usable.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>  // types only; the library is dlopen'ed so single-GPU use needs no NCCL at all
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/kmb200.h"
+#include "assign_tc.cuh"
+#include "kernels_misc.cuh"
+
+using namespace kmb;
+
+// ------------------------------------------------------------------------------------ errors
+static thread_local std::string g_err;
+static thread_local kmb200_profile g_prof;
+
+static int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CU_TRY(expr)                                                                                   \
+    do {                                                                                               \
+        cudaError_t e__ = (expr);                                                                      \
+        if (e__ != cudaSuccess)                                                                        \
+            return fail(e__ == cudaErrorMemoryAllocation ? KMB200_ERR_MEMORY : KMB200_ERR_DEVICE,      \
+                        "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__);  \
+    } while (0)
+#define KM_TRY(expr)            \
+    do {                        \
+        int rc__ = (expr);      \
+        if (rc__ != 0) return rc__; \
+    } while (0)
+
+// ------------------------------------------------------------------------------------ options
+static double g_eps_scale = 1.0;
+static int g_passes = 3;
+static int g_force_simt = 0;
+static float *g_dbg_scores = nullptr;  // set only inside kmb200_debug_scores
+
+// ------------------------------------------------------------------------------------ NCCL (dlopen)
+struct NcclApi {
+    void *handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                              cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+static std::mutex g_nccl_mu;
+
+static int nccl_load() {
+    std::lock_guard<std::mutex> lk(g_nccl_mu);
+    if (g_nccl.handle) return 0;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    void *h = nullptr;
+    for (const char *nm : names) {
+        h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (h) break;
+    }
+    if (!h) return fail(KMB200_ERR_COMM, "cannot dlopen libnccl.so.2: %s", dlerror());
+#define KMB_SYM(field, name)                                                        \
+    g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(dlsym(h, name));        \
+    if (!g_nccl.field) return fail(KMB200_ERR_COMM, "NCCL symbol %s missing", name);
+    KMB_SYM(GetUniqueId, "ncclGetUniqueId")
+    KMB_SYM(CommInitRank, "ncclCommInitRank")
+    KMB_SYM(CommDestroy, "ncclCommDestroy")
+    KMB_SYM(AllReduce, "ncclAllReduce")
+    KMB_SYM(AllGather, "ncclAllGather")
+    KMB_SYM(GetErrorString, "ncclGetErrorString")
+#undef KMB_SYM
+    g_nccl.handle = h;
+    return 0;
+}
+#define NCCL_TRY(expr)                                                                          \
+    do {                                                                                        \
+        ncclResult_t r__ = (expr);                                                              \
+        if (r__ != ncclSuccess)                                                                 \
+            return fail(KMB200_ERR_COMM, "%s failed: %s", #expr, g_nccl.GetErrorString(r__));   \
+    } while (0)
+
+struct kmb200_comm {
+    ncclComm_t comm = nullptr;
+    int world = 1, rank = 0;
+};
+
+// ------------------------------------------------------------------------------------ table
+struct Workspace {
+    int k = 0, kpad = 0, bn = 0;
+    double *cent = nullptr;       // [kpad x ld] FP64 master copy of the centres (padding zero)
+    double *cent2 = nullptr;      // [kpad x ld] output of finalize; swapped with cent every iteration
+    float *bhi = nullptr, *blo = nullptr, *cnorm = nullptr, *cstats = nullptr;
+    int32_t *labels = nullptr, *order = nullptr, *flag_list = nullptr, *flag_count = nullptr;
+    int32_t *counts = nullptr, *offsets = nullptr, *cursor = nullptr, *chunk_off = nullptr;
+    double *part = nullptr, *cpart = nullptr, *red = nullptr, *costj = nullptr;
+    int32_t *flags = nullptr;      // [0] centres that moved > tol, [1] empty clusters
+    int64_t max_chunks = 0;
+    CUtensorMap tm_x, tm_bhi, tm_blo;
+    // pinned host mirror read once per iteration
+    struct Host {
+        int32_t flags[2];
+        int32_t flag_count;
+        int32_t pad;
+        double cost;
+    } *host = nullptr;
+};
+
+struct kmb200_table {
+    int device = 0;
+    int64_t rows = 0;
+    int d = 0, ld = 0;
+    float *X = nullptr;
+    float *xnorm = nullptr;
+    void *stage = nullptr;
+    size_t stage_bytes = 0;
+    cudaStream_t stream = nullptr;
+    int num_sms = 0;
+    Workspace ws;
+};
+
+static void ws_free(Workspace &w) {
+    void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
+                    w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    if (w.host) cudaFreeHost(w.host);
+    w = Workspace();
+}
+
+// ------------------------------------------------------------------------------------ device gate
+extern "C" int kmb200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+extern "C" int kmb200_device_ok(void) {
+    const int n = kmb200_device_count();
+    for (int i = 0; i < n; ++i) {
+        int major = 0;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, i) == cudaSuccess && major == 10)
+            return 1;
+    }
+    return 0;
+}
+
+static int require_device() {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(KMB200_ERR_DEVICE, "no usable CUDA device: %s (libkmeans_b200 has no CPU fallback)",
+                    cudaGetErrorString(e));
+    }
+    int major = 0;
+    CU_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (major != 10)
+        return fail(KMB200_ERR_DEVICE, "device %d has compute capability %d.x; sm_100 (B200) is required", dev,
+                    major);
+    return 0;
+}
+
+extern "C" int kmb200_set_device(int32_t ordinal) {
+    CU_TRY(cudaSetDevice(ordinal));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+// 2-D FP32 row-major [rows x ld] tensor, box = 32 columns x box_rows rows, 128-byte swizzle.
+static int make_map(CUtensorMap *m, const float *base, uint64_t rows, uint64_t ld, uint32_t box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return fail(KMB200_ERR_DEVICE, "cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[2] = {ld, rows};
+    cuuint64_t strides[1] = {ld * sizeof(float)};
+    cuuint32_t box[2] = {32, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(KMB200_ERR_DEVICE, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ table API
+extern "C" int kmb200_table_create(int64_t rows, int32_t cols, kmb200_table **out) {
+    if (!out || rows <= 0 || cols <= 0) return fail(KMB200_ERR_ARG, "table_create: rows and cols must be positive");
+    if (rows >= (int64_t)2147483647 - 1024)
+        return fail(KMB200_ERR_LIMIT, "table_create: at most 2^31-1025 rows per GPU (row indices are int32)");
+    KM_TRY(require_device());
+    kmb200_table *t = new kmb200_table();
+    cudaGetDevice(&t->device);
+    t->rows = rows;
+    t->d = cols;
+    t->ld = (cols + 31) / 32 * 32;
+    cudaDeviceGetAttribute(&t->num_sms, cudaDevAttrMultiProcessorCount, t->device);
+    cudaError_t e = cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&t->X, (size_t)rows * t->ld * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&t->xnorm, (size_t)rows * sizeof(float));
+    if (e == cudaSuccess && t->ld != t->d) e = cudaMemsetAsync(t->X, 0, (size_t)rows * t->ld * sizeof(float), t->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(t->xnorm, 0, (size_t)rows * sizeof(float), t->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+    if (e != cudaSuccess) {
+        const int code = e == cudaErrorMemoryAllocation ? KMB200_ERR_MEMORY : KMB200_ERR_DEVICE;
+        fail(code, "table_create(%lld x %d): %s", (long long)rows, cols, cudaGetErrorString(e));
+        cudaGetLastError();
+        if (t->X) cudaFree(t->X);
+        if (t->xnorm) cudaFree(t->xnorm);
+        if (t->stream) cudaStreamDestroy(t->stream);
+        delete t;
+        return code;
+    }
+    *out = t;
+    return 0;
+}
+
+extern "C" int kmb200_table_free(kmb200_table *t) {
+    if (!t) return 0;
+    cudaSetDevice(t->device);
+    cudaStreamSynchronize(t->stream);
+    ws_free(t->ws);
+    if (t->stage) cudaFree(t->stage);
+    cudaFree(t->X);
+    cudaFree(t->xnorm);
+    cudaStreamDestroy(t->stream);
+    delete t;
+    return 0;
+}
+
+extern "C" int64_t kmb200_table_rows(const kmb200_table *t) { return t ? t->rows : -1; }
+extern "C" int32_t kmb200_table_cols(const kmb200_table *t) { return t ? t->d : -1; }
+
+static int launch_rownorm(kmb200_table *t, int64_t row0, int64_t nrows) {
+    const int64_t warps = (nrows + 3) / 4;
+    int blocks = (int)std::min<int64_t>((warps * 32 + 255) / 256, (int64_t)t->num_sms * 16);
+    if (blocks < 1) blocks = 1;
+    rownorm_kernel<<<blocks, 256, 0, t->stream>>>(t->X, t->xnorm, row0, nrows, t->ld);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+
+template <typename T>
+static int append_rows(kmb200_table *t, int64_t row0, const T *rows, int64_t nrows, int32_t ncols) {
+    if (!t || !rows) return fail(KMB200_ERR_ARG, "table_append: null argument");
+    if (ncols != t->d) return fail(KMB200_ERR_ARG, "table_append: ncols %d != table cols %d", ncols, t->d);
+    if (row0 < 0 || nrows < 0 || row0 + nrows > t->rows)
+        return fail(KMB200_ERR_ARG, "table_append: rows [%lld, %lld) outside the table of %lld rows",
+                    (long long)row0, (long long)(row0 + nrows), (long long)t->rows);
+    if (nrows == 0) return 0;
+    CU_TRY(cudaSetDevice(t->device));
+    if (sizeof(T) == sizeof(float)) {
+        // FP32 input lands directly in the table (strided copy when the row is padded)
+        const int64_t max_h = 1 << 20;
+        for (int64_t r = 0; r < nrows; r += max_h) {
+            const int64_t h = std::min(max_h, nrows - r);
+            CU_TRY(cudaMemcpy2DAsync(t->X + (row0 + r) * t->ld, (size_t)t->ld * 4, rows + r * t->d, (size_t)t->d * 4,
+                                     (size_t)t->d * 4, (size_t)h, cudaMemcpyHostToDevice, t->stream));
+        }
+    } else {
+        // FP64 input: staged in device memory, rounded to FP32 by a kernel
+        const size_t want = std::min<size_t>((size_t)nrows * t->d * sizeof(T), (size_t)256 << 20);
+        if (t->stage_bytes < want) {
+            if (t->stage) cudaFree(t->stage);
+            t->stage = nullptr;
+            t->stage_bytes = 0;
+            CU_TRY(cudaMalloc(&t->stage, want));
+            t->stage_bytes = want;
+        }
+        const int64_t rows_per = std::max<int64_t>(1, (int64_t)(t->stage_bytes / ((size_t)t->d * sizeof(T))));
+        for (int64_t r = 0; r < nrows; r += rows_per) {
+            const int64_t h = std::min(rows_per, nrows - r);
+            CU_TRY(cudaMemcpyAsync(t->stage, rows + r * t->d, (size_t)h * t->d * sizeof(T), cudaMemcpyHostToDevice,
+                                   t->stream));
+            const int64_t total = h * t->d;
+            const int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)t->num_sms * 32);
+            convert_rows_kernel<T><<<blocks, 256, 0, t->stream>>>(reinterpret_cast<const T *>(t->stage),
+                                                                  t->X + (row0 + r) * t->ld, h, t->d, t->ld);
+            CU_TRY(cudaGetLastError());
+        }
+    }
+    KM_TRY(launch_rownorm(t, row0, nrows));
+    CU_TRY(cudaStreamSynchronize(t->stream));
+    return 0;
+}
+
+extern "C" int kmb200_table_append_f64(kmb200_table *t, int64_t row0, const double *rows, int64_t nrows,
+                                       int32_t ncols) {
+    return append_rows<double>(t, row0, rows, nrows, ncols);
+}
+extern "C" int kmb200_table_append_f32(kmb200_table *t, int64_t row0, const float *rows, int64_t nrows,
+                                       int32_t ncols) {
+    return append_rows<float>(t, row0, rows, nrows, ncols);
+}
+
+extern "C" int kmb200_table_read_rows(const kmb200_table *t, int64_t row0, int64_t nrows, float *out) {
+    if (!t || !out) return fail(KMB200_ERR_ARG, "table_read_rows: null argument");
+    if (row0 < 0 || nrows < 0 || row0 + nrows > t->rows) return fail(KMB200_ERR_ARG, "table_read_rows: range");
+    if (nrows == 0) return 0;
+    CU_TRY(cudaSetDevice(t->device));
+    CU_TRY(cudaMemcpy2DAsync(out, (size_t)t->d * 4, t->X + row0 * t->ld, (size_t)t->ld * 4, (size_t)t->d * 4,
+                             (size_t)nrows, cudaMemcpyDeviceToHost, t->stream));
+    CU_TRY(cudaStreamSynchronize(t->stream));
+    return 0;
+}
+
+extern "C" int kmb200_table_fill_blobs(kmb200_table *t, const float *centres, int32_t k_true, uint64_t seed,
+                                       int64_t row_offset) {
+    if (!t || !centres || k_true <= 0) return fail(KMB200_ERR_ARG, "table_fill_blobs: bad argument");
+    CU_TRY(cudaSetDevice(t->device));
+    float *dc = nullptr;
+    CU_TRY(cudaMalloc(&dc, (size_t)k_true * t->d * sizeof(float)));
+    cudaError_t e = cudaMemcpyAsync(dc, centres, (size_t)k_true * t->d * sizeof(float), cudaMemcpyHostToDevice, t->stream);
+    if (e == cudaSuccess) {
+        blobs_kernel<<<t->num_sms * 16, 256, 0, t->stream>>>(t->X, t->rows, t->d, t->ld, dc, k_true, seed, row_offset);
+        e = cudaGetLastError();
+    }
+    int rc = 0;
+    if (e == cudaSuccess) rc = launch_rownorm(t, 0, t->rows);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+    cudaFree(dc);
+    if (e != cudaSuccess) return fail(KMB200_ERR_DEVICE, "table_fill_blobs: %s", cudaGetErrorString(e));
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------ communicator
+extern "C" int kmb200_comm_unique_id(uint8_t id[KMB200_UNIQUE_ID_BYTES]) {
+    if (!id) return fail(KMB200_ERR_ARG, "comm_unique_id: null");
+    KM_TRY(nccl_load());
+    ncclUniqueId uid;
+    static_assert(sizeof(ncclUniqueId) == KMB200_UNIQUE_ID_BYTES, "ncclUniqueId size");
+    NCCL_TRY(g_nccl.GetUniqueId(&uid));
+    memcpy(id, &uid, sizeof(uid));
+    return 0;
+}
+
+extern "C" int kmb200_comm_init(int32_t world, int32_t rank, const uint8_t id[KMB200_UNIQUE_ID_BYTES],
+                                kmb200_comm **out) {
+    if (!out || !id || world < 1 || rank < 0 || rank >= world) return fail(KMB200_ERR_ARG, "comm_init: bad argument");
+    KM_TRY(require_device());
+    KM_TRY(nccl_load());
+    ncclUniqueId uid;
+    memcpy(&uid, id, sizeof(uid));
+    kmb200_comm *c = new kmb200_comm();
+    c->world = world;
+    c->rank = rank;
+    ncclResult_t r = g_nccl.CommInitRank(&c->comm, world, uid, rank);
+    if (r != ncclSuccess) {
+        delete c;
+        return fail(KMB200_ERR_COMM, "ncclCommInitRank(world=%d, rank=%d) failed: %s", world, rank,
+                    g_nccl.GetErrorString(r));
+    }
+    *out = c;
+    return 0;
+}
+extern "C" int32_t kmb200_comm_rank(const kmb200_comm *c) { return c ? c->rank : 0; }
+extern "C" int32_t kmb200_comm_size(const kmb200_comm *c) { return c ? c->world : 1; }
+extern "C" int kmb200_comm_destroy(kmb200_comm *c) {
+    if (!c) return 0;
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    delete c;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ workspace
+static int pick_bn(int k) { return k <= 16 ? 16 : k <= 32 ? 32 : k <= 64 ? 64 : 128; }
+
+template <typename T>
+static int dmalloc(T **p, size_t count) {
+    CU_TRY(cudaMalloc(reinterpret_cast<void **>(p), std::max<size_t>(count, 1) * sizeof(T)));
+    return 0;
+}
+
+static int ws_prepare(kmb200_table *t, int k) {
+    Workspace &w = t->ws;
+    if (w.k == k && w.cent) return 0;
+    ws_free(w);
+    w.k = k;
+    w.bn = pick_bn(k);
+    w.kpad = (k + w.bn - 1) / w.bn * w.bn;
+    const size_t ld = t->ld, n = (size_t)t->rows;
+    w.max_chunks = (int64_t)((n + kSegChunk - 1) / kSegChunk) + k;
+    KM_TRY(dmalloc(&w.cent, (size_t)w.kpad * ld));
+    KM_TRY(dmalloc(&w.cent2, (size_t)w.kpad * ld));
+    CU_TRY(cudaMemset(w.cent2, 0, (size_t)w.kpad * ld * sizeof(double)));
+    KM_TRY(dmalloc(&w.bhi, (size_t)w.kpad * ld));
+    KM_TRY(dmalloc(&w.blo, (size_t)w.kpad * ld));
+    KM_TRY(dmalloc(&w.cnorm, (size_t)w.kpad));
+    KM_TRY(dmalloc(&w.cstats, 4));
+    KM_TRY(dmalloc(&w.labels, n));
+    KM_TRY(dmalloc(&w.order, n));
+    KM_TRY(dmalloc(&w.flag_list, n));
+    KM_TRY(dmalloc(&w.flag_count, 4));
+    KM_TRY(dmalloc(&w.counts, (size_t)k + 1));
+    KM_TRY(dmalloc(&w.offsets, (size_t)k + 1));
+    KM_TRY(dmalloc(&w.cursor, (size_t)k + 1));
+    KM_TRY(dmalloc(&w.chunk_off, (size_t)k + 1));
+    KM_TRY(dmalloc(&w.part, (size_t)w.max_chunks * ld));
+    KM_TRY(dmalloc(&w.cpart, (size_t)w.max_chunks));
+    KM_TRY(dmalloc(&w.red, (size_t)k * ld + k + 1));
+    KM_TRY(dmalloc(&w.costj, (size_t)k));
+    KM_TRY(dmalloc(&w.flags, 4));
+    CU_TRY(cudaMallocHost(reinterpret_cast<void **>(&w.host), sizeof(Workspace::Host)));
+    KM_TRY(make_map(&w.tm_x, t->X, (uint64_t)t->rows, ld, kTileM));
+    KM_TRY(make_map(&w.tm_bhi, w.bhi, (uint64_t)w.kpad, ld, (uint32_t)w.bn));
+    KM_TRY(make_map(&w.tm_blo, w.blo, (uint64_t)w.kpad, ld, (uint32_t)w.bn));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ launches
+static float score_eps(int ld) {
+    if (g_passes == 3) return (float)(g_eps_scale * ldexp(2.0 + 0.5 * std::sqrt((double)ld), -20));
+    return (float)(g_eps_scale * 1.25 * ldexp(1.0, -10));
+}
+
+template <int BN>
+static int launch_assign_bn(kmb200_table *t) {
+    Workspace &w = t->ws;
+    using Cfg = AssignCfg<BN>;
+    static bool attr_set[64] = {false};
+    const int stages = Cfg::stages();
+    const int smem = Cfg::smem_bytes(stages);
+    if (!attr_set[t->device & 63]) {
+        CU_TRY(cudaFuncSetAttribute(assign_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_set[t->device & 63] = true;
+    }
+    AssignParams p;
+    p.cnorm = w.cnorm;
+    p.xnorm = t->xnorm;
+    p.cstats = w.cstats;
+    p.labels = w.labels;
+    p.flag_count = w.flag_count;
+    p.flag_list = w.flag_list;
+    p.flag_cap = (int32_t)t->rows;
+    p.n = (int32_t)t->rows;
+    p.num_row_tiles = (int32_t)((t->rows + kTileM - 1) / kTileM);
+    p.num_col_tiles = w.kpad / BN;
+    p.num_k_chunks = t->ld / kChunkK;
+    p.stages = stages;
+    p.passes = g_passes;
+    p.eps = score_eps(t->ld);
+    p.dbg_scores = g_dbg_scores;
+    p.kpad = w.kpad;
+    const int grid = std::min(p.num_row_tiles, t->num_sms);
+    assign_tc_kernel<BN><<<grid, kAssignThreads, smem, t->stream>>>(w.tm_x, w.tm_bhi, w.tm_blo, p);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches++;
+    return 0;
+}
+
+static int launch_split(kmb200_table *t) {
+    Workspace &w = t->ws;
+    CU_TRY(cudaMemsetAsync(w.cstats, 0, 4 * sizeof(float), t->stream));
+    split_centers_kernel<<<w.kpad, 128, 0, t->stream>>>(w.cent, w.bhi, w.blo, w.cnorm, w.cstats, w.k, t->ld);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches++;
+    return 0;
+}
+
+static int launch_assign(kmb200_table *t) {
+    Workspace &w = t->ws;
+    CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
+    if (g_force_simt) {
+        recheck_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, w.cent, nullptr, nullptr, 0, t->rows, w.k, t->ld,
+                                                             w.labels);
+        CU_TRY(cudaGetLastError());
+        g_prof.kernel_launches++;
+        return 0;
+    }
+    switch (w.bn) {
+        case 16: return launch_assign_bn<16>(t);
+        case 32: return launch_assign_bn<32>(t);
+        case 64: return launch_assign_bn<64>(t);
+        default: return launch_assign_bn<128>(t);
+    }
+}
+
+static int launch_recheck(kmb200_table *t) {
+    Workspace &w = t->ws;
+    if (g_force_simt) return 0;
+    recheck_kernel<<<t->num_sms * 4, 256, 0, t->stream>>>(t->X, w.cent, w.flag_list, w.flag_count, (int32_t)t->rows,
+                                                         t->rows, w.k, t->ld, w.labels);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches++;
+    return 0;
+}
+
+static int launch_bucket(kmb200_table *t) {
+    Workspace &w = t->ws;
+    const int k = w.k;
+    const int blocks = (int)((t->rows + kBucketRows - 1) / kBucketRows);
+    const size_t sh = k <= kHistSmemMax ? (size_t)k * sizeof(int32_t) : 0;
+    CU_TRY(cudaMemsetAsync(w.counts, 0, ((size_t)k + 1) * sizeof(int32_t), t->stream));
+    label_hist_kernel<<<blocks, 256, sh, t->stream>>>(w.labels, t->rows, k, w.counts);
+    CU_TRY(cudaGetLastError());
+    scan_kernel<<<1, 1024, 0, t->stream>>>(w.counts, k, w.offsets, w.cursor, w.chunk_off);
+    CU_TRY(cudaGetLastError());
+    scatter_kernel<<<blocks, 256, sh, t->stream>>>(w.labels, t->rows, k, w.cursor, w.order);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches += 3;
+    return 0;
+}
+
+static int launch_accumulate(kmb200_table *t) {
+    Workspace &w = t->ws;
+    const int ld = t->ld;
+    const size_t sh = (size_t)std::max(8 * 1024, ld * 8);
+    segment_sums_kernel<<<(unsigned)w.max_chunks, 256, sh, t->stream>>>(t->X, w.cent, w.order, w.offsets, w.chunk_off,
+                                                                        w.k, ld, w.part, w.cpart);
+    CU_TRY(cudaGetLastError());
+    segment_reduce_kernel<<<w.k, 128, 0, t->stream>>>(w.part, w.cpart, w.offsets, w.chunk_off, w.k, ld, w.red, w.costj);
+    CU_TRY(cudaGetLastError());
+    cost_sum_kernel<<<1, 1024, 0, t->stream>>>(w.costj, w.k, ld, w.red);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches += 3;
+    return 0;
+}
+
+static int do_allreduce(kmb200_table *t, kmb200_comm *comm) {
+    if (!comm || comm->world == 1) return 0;
+    Workspace &w = t->ws;
+    NCCL_TRY(g_nccl.AllReduce(w.red, w.red, (size_t)w.k * t->ld + w.k + 1, ncclDouble, ncclSum, comm->comm, t->stream));
+    return 0;
+}
+
+static int upload_centers(kmb200_table *t, const double *centers, int k, int d) {
+    Workspace &w = t->ws;
+    CU_TRY(cudaMemsetAsync(w.cent, 0, (size_t)w.kpad * t->ld * sizeof(double), t->stream));
+    CU_TRY(cudaMemcpy2DAsync(w.cent, (size_t)t->ld * 8, centers, (size_t)d * 8, (size_t)d * 8, (size_t)k,
+                             cudaMemcpyHostToDevice, t->stream));
+    return 0;
+}
+static int download_centers(kmb200_table *t, double *out, int k, int d) {
+    Workspace &w = t->ws;
+    CU_TRY(cudaMemcpy2DAsync(out, (size_t)d * 8, w.cent, (size_t)t->ld * 8, (size_t)d * 8, (size_t)k,
+                             cudaMemcpyDeviceToHost, t->stream));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ empty clusters
+// oneDAL's finalizeCompute gives an empty cluster the farthest remaining candidate row and takes that
+// row's distance out of the objective.  Rare, host-driven: m = number of
+// empty clusters; every rank finds its m farthest rows, the lists are all-gathered and merged in
+// (distance desc, rank asc, row asc) order identically on every rank.
+static int handle_empty_clusters(kmb200_table *t, kmb200_comm *comm, int m, double tol, double *cost,
+                                 int *moved_extra) {
+    Workspace &w = t->ws;
+    const int k = w.k, ld = t->ld, d = t->d;
+    const int world = comm ? comm->world : 1;
+    const int64_t n = t->rows;
+    g_prof.empty_cluster_events++;
+    double *dist = nullptr, *bval = nullptr, *dgather = nullptr;
+    int32_t *bidx = nullptr, *excl = nullptr;
+    const int nb = std::min<int>(t->num_sms * 4, 1024);
+    const int rec = 2 + d;  // distance, local row, row values
+    std::vector<double> mine((size_t)m * rec, 0.0), all((size_t)m * rec * world, 0.0);
+    std::vector<int32_t> chosen;
+    std::vector<float> rowbuf(d);
+    int rc = 0;
+    auto cleanup = [&]() {
+        if (dist) cudaFree(dist);
+        if (bval) cudaFree(bval);
+        if (bidx) cudaFree(bidx);
+        if (excl) cudaFree(excl);
+        if (dgather) cudaFree(dgather);
+    };
+#define EC_TRY(expr)                                                                     \
+    do {                                                                                 \
+        cudaError_t e__ = (expr);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            cleanup();                                                                   \
+            return fail(KMB200_ERR_DEVICE, "%s failed: %s", #expr, cudaGetErrorString(e__)); \
+        }                                                                                \
+    } while (0)
+    EC_TRY(cudaMalloc(&dist, (size_t)n * sizeof(double)));
+    EC_TRY(cudaMalloc(&bval, (size_t)(nb + 1) * sizeof(double)));
+    EC_TRY(cudaMalloc(&bidx, (size_t)(nb + 1) * sizeof(int32_t)));
+    EC_TRY(cudaMalloc(&excl, (size_t)std::max(m, 1) * sizeof(int32_t)));
+    // distances to the centres this iteration's assignment used: w.cent still holds them (finalize
+    // wrote the new centres to w.cent2)
+    rowdist_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, w.cent, w.labels, n, ld, dist);
+    EC_TRY(cudaGetLastError());
+    g_prof.kernel_launches++;
+    for (int e = 0; e < m; ++e) {
+        if (e > 0) EC_TRY(cudaMemcpyAsync(excl, chosen.data(), chosen.size() * sizeof(int32_t), cudaMemcpyHostToDevice, t->stream));
+        argmax_kernel<<<nb, 256, 0, t->stream>>>(dist, n, excl, (int)chosen.size(), bval, bidx, 0);
+        argmax_kernel<<<1, 256, 0, t->stream>>>(nullptr, 0, nullptr, 0, bval, bidx, nb);
+        g_prof.kernel_launches += 2;
+        double v;
+        int32_t idx;
+        EC_TRY(cudaMemcpyAsync(&v, bval + nb, sizeof(double), cudaMemcpyDeviceToHost, t->stream));
+        EC_TRY(cudaMemcpyAsync(&idx, bidx + nb, sizeof(int32_t), cudaMemcpyDeviceToHost, t->stream));
+        EC_TRY(cudaStreamSynchronize(t->stream));
+        double *r = &mine[(size_t)e * rec];
+        if (idx < 0) {
+            r[0] = -1.0;
+            r[1] = -1.0;
+            continue;
+        }
+        chosen.push_back(idx);
+        EC_TRY(cudaMemcpyAsync(rowbuf.data(), t->X + (size_t)idx * t->ld, (size_t)d * sizeof(float), cudaMemcpyDeviceToHost, t->stream));
+        EC_TRY(cudaStreamSynchronize(t->stream));
+        r[0] = v;
+        r[1] = (double)idx;
+        for (int c = 0; c < d; ++c) r[2 + c] = (double)rowbuf[c];
+    }
+    if (world > 1) {
+        const size_t cnt = (size_t)m * rec;
+        EC_TRY(cudaMalloc(&dgather, cnt * (world + 1) * sizeof(double)));
+        EC_TRY(cudaMemcpyAsync(dgather, mine.data(), cnt * sizeof(double), cudaMemcpyHostToDevice, t->stream));
+        ncclResult_t r = g_nccl.AllGather(dgather, dgather + cnt, cnt, ncclDouble, comm->comm, t->stream);
+        if (r != ncclSuccess) {
+            cleanup();
+            return fail(KMB200_ERR_COMM, "ncclAllGather failed: %s", g_nccl.GetErrorString(r));
+        }
+        EC_TRY(cudaMemcpyAsync(all.data(), dgather + cnt, cnt * world * sizeof(double), cudaMemcpyDeviceToHost, t->stream));
+        EC_TRY(cudaStreamSynchronize(t->stream));
+    } else {
+        all = mine;
+    }
+    // merge: (distance desc, rank asc, row asc); records are already rank-major, row order inside a
+    // rank is distance desc with row-asc ties, so a stable sort by distance keeps the rule.
+    std::vector<int> idx((size_t)m * world);
+    for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
+    std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return all[(size_t)a * rec] > all[(size_t)b * rec]; });
+    // substitute in cluster-index order
+    std::vector<double> red_counts(k);
+    EC_TRY(cudaMemcpyAsync(red_counts.data(), w.red + (size_t)k * t->ld, (size_t)k * sizeof(double), cudaMemcpyDeviceToHost, t->stream));
+    EC_TRY(cudaStreamSynchronize(t->stream));
+    std::vector<double> oldc(d);
+    int used = 0;
+    for (int j = 0; j < k; ++j) {
+        if (red_counts[j] > 0.0) continue;
+        if (used >= (int)idx.size() || !(all[(size_t)idx[used] * rec] > 0.0)) {
+            rc = fail(KMB200_ERR_EMPTY, "cluster %d is empty and no positive-distance candidate row is left", j);
+            break;
+        }
+        const double *r = &all[(size_t)idx[used] * rec];
+        ++used;
+        EC_TRY(cudaMemcpyAsync(oldc.data(), w.cent + (size_t)j * t->ld, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, t->stream));
+        EC_TRY(cudaStreamSynchronize(t->stream));
+        double s = 0.0;
+        for (int c = 0; c < d; ++c) {
+            const double df = r[2 + c] - oldc[c];
+            s += df * df;
+        }
+        if (!(s <= tol * tol)) (*moved_extra)++;
+        EC_TRY(cudaMemcpyAsync(w.cent2 + (size_t)j * t->ld, r + 2, (size_t)d * sizeof(double), cudaMemcpyHostToDevice, t->stream));
+        EC_TRY(cudaStreamSynchronize(t->stream));
+        *cost -= r[0];
+    }
+#undef EC_TRY
+    cleanup();
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------ profile
+struct EventPool {
+    std::vector<cudaEvent_t> ev;
+    int per_iter = 7;
+    int cap_iters = 0;
+    ~EventPool() {
+        for (auto e : ev) cudaEventDestroy(e);
+    }
+    int ensure(int iters) {
+        iters = std::min(iters, 1024);
+        while ((int)ev.size() < iters * per_iter) {
+            cudaEvent_t e;
+            CU_TRY(cudaEventCreate(&e));
+            ev.push_back(e);
+        }
+        cap_iters = iters;
+        return 0;
+    }
+};
+static thread_local EventPool g_events;
+
+static void prof_reset() { memset(&g_prof, 0, sizeof(g_prof)); }
+
+extern "C" int kmb200_get_profile(kmb200_profile *out) {
+    if (!out) return fail(KMB200_ERR_ARG, "get_profile: null");
+    *out = g_prof;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ the driver
+static int check_fit_args(kmb200_table *t, const double *centers, int k, int d) {
+    if (!t || !centers) return fail(KMB200_ERR_ARG, "null table or centres");
+    if (k <= 0) return fail(KMB200_ERR_ARG, "k must be positive (got %d)", k);
+    if (d != t->d) return fail(KMB200_ERR_ARG, "centre dimension %d != table cols %d", d, t->d);
+    if (k > 65536) return fail(KMB200_ERR_LIMIT, "k = %d is beyond the supported 65536", k);
+    return 0;
+}
+
+extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init_centers, int32_t k, int32_t d,
+                          double tol, int32_t max_iter, double *out_centers, double *out_cost, int32_t *out_iters) {
+    KM_TRY(check_fit_args(t, init_centers, k, d));
+    if (!out_centers || !out_cost || !out_iters) return fail(KMB200_ERR_ARG, "fit: null output");
+    if (max_iter < 0) return fail(KMB200_ERR_ARG, "fit: max_iter must be >= 0");
+    if (comm && comm->world > 1) KM_TRY(nccl_load());
+    CU_TRY(cudaSetDevice(t->device));
+    KM_TRY(require_device());
+    prof_reset();
+    KM_TRY(ws_prepare(t, k));
+    Workspace &w = t->ws;
+    cudaStream_t st = t->stream;
+    KM_TRY(upload_centers(t, init_centers, k, d));
+    KM_TRY(launch_split(t));
+    KM_TRY(g_events.ensure(max_iter));
+
+    double cost = 0.0;
+    int it = 0;
+    bool converged = false;
+    const int P = g_events.per_iter;
+    for (it = 0; it < max_iter && !converged; ++it) {
+        const bool timed = it < g_events.cap_iters;
+        cudaEvent_t *ev = timed ? &g_events.ev[(size_t)it * P] : nullptr;
+        if (timed) CU_TRY(cudaEventRecord(ev[0], st));
+        KM_TRY(launch_assign(t));
+        if (timed) CU_TRY(cudaEventRecord(ev[1], st));
+        KM_TRY(launch_recheck(t));
+        if (timed) CU_TRY(cudaEventRecord(ev[2], st));
+        KM_TRY(launch_bucket(t));
+        if (timed) CU_TRY(cudaEventRecord(ev[3], st));
+        KM_TRY(launch_accumulate(t));
+        if (timed) CU_TRY(cudaEventRecord(ev[4], st));
+        KM_TRY(do_allreduce(t, comm));
+        if (timed) CU_TRY(cudaEventRecord(ev[5], st));
+        CU_TRY(cudaMemsetAsync(w.flags, 0, 4 * sizeof(int32_t), st));
+        finalize_kernel<<<k, 128, (size_t)d * sizeof(double), st>>>(w.red, w.cent, w.cent2, k, t->ld, d, tol, w.flags);
+        CU_TRY(cudaGetLastError());
+        g_prof.kernel_launches++;
+        // one host round trip per iteration: the reference's iteration count must be reproduced
+        // exactly, so the converged flag (and the rare empty-cluster count) is read every time
+        CU_TRY(cudaMemcpyAsync(&w.host->cost, w.red + (size_t)k * t->ld + k, sizeof(double), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaMemcpyAsync(w.host->flags, w.flags, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaMemcpyAsync(&w.host->flag_count, w.flag_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaStreamSynchronize(st));
+        cost = w.host->cost;
+        int moved = w.host->flags[0];
+        if (w.host->flags[1] > 0) KM_TRY(handle_empty_clusters(t, comm, w.host->flags[1], tol, &cost, &moved));
+        std::swap(w.cent, w.cent2);
+        KM_TRY(launch_split(t));  // TF32 split + norms of the new centres for the next assignment
+        if (timed) CU_TRY(cudaEventRecord(ev[6], st));
+        g_prof.rechecked_rows += g_force_simt ? 0 : std::min<int64_t>(w.host->flag_count, t->rows);
+        converged = tol >= 0.0 && moved == 0;
+    }
+    KM_TRY(download_centers(t, out_centers, k, d));
+    CU_TRY(cudaStreamSynchronize(st));
+    *out_cost = cost;
+    *out_iters = it;
+    g_prof.iterations = it;
+    const int timed_iters = std::min(it, g_events.cap_iters);
+    for (int i = 0; i < timed_iters; ++i) {
+        cudaEvent_t *ev = &g_events.ev[(size_t)i * P];
+        float ms[6] = {0, 0, 0, 0, 0, 0};
+        for (int s = 0; s < 6; ++s) cudaEventElapsedTime(&ms[s], ev[s], ev[s + 1]);
+        g_prof.assign_ms += ms[0];
+        g_prof.recheck_ms += ms[1];
+        g_prof.bucket_ms += ms[2];
+        g_prof.accumulate_ms += ms[3];
+        g_prof.allreduce_ms += ms[4];
+        g_prof.finalize_ms += ms[5];
+    }
+    if (timed_iters > 0) {
+        float tot = 0.f;
+        cudaEventElapsedTime(&tot, g_events.ev[0], g_events.ev[(size_t)(timed_iters - 1) * P + 6]);
+        g_prof.total_ms = tot;
+    }
+    return 0;
+}
+
+extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *centers, int32_t k, int32_t d,
+                             int32_t *labels_host, int64_t *sizes_host, double *cost_host) {
+    KM_TRY(check_fit_args(t, centers, k, d));
+    if (comm && comm->world > 1) KM_TRY(nccl_load());
+    CU_TRY(cudaSetDevice(t->device));
+    KM_TRY(require_device());
+    prof_reset();
+    KM_TRY(ws_prepare(t, k));
+    Workspace &w = t->ws;
+    cudaStream_t st = t->stream;
+    KM_TRY(g_events.ensure(1));
+    cudaEvent_t *ev = &g_events.ev[0];
+    KM_TRY(upload_centers(t, centers, k, d));
+    KM_TRY(launch_split(t));
+    CU_TRY(cudaEventRecord(ev[0], st));
+    KM_TRY(launch_assign(t));
+    CU_TRY(cudaEventRecord(ev[1], st));
+    KM_TRY(launch_recheck(t));
+    CU_TRY(cudaEventRecord(ev[2], st));
+    KM_TRY(launch_bucket(t));
+    CU_TRY(cudaEventRecord(ev[3], st));
+    KM_TRY(launch_accumulate(t));
+    CU_TRY(cudaEventRecord(ev[4], st));
+    KM_TRY(do_allreduce(t, comm));
+    CU_TRY(cudaEventRecord(ev[5], st));
+    if (labels_host)
+        CU_TRY(cudaMemcpyAsync(labels_host, w.labels, (size_t)t->rows * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    std::vector<double> tail((size_t)k + 1);
+    CU_TRY(cudaMemcpyAsync(tail.data(), w.red + (size_t)k * t->ld, ((size_t)k + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(&w.host->flag_count, w.flag_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    if (sizes_host)
+        for (int j = 0; j < k; ++j) sizes_host[j] = (int64_t)llround(tail[j]);
+    if (cost_host) *cost_host = tail[k];
+    g_prof.iterations = 1;
+    g_prof.rechecked_rows = g_force_simt ? 0 : std::min<int64_t>(w.host->flag_count, t->rows);
+    cudaEventElapsedTime(&g_prof.assign_ms, ev[0], ev[1]);
+    cudaEventElapsedTime(&g_prof.recheck_ms, ev[1], ev[2]);
+    cudaEventElapsedTime(&g_prof.bucket_ms, ev[2], ev[3]);
+    cudaEventElapsedTime(&g_prof.accumulate_ms, ev[3], ev[4]);
+    cudaEventElapsedTime(&g_prof.allreduce_ms, ev[4], ev[5]);
+    cudaEventElapsedTime(&g_prof.total_ms, ev[0], ev[5]);
+    return 0;
+}
+
+// Test hook: the raw tensor-core scores ||c_j||^2 - 2 x.c_j (FP32) of every row against every padded
+// centre column, so tests can measure the 3xTF32 error against FP64 and validate the near-tie bound.
+extern "C" int kmb200_debug_scores(kmb200_table *t, const double *centers, int32_t k, int32_t d, float *scores_host,
+                                   int32_t *kpad_out) {
+    KM_TRY(check_fit_args(t, centers, k, d));
+    CU_TRY(cudaSetDevice(t->device));
+    KM_TRY(require_device());
+    KM_TRY(ws_prepare(t, k));
+    Workspace &w = t->ws;
+    if (kpad_out) *kpad_out = w.kpad;
+    if (!scores_host) return 0;
+    float *dev = nullptr;
+    CU_TRY(cudaMalloc(&dev, (size_t)t->rows * w.kpad * sizeof(float)));
+    int rc = upload_centers(t, centers, k, d);
+    if (!rc) rc = launch_split(t);
+    const int simt = g_force_simt;
+    g_force_simt = 0;
+    g_dbg_scores = dev;
+    if (!rc) rc = launch_assign(t);
+    g_dbg_scores = nullptr;
+    g_force_simt = simt;
+    cudaError_t e = cudaMemcpyAsync(scores_host, dev, (size_t)t->rows * w.kpad * sizeof(float), cudaMemcpyDeviceToHost, t->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+    cudaFree(dev);
+    if (rc) return rc;
+    if (e != cudaSuccess) return fail(KMB200_ERR_DEVICE, "debug_scores: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ misc
+extern "C" int kmb200_set_option(const char *name, double value) {
+    if (!name) return fail(KMB200_ERR_ARG, "set_option: null name");
+    if (!strcmp(name, "eps_scale")) {
+        if (!(value > 0)) return fail(KMB200_ERR_ARG, "eps_scale must be > 0");
+        g_eps_scale = value;
+    } else if (!strcmp(name, "passes")) {
+        if (value != 1 && value != 3) return fail(KMB200_ERR_ARG, "passes must be 1 or 3");
+        g_passes = (int)value;
+    } else if (!strcmp(name, "force_simt")) {
+        g_force_simt = value != 0;
+    } else {
+        return fail(KMB200_ERR_ARG, "unknown option '%s'", name);
+    }
+    return 0;
+}
+
+extern "C" const char *kmb200_last_error(void) { return g_err.c_str(); }
+extern "C" const char *kmb200_version(void) { return "kmeans_b200 0.1 (sm_100a; tcgen05 3xTF32 assign)"; }

@@ -1,0 +1,202 @@
+"""FP64 CPU oracle for the K-means Lloyd path of OAP MLlib  --  TEST INFRASTRUCTURE ONLY.
+
+This file is the checker, never the product: only ``tests/``, ``__graft_entry__.smoke()``
+and ``bench.py``'s CPU-baseline / ``--impl reference`` legs may import it.  The shipped
+path (``oap_mllib_b200``) never routes through it and fails loudly without its CUDA library.
+
+What it restates (reference = /root/reference, read-only):
+
+* Lloyd driver loop, iteration count, returned cost, convergence rule:
+  ``mllib-dal/src/main/native/KMeansDALImpl.cpp:135-168`` (isCenterConverged /
+  areAllCentersConverged: every centre has sum_d (new-old)^2 <= tol^2, sequential FP64 sum)
+  and ``:195-248`` (``for (it = 0; it < iteration_num && !converged; it++)``; the cost
+  returned is the objective of the LAST executed assignment step, i.e. measured against
+  that iteration's *input* centroids; ``iterationNum`` = executed iterations).
+* What goes in / comes out: ``mllib-dal/src/main/scala/org/apache/spark/ml/clustering/
+  KMeansDALImpl.scala:48-76,84-99``.
+* The per-iteration arithmetic lives in Intel oneDAL 2021.2.0
+  (``kmeans::Distributed<step1Local,double>`` at ``KMeansDALImpl.cpp:70-77`` and
+  ``step2Master`` at ``:103-130``), a system-scope dependency that is NOT under
+  /root/reference (``mllib-dal/pom.xml:20,64-70``).  Its published algorithm (lloydDense):
+  per row argmin_j(||c_j||^2 - 2 x.c_j) with a strict ``>`` scan (lowest index wins ties),
+  objective += that + ||x||^2, per-cluster FP64 sums and int counts, centre = sum * (1/count)
+  (reciprocal multiply), empty cluster -> farthest remaining "candidate" row, whose distance
+  is subtracted from the objective.  The in-tree readable statement of the same step is the
+  vanilla Spark loop ``mllib-dal/src/main/scala/org/apache/spark-3.1.1/mllib/clustering/
+  KMeans.scala:275-335`` which the reference's own test asserts equal to the DAL result
+  (``mllib-dal/src/test/scala/org/apache/spark/ml/clustering/IntelKMeansSuite.scala:479``).
+
+Pinning: checked against every known answer the reference's tests hold for this path
+(``tests/golden/reference_kats.json``, extracted from IntelKMeansSuite.scala:110-141,
+:204-218, :413-480 and examples/data/sample_kmeans_data.txt).  The reference tests do NOT
+pin per-iteration cost values, tie-breaking, the empty-cluster rule or the multi-rank merge
+order: for those, **parity is unpinned** (oneDAL cannot be built or run in this image).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+__all__ = ["assign", "lloyd_step", "lloyd", "merge_partials", "finalize", "gaussian_blobs",
+           "row_init_centers", "near_tie_mask"]
+
+
+def assign(X: np.ndarray, C: np.ndarray, block: int = 4096):
+    """One assignment pass (oneDAL step1Local's distance part).
+
+    Returns (labels int32[n], second-best gap info, min squared distance float64[n]).
+    G = ||c||^2 - 2 X C^T by dgemm on row blocks, first minimum wins (np.argmin returns the
+    lowest index among equal minima == oneDAL's strict ``if (min > G[i][j])`` scan).
+    """
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    C = np.ascontiguousarray(C, dtype=np.float64)
+    n = X.shape[0]
+    cn = np.einsum("ij,ij->i", C, C)
+    labels = np.empty(n, dtype=np.int32)
+    best = np.empty(n, dtype=np.float64)
+    second = np.empty(n, dtype=np.float64)
+    Ct2 = (-2.0 * C).T.copy()
+    for r0 in range(0, n, block):
+        xb = X[r0:r0 + block]
+        G = xb @ Ct2
+        G += cn
+        lab = np.argmin(G, axis=1)
+        rows = np.arange(G.shape[0])
+        b = G[rows, lab]
+        if C.shape[0] > 1:
+            G[rows, lab] = np.inf
+            s = G.min(axis=1)
+        else:
+            s = np.full_like(b, np.inf)
+        xn = np.einsum("ij,ij->i", xb, xb)
+        labels[r0:r0 + block] = lab
+        best[r0:r0 + block] = b + xn      # squared distance to the winner (expanded form)
+        second[r0:r0 + block] = s + xn
+    return labels, best, second
+
+
+def near_tie_mask(best: np.ndarray, second: np.ndarray, rel: float = 1e-6) -> np.ndarray:
+    """Rows whose best / second-best squared distances differ by <= rel (relative): the
+    'exact-distance near-ties' BASELINE.json excuses from label identity."""
+    scale = np.maximum(np.abs(second), 1e-300)
+    return (second - best) <= rel * scale
+
+
+def partial_result(X: np.ndarray, C: np.ndarray, block: int = 4096):
+    """oneDAL step1Local PartialResult of one rank: counts, sums, objective, candidates."""
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    k, d = C.shape
+    labels, best, _ = assign(X, C, block)
+    counts = np.bincount(labels, minlength=k).astype(np.int64)
+    sums = np.zeros((k, d), dtype=np.float64)
+    order = np.argsort(labels, kind="stable")
+    if len(order):
+        starts = np.concatenate(([0], np.cumsum(counts)))[:-1]
+        nz = counts > 0
+        red = np.add.reduceat(X[order], starts[nz], axis=0)
+        sums[nz] = red
+    # objective in the direct form sum ||x - c_label||^2 (the expanded form differs by
+    # ~1e-12 relative; both are inside the 1e-5 parity tolerance)
+    diff = X - C[labels]
+    dist = np.einsum("ij,ij->i", diff, diff)
+    objective = float(dist.sum())
+    # candidates for empty clusters: the k rows with the largest distance to their centre
+    m = min(k, X.shape[0])
+    if m:
+        # descending distance, ties -> lowest row index
+        cand = np.lexsort((np.arange(len(dist)), -dist))[:m]
+    else:
+        cand = np.zeros(0, dtype=np.int64)
+    return {"counts": counts, "sums": sums, "objective": objective,
+            "cand_dist": dist[cand].copy(), "cand_rows": X[cand].copy(), "labels": labels}
+
+
+def merge_partials(parts):
+    """oneDAL step2Master.compute(): element-wise sums over ranks; candidates merged keeping
+    the k largest distances (rank order breaks ties)."""
+    counts = sum(p["counts"] for p in parts)
+    sums = np.sum([p["sums"] for p in parts], axis=0)
+    objective = float(sum(p["objective"] for p in parts))
+    cd = np.concatenate([p["cand_dist"] for p in parts])
+    cr = np.concatenate([p["cand_rows"] for p in parts], axis=0)
+    k = len(counts)
+    keep = np.lexsort((np.arange(len(cd)), -cd))[:k]
+    return {"counts": counts, "sums": sums, "objective": objective,
+            "cand_dist": cd[keep], "cand_rows": cr[keep]}
+
+
+def finalize(merged, old_centers: np.ndarray):
+    """oneDAL step2Master.finalizeCompute(): centre = sum * (1/count); an empty cluster takes
+    the next unused candidate (descending distance) and that distance leaves the objective."""
+    counts, sums = merged["counts"], merged["sums"]
+    k, d = sums.shape
+    new = np.empty((k, d), dtype=np.float64)
+    objective = merged["objective"]
+    used = 0
+    for j in range(k):
+        if counts[j] > 0:
+            new[j] = sums[j] * (1.0 / float(counts[j]))
+        else:
+            if used >= len(merged["cand_dist"]) or not merged["cand_dist"][used] > 0.0:
+                raise RuntimeError("more empty clusters than positive-distance candidates")
+            new[j] = merged["cand_rows"][used]
+            objective -= float(merged["cand_dist"][used])
+            used += 1
+    return new, objective
+
+
+def centers_converged(old: np.ndarray, new: np.ndarray, tol: float) -> bool:
+    """KMeansDALImpl.cpp:135-168 -- every centre: sequential sum_d (new-old)^2 <= tol*tol."""
+    diff = new - old
+    moved = np.zeros(old.shape[0], dtype=np.float64)
+    for c in range(old.shape[1]):           # sequential in d, like the reference loop
+        moved += diff[:, c] * diff[:, c]
+    return bool(np.all(moved <= tol * tol))
+
+
+def lloyd_step(shards, C: np.ndarray, block: int = 4096):
+    """One kmeans_compute() (KMeansDALImpl.cpp:34-133): step1 per rank, gather, step2."""
+    parts = [partial_result(X, C, block) for X in shards]
+    merged = merge_partials(parts)
+    new, objective = finalize(merged, C)
+    return new, objective, merged["counts"], [p["labels"] for p in parts]
+
+
+def lloyd(X, init_centers, tol: float = 1e-4, max_iter: int = 20, n_ranks: int = 1,
+          block: int = 4096, return_labels: bool = False):
+    """The whole cKMeansDALComputeWithInitCenters (KMeansDALImpl.cpp:175-249).
+
+    Returns (centers k x d float64, total_cost, iterations[, labels of the last assignment]).
+    max_iter == 0: the reference returns an uninitialised cost (its :195); we return 0.0.
+    """
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    C = np.array(init_centers, dtype=np.float64, copy=True)
+    bounds = np.linspace(0, X.shape[0], n_ranks + 1).astype(np.int64)
+    shards = [X[bounds[r]:bounds[r + 1]] for r in range(n_ranks)]
+    cost, it, converged, labels = 0.0, 0, False, None
+    while it < max_iter and not converged:
+        new, cost, _, labs = lloyd_step(shards, C, block)
+        converged = centers_converged(C, new, tol)
+        C = new
+        labels = np.concatenate(labs)
+        it += 1
+    if return_labels:
+        return C, cost, it, labels
+    return C, cost, it
+
+
+# ---------------------------------------------------------------------------------------
+# synthetic inputs: Gaussian blobs, centre_j ~ U(-10,10)^d, unit noise
+# ---------------------------------------------------------------------------------------
+def gaussian_blobs(n: int, d: int, k_true: int, seed: int = 42, dtype=np.float32):
+    rng = np.random.default_rng(seed)
+    centres = rng.uniform(-10.0, 10.0, size=(k_true, d))
+    lab = rng.integers(0, k_true, size=n)
+    X = centres[lab] + rng.standard_normal(size=(n, d))
+    return X.astype(dtype), lab.astype(np.int32), centres
+
+
+def row_init_centers(X: np.ndarray, k: int) -> np.ndarray:
+    """Deterministic stand-in for Spark's initRandom: rows floor(j*N/k), j = 0..k-1."""
+    n = X.shape[0]
+    idx = (np.arange(k, dtype=np.int64) * n) // k
+    return np.asarray(X[idx], dtype=np.float64)
