@@ -163,6 +163,9 @@ def run_ours(args, rank, local_rank, world):
         rows = args.rows
     torch.cuda.set_device(local_rank)
     _lib.check(m.lib().kmb200_set_device(local_rank))
+    for opt in args.option:
+        name, val = opt.split("=")
+        _lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -340,6 +343,7 @@ def main():
     ap.add_argument("--cpu-sample-rows", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--option", action="append", default=[], help="library option name=value (experiments)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

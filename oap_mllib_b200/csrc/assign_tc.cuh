@@ -51,7 +51,7 @@ struct AssignParams {
     const float *cstats;   // [0] = max_j ||c_j||
     int32_t *labels;       // [n]
     int32_t *flag_count;   // number of near-tie rows appended to flag_list
-    int32_t *flag_list;    // [flag_cap]
+    int2 *flag_list;       // [flag_cap] (row, runner-up centre) or (row, -1) when a third centre is inside the bound too
     int32_t flag_cap;
     int32_t n;             // rows in the table
     int32_t num_row_tiles; // ceil(n / 128)
@@ -62,6 +62,7 @@ struct AssignParams {
     float eps;             // relative error bound of one score
     float *dbg_scores;     // optional [n x kpad] dump of the tensor-core scores (tests only), else nullptr
     int32_t kpad;
+    int32_t knockout;      // debugging only: 1 = no TMA, 2 = no transform work, 4 = no epilogue work (results invalid)
 };
 
 template <int BN>
@@ -118,20 +119,24 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
     if (warp == 0) {
         // ================================ TMA producer ================================
         if (lane == 0) {
-            uint32_t it = 0;
+            uint32_t s = 0, ph = 0;
             const uint32_t stage_tx = kXStageBytes + (p.passes == 3 ? 2 : 1) * Cfg::kBStageBytes;
             for (int rt = blockIdx.x; rt < p.num_row_tiles; rt += gridDim.x) {
                 for (int nt = 0; nt < NT; ++nt) {
-                    for (int kc = 0; kc < KC; ++kc, ++it) {
-                        const uint32_t s = it % S, ph = (it / S) & 1;
+                    for (int kc = 0; kc < KC; ++kc) {
                         mbar_wait(&empty[s], ph ^ 1);
                         uint8_t *st = smem + s * Cfg::kStageBytes;
-                        mbar_arrive_expect_tx(&full[s], stage_tx);
-                        tma_load_2d(&tm_x, &full[s], st, kc * kChunkK, rt * kTileM);
-                        tma_load_2d(&tm_bhi, &full[s], st + kXStageBytes, kc * kChunkK, nt * BN);
-                        if (p.passes == 3)
-                            tma_load_2d(&tm_blo, &full[s], st + kXStageBytes + Cfg::kBStageBytes, kc * kChunkK,
-                                        nt * BN);
+                        if (p.knockout & 1) {
+                            mbar_arrive(&full[s]);
+                        } else {
+                            mbar_arrive_expect_tx(&full[s], stage_tx);
+                            tma_load_2d(&tm_x, &full[s], st, kc * kChunkK, rt * kTileM);
+                            tma_load_2d(&tm_bhi, &full[s], st + kXStageBytes, kc * kChunkK, nt * BN);
+                            if (p.passes == 3)
+                                tma_load_2d(&tm_blo, &full[s], st + kXStageBytes + Cfg::kBStageBytes, kc * kChunkK,
+                                            nt * BN);
+                        }
+                        if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
                     }
                 }
             }
@@ -140,7 +145,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         // ================================ MMA issuer ==================================
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc_tf32(kTileM, BN);
-            uint32_t it = 0, tile = 0;
+            uint32_t it = 0, tile = 0, s = 0, ph = 0;
             for (int rt = blockIdx.x; rt < p.num_row_tiles; rt += gridDim.x) {
                 for (int nt = 0; nt < NT; ++nt, ++tile) {
                     const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
@@ -148,7 +153,6 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
                     for (int kc = 0; kc < KC; ++kc, ++it) {
-                        const uint32_t s = it % S, ph = (it / S) & 1;
                         const uint32_t xb = it & 1, xph = (it >> 1) & 1;
                         mbar_wait(&full[s], ph);     // B chunk landed in shared memory
                         mbar_wait(&a_full[xb], xph); // transform wrote the A chunk to TMEM
@@ -174,6 +178,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                         }
                         tc_commit(&empty[s]);     // shared-memory stage may be refilled
                         tc_commit(&a_empty[xb]);  // TMEM A buffer may be rewritten
+                        if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
                     }
                     tc_commit(&acc_full[ab]);  // accumulator tile complete -> epilogue
                 }
@@ -183,14 +188,19 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         // ================================ transform ===================================
         const int r = threadIdx.x - 128;  // row inside the tile == TMEM lane
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
-        uint32_t it = 0;
+        uint32_t it = 0, s = 0, ph = 0;
         for (int rt = blockIdx.x; rt < p.num_row_tiles; rt += gridDim.x) {
             for (int nt = 0; nt < NT; ++nt) {
                 for (int kc = 0; kc < KC; ++kc, ++it) {
-                    const uint32_t s = it % S, ph = (it / S) & 1;
                     const uint32_t xb = it & 1, xph = (it >> 1) & 1;
                     mbar_wait(&full[s], ph);
                     const uint8_t *xs = smem + s * Cfg::kStageBytes + r * 128;
+                    if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
+                    if (p.knockout & 2) {
+                        mbar_wait(&a_empty[xb], xph ^ 1);
+                        mbar_arrive(&a_full[xb]);
+                        continue;
+                    }
                     float x[32];
 #pragma unroll
                     for (int g = 0; g < 8; ++g) {
@@ -225,8 +235,8 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         const float cmax = p.cstats[0];
         uint32_t tile = 0;
         for (int rt = blockIdx.x; rt < p.num_row_tiles; rt += gridDim.x) {
-            float best = __int_as_float(0x7f800000), second = best;
-            int bidx = 0;
+            float best = __int_as_float(0x7f800000), second = best, third = best;
+            int bidx = 0, sidx = 0;
             for (int nt = 0; nt < NT; ++nt, ++tile) {
                 const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
                 float *cn = cn_s + ab * BN;
@@ -234,6 +244,10 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                 asm volatile("bar.sync 1, 128;" ::: "memory");  // epilogue warps only
                 mbar_wait(&acc_full[ab], aph);
                 tc_fence_after();
+                if (p.knockout & 4) {
+                    mbar_arrive(&acc_empty[ab]);
+                    continue;
+                }
                 const uint32_t acc = tmem_base + lane_addr + Cfg::kAccCol0 + ab * BN;
                 constexpr int G = BN >= 32 ? 32 : 16;
 #pragma unroll 1
@@ -247,8 +261,14 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                         const float sc = __uint_as_float(v[i]) + cn[c0 + i];
                         if (p.dbg_scores != nullptr && rt * kTileM + r < p.n)
                             p.dbg_scores[(size_t)(rt * kTileM + r) * p.kpad + nt * BN + c0 + i] = sc;
+                        // running top-3 values with the indices of the best two; strict '<' keeps
+                        // the lowest index among equal scores
+                        const int j = nt * BN + c0 + i;
+                        const bool lt1 = sc < best, lt2 = sc < second;
+                        third = fminf(third, fmaxf(sc, second));
+                        sidx = lt1 ? bidx : (lt2 ? j : sidx);
                         second = fminf(second, fmaxf(sc, best));
-                        if (sc < best) bidx = nt * BN + c0 + i;  // strict: lowest index wins ties
+                        bidx = lt1 ? j : bidx;
                         best = fminf(best, sc);
                     }
                 }
@@ -262,7 +282,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                 const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
                 if (second - best <= bound) {
                     const int pos = atomicAdd(p.flag_count, 1);
-                    if (pos < p.flag_cap) p.flag_list[pos] = row;
+                    if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, (third - best <= bound) ? -1 : sidx);
                 }
             }
         }

@@ -107,11 +107,27 @@ __global__ void split_centers_kernel(const double *__restrict__ cent, float *__r
 }
 
 // ------------------------------------------------------------------ exact (FP64) assignment
-// One warp per listed row (list == nullptr: every row).  score_j = ||c_j||^2 - 2 x.c_j in FP64,
-// first minimum wins.  Used (a) to re-evaluate rows whose tensor-core top-2 gap is inside the error
-// bound, (b) as the CUDA-core reference path for tests (option "force_simt").
+// score_j = ||c_j||^2 - 2 x.c_j in FP64 for one row held by a warp (lanes split the columns).
+__device__ __forceinline__ double exact_score(const float *__restrict__ xrow, const double *__restrict__ cj, int ld,
+                                              int lane) {
+    double dot = 0.0, cn = 0.0;
+    for (int c0 = lane; c0 < ld; c0 += 32) {
+        const double c = __ldg(cj + c0);
+        dot = fma((double)__ldg(xrow + c0), c, dot);
+        cn = fma(c, c, cn);
+    }
+    dot = warp_sum(dot);
+    cn = warp_sum(cn);
+    return cn - 2.0 * dot;
+}
+
+// One warp per listed entry.  The tensor-core epilogue lists every row whose best / second-best gap
+// is inside the score error bound as (row, runner-up centre) -- then the winner is decided between
+// labels[row] and the runner-up in FP64 -- or as (row, -1) when a third centre is inside the bound
+// too, in which case all k centres are re-scored.  list == nullptr: every row, all centres (the
+// CUDA-core reference path behind option "force_simt").  First minimum (lowest index) wins ties.
 __global__ void recheck_kernel(const float *__restrict__ X, const double *__restrict__ cent,
-                               const int32_t *__restrict__ list, const int32_t *__restrict__ list_count,
+                               const int2 *__restrict__ list, const int32_t *__restrict__ list_count,
                                int32_t list_cap, int64_t n, int k, int ld, int32_t *__restrict__ labels) {
     const int lane = threadIdx.x & 31;
     const int64_t warp_global = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
@@ -121,20 +137,35 @@ __global__ void recheck_kernel(const float *__restrict__ X, const double *__rest
         count = *list_count;
         if (count > list_cap) count = list_cap;
     }
-    const int per_lane = ld >> 5;  // ld is a multiple of 32
-    const bool cached = per_lane <= 16;  // rows up to 512 floats are held in registers
+    const int per_lane = ld >> 5;        // ld is a multiple of 32
+    const bool cached = per_lane <= 16;  // rows up to 512 floats are held in registers for the full scan
     for (int64_t w = warp_global; w < count; w += nwarps) {
-        const int64_t row = list ? (int64_t)list[w] : w;
+        int64_t row = w;
+        int runner = -1;
+        if (list) {
+            const int2 e = list[w];
+            row = e.x;
+            runner = e.y;
+        }
+        const float *xrow = X + row * ld;
+        if (runner >= 0) {
+            const int cur = labels[row];
+            const double s_cur = exact_score(xrow, cent + (size_t)cur * ld, ld, lane);
+            const double s_run = exact_score(xrow, cent + (size_t)runner * ld, ld, lane);
+            const bool take = s_run < s_cur || (s_run == s_cur && runner < cur);
+            if (lane == 0 && take) labels[row] = runner;
+            continue;
+        }
         double xr[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i)
-            xr[i] = (cached && i < per_lane) ? (double)__ldg(X + row * ld + i * 32 + lane) : 0.0;
+        for (int i = 0; i < 16; ++i) xr[i] = (cached && i < per_lane) ? (double)__ldg(xrow + i * 32 + lane) : 0.0;
         double best = INFINITY;
         int bidx = 0;
         for (int j = 0; j < k; ++j) {
             const double *cj = cent + (size_t)j * ld;
-            double dot = 0.0, cn = 0.0;
+            double sc;
             if (cached) {
+                double dot = 0.0, cn = 0.0;
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
                     if (i < per_lane) {
@@ -143,16 +174,12 @@ __global__ void recheck_kernel(const float *__restrict__ X, const double *__rest
                         cn = fma(c, c, cn);
                     }
                 }
+                dot = warp_sum(dot);
+                cn = warp_sum(cn);
+                sc = cn - 2.0 * dot;
             } else {
-                for (int c0 = lane; c0 < ld; c0 += 32) {
-                    const double c = __ldg(cj + c0);
-                    dot = fma((double)__ldg(X + row * ld + c0), c, dot);
-                    cn = fma(c, c, cn);
-                }
+                sc = exact_score(xrow, cj, ld, lane);
             }
-            dot = warp_sum(dot);
-            cn = warp_sum(cn);
-            const double sc = cn - 2.0 * dot;
             if (sc < best) {
                 best = sc;
                 bidx = j;

@@ -52,6 +52,7 @@ static int fail(int code, const char *fmt, ...) {
 static double g_eps_scale = 1.0;
 static int g_passes = 3;
 static int g_force_simt = 0;
+static int g_knockout = 0;
 static float *g_dbg_scores = nullptr;  // set only inside kmb200_debug_scores
 
 // ------------------------------------------------------------------------------------ NCCL (dlopen)
@@ -109,7 +110,8 @@ struct Workspace {
     double *cent = nullptr;       // [kpad x ld] FP64 master copy of the centres (padding zero)
     double *cent2 = nullptr;      // [kpad x ld] output of finalize; swapped with cent every iteration
     float *bhi = nullptr, *blo = nullptr, *cnorm = nullptr, *cstats = nullptr;
-    int32_t *labels = nullptr, *order = nullptr, *flag_list = nullptr, *flag_count = nullptr;
+    int32_t *labels = nullptr, *order = nullptr, *flag_count = nullptr;
+    int2 *flag_list = nullptr;    // near-tie rows: (row, runner-up centre or -1)
     int32_t *counts = nullptr, *offsets = nullptr, *cursor = nullptr, *chunk_off = nullptr;
     double *part = nullptr, *cpart = nullptr, *red = nullptr, *costj = nullptr;
     int32_t *flags = nullptr;      // [0] centres that moved > tol, [1] empty clusters
@@ -442,8 +444,12 @@ static int ws_prepare(kmb200_table *t, int k) {
 }
 
 // ------------------------------------------------------------------------------------ launches
+// Relative bound on |tensor-core score - exact score| / (2|x||c|max + |c|max^2).  3xTF32: the FP32
+// accumulator in TMEM is updated 3*ld/8 times per score and each update may lose up to one ulp
+// (the tensor core truncates), plus the TF32 hi/lo split residuals (~3*2^-22) and the FP32 norm /
+// final add; measured maxima sit at ~0.35 of this (tests/test_gpu_parity.py).
 static float score_eps(int ld) {
-    if (g_passes == 3) return (float)(g_eps_scale * ldexp(2.0 + 0.5 * std::sqrt((double)ld), -20));
+    if (g_passes == 3) return (float)(g_eps_scale * ldexp(3.0 * ld / 8.0 + 16.0, -24));
     return (float)(g_eps_scale * 1.25 * ldexp(1.0, -10));
 }
 
@@ -475,6 +481,7 @@ static int launch_assign_bn(kmb200_table *t) {
     p.eps = score_eps(t->ld);
     p.dbg_scores = g_dbg_scores;
     p.kpad = w.kpad;
+    p.knockout = g_knockout;
     const int grid = std::min(p.num_row_tiles, t->num_sms);
     assign_tc_kernel<BN><<<grid, kAssignThreads, smem, t->stream>>>(w.tm_x, w.tm_bhi, w.tm_blo, p);
     CU_TRY(cudaGetLastError());
@@ -889,6 +896,8 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         g_passes = (int)value;
     } else if (!strcmp(name, "force_simt")) {
         g_force_simt = value != 0;
+    } else if (!strcmp(name, "knockout")) {
+        g_knockout = (int)value;  // timing experiments only: results are invalid when non-zero
     } else {
         return fail(KMB200_ERR_ARG, "unknown option '%s'", name);
     }
