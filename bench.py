@@ -232,6 +232,8 @@ def run_ours(args, rank, local_rank, world):
     clocks = sampler.stop()
     prof = _lib.profile()
     assert iters == args.steps
+    if any(o.startswith("role_prof") for o in args.option):
+        _lib.check(m.lib().kmb200_set_option(b"role_prof", 0.0))   # prints the MMA-warp cycle counters
     dev_ms = max_over_ranks(prof["total_ms"])
     wall_ms = max_over_ranks(wall * 1e3)
     ms_per_step = dev_ms / args.steps

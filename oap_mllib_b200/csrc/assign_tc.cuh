@@ -62,6 +62,7 @@ struct AssignParams {
     float eps;             // relative error bound of one score
     float *dbg_scores;     // optional [n x kpad] dump of the tensor-core scores (tests only), else nullptr
     int32_t kpad;
+    long long *role_prof;  // optional cycle counters of the MMA-issuer warp of CTA 0 (diagnostics), else nullptr
     int32_t knockout;      // debugging only: 1 = no TMA, 2 = no transform work, 4 = no epilogue work (results invalid)
 };
 
@@ -118,13 +119,15 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
 
     if (warp == 0) {
         // ================================ TMA producer ================================
-        if (lane == 0) {
-            uint32_t s = 0, ph = 0;
-            const uint32_t stage_tx = kXStageBytes + (p.passes == 3 ? 2 : 1) * Cfg::kBStageBytes;
-            for (int rt = blockIdx.x; rt < p.num_row_tiles; rt += gridDim.x) {
-                for (int nt = 0; nt < NT; ++nt) {
-                    for (int kc = 0; kc < KC; ++kc) {
-                        mbar_wait(&empty[s], ph ^ 1);
+        // The whole warp walks the loop (converged), one elected lane issues: this keeps the
+        // uniform-datapath instructions (UTMALDG) out of divergent code.
+        uint32_t s = 0, ph = 0;
+        const uint32_t stage_tx = kXStageBytes + (p.passes == 3 ? 2 : 1) * Cfg::kBStageBytes;
+        for (int rt = blockIdx.x; rt < p.num_row_tiles; rt += gridDim.x) {
+            for (int nt = 0; nt < NT; ++nt) {
+                for (int kc = 0; kc < KC; ++kc) {
+                    mbar_wait(&empty[s], ph ^ 1);
+                    if (elect_one()) {
                         uint8_t *st = smem + s * Cfg::kStageBytes;
                         if (p.knockout & 1) {
                             mbar_arrive(&full[s]);
@@ -136,27 +139,34 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                                 tma_load_2d(&tm_blo, &full[s], st + kXStageBytes + Cfg::kBStageBytes, kc * kChunkK,
                                             nt * BN);
                         }
-                        if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
                     }
+                    __syncwarp();
+                    if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
         // ================================ MMA issuer ==================================
-        if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_tf32(kTileM, BN);
-            uint32_t it = 0, tile = 0, s = 0, ph = 0;
-            for (int rt = blockIdx.x; rt < p.num_row_tiles; rt += gridDim.x) {
-                for (int nt = 0; nt < NT; ++nt, ++tile) {
-                    const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
-                    mbar_wait(&acc_empty[ab], aph ^ 1);  // epilogue has drained this accumulator
+        constexpr uint32_t idesc = make_idesc_tf32(kTileM, BN);
+        uint32_t it = 0, tile = 0, s = 0, ph = 0;
+        long long t_wait_acc = 0, t_wait_full = 0, t_wait_a = 0, t_issue = 0, t_mark = 0;
+        const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
+        for (int rt = blockIdx.x; rt < p.num_row_tiles; rt += gridDim.x) {
+            for (int nt = 0; nt < NT; ++nt, ++tile) {
+                const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
+                if (prof) t_mark = clock64();
+                mbar_wait(&acc_empty[ab], aph ^ 1);  // epilogue has drained this accumulator
+                if (prof) { const long long t = clock64(); t_wait_acc += t - t_mark; t_mark = t; }
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
+                for (int kc = 0; kc < KC; ++kc, ++it) {
+                    const uint32_t xb = it & 1, xph = (it >> 1) & 1;
+                    mbar_wait(&full[s], ph);     // B chunk landed in shared memory
+                    if (prof) { const long long t = clock64(); t_wait_full += t - t_mark; t_mark = t; }
+                    mbar_wait(&a_full[xb], xph); // transform wrote the A chunk to TMEM
+                    if (prof) { const long long t = clock64(); t_wait_a += t - t_mark; t_mark = t; }
                     tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
-                    for (int kc = 0; kc < KC; ++kc, ++it) {
-                        const uint32_t xb = it & 1, xph = (it >> 1) & 1;
-                        mbar_wait(&full[s], ph);     // B chunk landed in shared memory
-                        mbar_wait(&a_full[xb], xph); // transform wrote the A chunk to TMEM
-                        tc_fence_after();
+                    if (elect_one()) {
                         const uint32_t a_hi = tmem_base + xb * 64;
                         const uint32_t a_lo = a_hi + 32;
                         const uint32_t bsm = smem_u32(smem + s * Cfg::kStageBytes + kXStageBytes);
@@ -178,11 +188,20 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                         }
                         tc_commit(&empty[s]);     // shared-memory stage may be refilled
                         tc_commit(&a_empty[xb]);  // TMEM A buffer may be rewritten
-                        if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
+                        if (kc == KC - 1) tc_commit(&acc_full[ab]);  // accumulator tile complete -> epilogue
                     }
-                    tc_commit(&acc_full[ab]);  // accumulator tile complete -> epilogue
+                    __syncwarp();
+                    if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
+                    if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
                 }
             }
+        }
+        if (prof && lane == 0) {
+            p.role_prof[0] = t_wait_acc;
+            p.role_prof[1] = t_wait_full;
+            p.role_prof[2] = t_wait_a;
+            p.role_prof[3] = t_issue;
+            p.role_prof[4] = it;
         }
     } else if (warp >= 4 && warp < 8) {
         // ================================ transform ===================================

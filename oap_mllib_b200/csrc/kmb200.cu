@@ -53,6 +53,7 @@ static double g_eps_scale = 1.0;
 static int g_passes = 3;
 static int g_force_simt = 0;
 static int g_knockout = 0;
+static long long *g_role_prof = nullptr;  // device buffer, allocated by option "role_prof"
 static float *g_dbg_scores = nullptr;  // set only inside kmb200_debug_scores
 
 // ------------------------------------------------------------------------------------ NCCL (dlopen)
@@ -482,6 +483,7 @@ static int launch_assign_bn(kmb200_table *t) {
     p.dbg_scores = g_dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;
+    p.role_prof = g_role_prof;
     const int grid = std::min(p.num_row_tiles, t->num_sms);
     assign_tc_kernel<BN><<<grid, kAssignThreads, smem, t->stream>>>(w.tm_x, w.tm_bhi, w.tm_blo, p);
     CU_TRY(cudaGetLastError());
@@ -896,6 +898,20 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         g_passes = (int)value;
     } else if (!strcmp(name, "force_simt")) {
         g_force_simt = value != 0;
+    } else if (!strcmp(name, "role_prof")) {
+        // diagnostics: value != 0 allocates the counter buffer; value == 0 prints and frees it
+        if (value != 0 && !g_role_prof) {
+            CU_TRY(cudaMalloc(&g_role_prof, 16 * sizeof(long long)));
+            CU_TRY(cudaMemset(g_role_prof, 0, 16 * sizeof(long long)));
+        } else if (value == 0 && g_role_prof) {
+            long long h[16];
+            CU_TRY(cudaDeviceSynchronize());
+            CU_TRY(cudaMemcpy(h, g_role_prof, sizeof(h), cudaMemcpyDeviceToHost));
+            fprintf(stderr, "[kmb200 role_prof] last assign launch, CTA 0 MMA warp: chunks=%lld cycles/chunk: wait_acc=%.1f wait_full=%.1f wait_a=%.1f issue=%.1f\n",
+                    h[4], (double)h[0] / h[4], (double)h[1] / h[4], (double)h[2] / h[4], (double)h[3] / h[4]);
+            cudaFree(g_role_prof);
+            g_role_prof = nullptr;
+        }
     } else if (!strcmp(name, "knockout")) {
         g_knockout = (int)value;  // timing experiments only: results are invalid when non-zero
     } else {

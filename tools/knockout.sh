@@ -1,11 +1,16 @@
 #!/bin/bash
 # Timing experiments for the assign kernel (results are invalid with knockout != 0): which role limits it?
 ROWS=${ROWS:-20000000}
-for opt in "passes=3" "passes=1" "knockout=1" "knockout=2" "knockout=4" "knockout=7" "knockout=3" "knockout=5"; do
+OPTS=${OPTS:-"passes=3 passes=1 knockout=1 knockout=2 knockout=4 knockout=7"}
+for opt in $OPTS; do
   echo "== $opt"
-  timeout -k 5 120 python bench.py --rows $ROWS --steps 3 --warmup 3 --no-e2e --no-cpu --option $opt 2>&1 | tail -1 | python -c "
+  timeout -k 5 120 python bench.py --rows $ROWS --steps 3 --warmup 3 --no-e2e --no-cpu --option $opt --option role_prof=1 2>&1 | grep -E "role_prof|^\{" | python -c "
 import sys, json
-d = json.loads(sys.stdin.read())
-print({k: round(v, 2) for k, v in d['phases_ms_per_step'].items()}, 'rechecked', d['rechecked_rows_per_step'], 'exec TF/s', round(3 * d['roofline']['achieved'], 1))
+for line in sys.stdin:
+    if line.startswith('{'):
+        d = json.loads(line)
+        print({k: round(v, 2) for k, v in d['phases_ms_per_step'].items()}, 'rechecked', d['rechecked_rows_per_step'], 'exec TF/s', round(3 * d['roofline']['achieved'], 1))
+    else:
+        print(line.strip())
 "
 done
