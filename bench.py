@@ -185,8 +185,9 @@ def run_ours(args, rank, local_rank, world):
         return float(t.item())
 
     # ---- shard the rows (strong scaling: the same total N on every GPU count) -----------------
-    bounds = [(rows * r) // world for r in range(world + 1)]
-    n_local, row0 = bounds[rank + 1] - bounds[rank], bounds[rank]
+    from oap_mllib_b200.sharding import shard_bounds
+    row0, row1 = shard_bounds(rows, world)[rank]
+    n_local = row1 - row0
     rng = np.random.default_rng(42)
     centres = rng.uniform(-10, 10, (k, d)).astype(np.float32)
     table = m.Table(n_local, d)

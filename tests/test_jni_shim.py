@@ -1,0 +1,146 @@
+"""The JNI layer (csrc/jni_shim.cpp) driven through a hand-built JNIEnv function table: there is no
+JVM in this image, so the slots the shim uses are filled with ctypes callbacks.  Slot numbers are
+those of the JNI specification's interface function table (mirrored in csrc/jni_min.h)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+SLOTS = dict(FindClass=6, ThrowNew=14, GetObjectClass=31, GetFieldID=94, SetIntField=109, SetLongField=110,
+             SetDoubleField=112, GetStringUTFChars=169, ReleaseStringUTFChars=170, GetArrayLength=171,
+             NewByteArray=176, NewDoubleArray=182, GetByteArrayRegion=200, SetByteArrayRegion=208,
+             SetDoubleArrayRegion=214, GetPrimitiveArrayCritical=222, ReleasePrimitiveArrayCritical=223)
+P = C.c_void_p
+
+
+class FakeJvm:
+    """Objects are small integers; arrays map to numpy buffers; fields are recorded in dicts."""
+
+    def __init__(self):
+        self.objs, self.fields, self.field_names, self.thrown, self.keep = {}, {}, {}, [], []
+        self.next = 100
+        table = (P * 235)()
+        def put(name, restype, argtypes, fn):
+            cb = C.CFUNCTYPE(restype, *argtypes)(fn)
+            self.keep.append(cb)
+            table[SLOTS[name]] = C.cast(cb, P)
+        put("FindClass", P, [P, C.c_char_p], lambda env, n: 7)
+        put("ThrowNew", C.c_int, [P, P, C.c_char_p], lambda env, c, msg: self.thrown.append(msg.decode()) or 0)
+        put("GetObjectClass", P, [P, P], lambda env, o: 8)
+        put("GetFieldID", P, [P, P, C.c_char_p, C.c_char_p], self._field_id)
+        put("SetIntField", None, [P, P, P, C.c_int32], self._set_field)
+        put("SetLongField", None, [P, P, P, C.c_int64], self._set_field)
+        put("SetDoubleField", None, [P, P, P, C.c_double], self._set_field)
+        put("GetStringUTFChars", P, [P, P, P], lambda env, s, c: C.cast(self.objs[s], P).value)
+        put("ReleaseStringUTFChars", None, [P, P, P], lambda env, s, c: None)
+        put("NewByteArray", P, [P, C.c_int32], lambda env, n: self.new(np.zeros(n, np.int8)))
+        put("NewDoubleArray", P, [P, C.c_int32], lambda env, n: self.new(np.zeros(n, np.float64)))
+        put("GetByteArrayRegion", None, [P, P, C.c_int32, C.c_int32, P],
+            lambda env, a, s, n, buf: C.memmove(buf, self.objs[a].ctypes.data + s, n) and None)
+        put("SetByteArrayRegion", None, [P, P, C.c_int32, C.c_int32, P],
+            lambda env, a, s, n, buf: C.memmove(self.objs[a].ctypes.data + s, buf, n) and None)
+        put("SetDoubleArrayRegion", None, [P, P, C.c_int32, C.c_int32, P],
+            lambda env, a, s, n, buf: C.memmove(self.objs[a].ctypes.data + 8 * s, buf, 8 * n) and None)
+        put("GetPrimitiveArrayCritical", P, [P, P, P], lambda env, a, c: self.objs[a].ctypes.data)
+        put("ReleasePrimitiveArrayCritical", None, [P, P, P, C.c_int32], lambda env, a, p, m: None)
+        self.table = table
+        self.table_ptr = P(C.addressof(table))          # JNIEnv  = pointer to the table
+        self.env = C.pointer(self.table_ptr)             # JNIEnv* = what natives receive
+
+    def new(self, obj):
+        self.next += 1
+        self.objs[self.next] = obj
+        return self.next
+
+    def string(self, s):
+        return self.new(C.create_string_buffer(s.encode()))
+
+    def _field_id(self, env, cls, name, sig):
+        fid = 1000 + len(self.field_names)
+        self.field_names[fid] = name.decode()
+        return fid
+
+    def _set_field(self, env, obj, fid, value):
+        self.fields.setdefault(obj, {})[self.field_names[fid]] = value
+
+
+@pytest.fixture()
+def jni(built_lib):
+    h = C.CDLL(built_lib)
+    return h, FakeJvm()
+
+
+def fn(h, name, restype, argtypes):
+    f = getattr(h, name)
+    f.restype, f.argtypes = restype, argtypes
+    return f
+
+
+def test_platform_gate_and_setenv(jni):
+    h, vm = jni
+    ok = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cCheckPlatformCompatibility", C.c_uint8, [P, P])(vm.env, None)
+    assert ok in (0, 1)
+    setenv = fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_setEnv", C.c_int32, [P, P, P, P, C.c_uint8])
+    assert setenv(vm.env, None, vm.string("KMB200_JNI_TEST"), vm.string("ofi"), 1) == 0
+    assert os.environ.get("KMB200_JNI_TEST") == "ofi" or True     # os.environ caches; the libc env is what counts
+    libc = C.CDLL(None)
+    libc.getenv.restype = C.c_char_p
+    assert libc.getenv(b"KMB200_JNI_TEST") == b"ofi"
+    assert fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_isRoot", C.c_uint8, [P, P])(vm.env, None) == 1
+    assert fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_rankID", C.c_int32, [P, P])(vm.env, None) == 0
+
+
+@pytest.mark.gpu
+def test_jni_fit_matches_oracle(jni):
+    from oracle import kmeans_oracle as ko
+    h, vm = jni
+    X, _, _ = ko.gaussian_blobs(5000, 24, 9, seed=3)
+    X = X.astype(np.float64)
+    init = ko.row_init_centers(X, 9)
+    n, d = X.shape
+    new_table = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cNewTable", C.c_int64, [P, P, C.c_int64, C.c_int32])
+    set_batch = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cSetDoubleBatch", None,
+                   [P, P, C.c_int64, C.c_int32, P, C.c_int32, C.c_int32])
+    new_cent = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cNewCenters", C.c_int64, [P, P, C.c_int32, C.c_int32])
+    set_val = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_setNumericTableValue", None,
+                 [P, P, C.c_int64, C.c_int32, C.c_int32, C.c_double])
+    get_cent = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cGetCenters", P, [P, P, C.c_int64])
+    free_cent = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cFreeCenters", None, [P, P, C.c_int64])
+    free_tab = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cFreeDataMemory", None, [P, P, C.c_int64])
+    c_init = fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_c_1init", C.c_int32, [P, P, C.c_int32, C.c_int32, P, P])
+    cleanup = fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_c_1cleanup", None, [P, P])
+    compute = fn(h, "Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansDALComputeWithInitCenters", C.c_int64,
+                 [P, P, C.c_int64, C.c_int64, C.c_int32, C.c_double, C.c_int32, C.c_int32, C.c_int32, P])
+
+    table = new_table(vm.env, None, n, d)
+    assert table != 0 and not vm.thrown, vm.thrown
+    for r0 in range(0, n, 2048):                      # row batches, like the patched OneDAL.scala
+        blk = np.ascontiguousarray(X[r0:r0 + 2048])
+        set_batch(vm.env, None, table, r0, vm.new(blk), blk.shape[0], d)
+    cent = new_cent(vm.env, None, 9, d)
+    for i in range(9):
+        for j in range(d):
+            set_val(vm.env, None, cent, i, j, float(init[i, j]))
+    param = vm.new(object())
+    assert c_init(vm.env, None, 1, 0, vm.new(np.zeros(128, np.int8)), param) == 1
+    assert vm.fields[param] == {"commSize": 1, "rankId": 0}
+    result = vm.new(object())
+    out = compute(vm.env, None, table, cent, 9, 1e-4, 15, 1, 1, result)
+    assert out != 0 and not vm.thrown, vm.thrown
+    got = vm.objs[get_cent(vm.env, None, out)].reshape(9, d)
+    want_c, want_cost, want_it = ko.lloyd(X.astype(np.float32).astype(np.float64), init, 1e-4, 15)
+    assert vm.fields[result]["iterationNum"] == want_it
+    assert abs(vm.fields[result]["totalCost"] - want_cost) <= 1e-5 * want_cost
+    np.testing.assert_allclose(got, want_c, rtol=1e-5, atol=1e-5)
+    cleanup(vm.env, None)
+    free_cent(vm.env, None, out)
+    free_cent(vm.env, None, cent)
+    free_tab(vm.env, None, table)
+    # errors surface as a Java exception, not as a crash: a table with a wrong column count
+    bad = new_cent(vm.env, None, 2, d + 1)
+    t2 = new_table(vm.env, None, 10, d)
+    assert compute(vm.env, None, t2, bad, 2, 1e-4, 1, 1, 1, result) == 0
+    assert vm.thrown and "dimension" in vm.thrown[-1]
+    free_cent(vm.env, None, bad)
+    free_tab(vm.env, None, t2)
