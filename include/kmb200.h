@@ -129,6 +129,31 @@ int kmb200_get_profile(kmb200_profile *out);
  * re-check), "force_simt" (1 = use the CUDA-core FP32 assign kernel instead of tcgen05; debugging). */
 int kmb200_set_option(const char *name, double value);
 
+/* ---- cluster sizes without any device allocation ------------------------------------------------
+ * No counterpart in the reference (its summary pass counts on the JVM).  Histogram of a label
+ * vector: sizes_dev[j] = number of i in [0, n) with labels_dev[i] == j.  Every other entry point of
+ * this library cudaMallocs its scratch; this one does not call cudaMalloc, cudaFree or any other
+ * allocating routine, so it is usable by hosts that cannot allocate on the device when they call
+ * in: executors whose GPU memory has been given entirely to a pool allocator (cudaMalloc then fails
+ * even though the pool has room) and latency-bound loops that must avoid the device-wide
+ * synchronisation an allocation or a free implies.
+ *
+ *   labels_dev  DEVICE pointer, n int32 values, each in [0, k) (anything else is undefined behaviour)
+ *   sizes_dev   DEVICE pointer, k int64 values, overwritten
+ *   cuda_stream a cudaStream_t (NULL = the default stream); the work is only ENQUEUED on it, the
+ *               result is valid once that stream has run it
+ *   limit       k <= 65536: the k int32 counters of scratch sit in a fixed 256 KiB array inside
+ *               the library image (each GPU that loads the library holds it until the process
+ *               exits); larger k is refused with KMB200_ERR_LIMIT
+ *
+ * The first call on a device looks up that array's device address (a one-off driver query, no
+ * allocation): make that first call before starting any stream capture.  All calls on one device
+ * share the array, which keeps the previous call's counts until the next call clears the part it
+ * needs; two calls whose work overlaps on the GPU (different streams, no dependency) race on it and
+ * both results are then garbage -- order them with an event or use one stream. */
+int kmb200_cluster_sizes_noalloc(const int32_t *labels_dev, int64_t n, int32_t k, int64_t *sizes_dev,
+                                 void *cuda_stream);
+
 /* Test hook (no reference counterpart): raw tensor-core scores ||c_j||^2 - 2 x.c_j (FP32) of every
  * row against every padded centre column (rows x kpad, row-major).  scores_host may be NULL to
  * query kpad only.  Lets the tests measure the 3xTF32 error against FP64. */

@@ -887,6 +887,61 @@ extern "C" int kmb200_debug_scores(kmb200_table *t, const double *centers, int32
     return 0;
 }
 
+// ------------------------------------------------------------------------------------ no-allocation entry
+// Cluster sizes from a label vector without touching the device allocator.  The label histogram
+// needs k int32 counters of scratch; the regular path (launch_bucket) keeps them in the workspace
+// that ws_prepare cudaMallocs.  Some hosts of this library must not allocate on the device at call
+// time: an executor whose GPU memory is handed, whole, to a pool allocator (e.g. an RMM pool shared
+// with other Spark plugins) gets out-of-memory from cudaMalloc although the pool has room, and a
+// latency-bound serving loop cannot afford the device-wide synchronisation cudaMalloc / cudaFree
+// imply.  For them the counters live in the module itself: a fixed array that every GPU loading the
+// library carries until the process exits (256 KiB per GPU).
+constexpr int kNoAllocMaxClusters = 65536;
+static __device__ __align__(256) int32_t g_noalloc_counters[kNoAllocMaxClusters];
+// g_noalloc_counters is only a host-side handle here: the device address is looked up once per
+// device (with that device current) and remembered.
+static int32_t *g_noalloc_addr[64] = {nullptr};
+static std::mutex g_noalloc_mu;
+
+extern "C" int kmb200_cluster_sizes_noalloc(const int32_t *labels_dev, int64_t n, int32_t k, int64_t *sizes_dev,
+                                            void *cuda_stream) {
+    if (!labels_dev && n > 0) return fail(KMB200_ERR_ARG, "cluster_sizes_noalloc: labels_dev is null");
+    if (!sizes_dev) return fail(KMB200_ERR_ARG, "cluster_sizes_noalloc: sizes_dev is null");
+    if (n < 0 || k <= 0) return fail(KMB200_ERR_ARG, "cluster_sizes_noalloc: n must be >= 0 and k > 0");
+    if (k > kNoAllocMaxClusters)
+        return fail(KMB200_ERR_LIMIT,
+                    "cluster_sizes_noalloc: k = %d is larger than the built-in scratch of %d counters; use "
+                    "kmb200_assign, which allocates its own",
+                    k, kNoAllocMaxClusters);
+    KM_TRY(require_device());
+    int dev = 0;
+    CU_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(KMB200_ERR_LIMIT, "cluster_sizes_noalloc: device ordinal %d not supported", dev);
+    int32_t *counters = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_addr[dev]) {
+            void *addr = nullptr;
+            CU_TRY(cudaGetSymbolAddress(&addr, g_noalloc_counters));  // this device's copy of the array
+            g_noalloc_addr[dev] = static_cast<int32_t *>(addr);
+        }
+        counters = g_noalloc_addr[dev];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    // the array still holds the previous call's histogram: the k counters used now must start at zero
+    CU_TRY(cudaMemsetAsync(counters, 0, (size_t)k * sizeof(int32_t), st));
+    if (n > 0) {
+        const int64_t blocks = (n + kBucketRows - 1) / kBucketRows;
+        if (blocks > 2147483647LL) return fail(KMB200_ERR_LIMIT, "cluster_sizes_noalloc: too many rows");
+        const size_t sh = k <= kHistSmemMax ? (size_t)k * sizeof(int32_t) : 0;
+        label_hist_kernel<<<(unsigned)blocks, 256, sh, st>>>(labels_dev, n, k, counters);
+        CU_TRY(cudaGetLastError());
+    }
+    counts_to_i64_kernel<<<(k + 255) / 256, 256, 0, st>>>(counters, k, reinterpret_cast<unsigned long long *>(sizes_dev));
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------ misc
 extern "C" int kmb200_set_option(const char *name, double value) {
     if (!name) return fail(KMB200_ERR_ARG, "set_option: null name");
