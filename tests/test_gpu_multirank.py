@@ -1,0 +1,22 @@
+"""Two-GPU parity through NCCL (skipped on a single-GPU box; the N > 1 host logic is covered on CPU
+by tests/test_multirank_cpu.py)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.gpu
+def test_two_gpus_match_two_rank_oracle(built_lib):
+    import oap_mllib_b200 as m
+    if m.lib().kmb200_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29577", os.path.join(ROOT, "tools", "multigpu_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    sys.stdout.write(r.stdout[-4000:])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count(" OK") == 4
