@@ -1,0 +1,318 @@
+// Second-generation assign kernel for rows of at most 256 floats (ld <= 256): same arithmetic as
+// assign_tc_kernel (3xTF32, FP32 accumulators in TMEM, top-3 epilogue), restructured to cut the
+// L2 -> SM traffic and the per-chunk handshakes that limited the first kernel:
+//   * the X tile (128 rows x ld) stays RESIDENT in shared memory for all centroid tiles of a row
+//     tile (loaded once by its own producer warp; the first kernel re-read it k/BN times from L2);
+//   * with CL == 2 the kernel runs as clusters of two CTAs (one TPC): rank 0 loads the B_hi chunk,
+//     rank 1 the B_lo chunk, each MULTICAST into both CTAs' shared memory, so every centroid byte
+//     leaves L2 once per CTA pair; a stage is recycled when BOTH CTAs' MMAs have consumed it
+//     (tcgen05.commit multicast onto both CTAs' "empty" barriers);
+//   * the TMEM A operand is double-buffered at a granularity of TWO K-chunks (2 x 128 columns) and
+//     the MMA warp polls all barriers of a chunk pair together, so one handshake covers 24 MMAs.
+// Roles: warp 0 B producer, warp 1 MMA issuer, warp 2 TMEM allocator, warp 3 X producer,
+// warps 4-7 transform (thread r = row r), warps 8-11 epilogue (thread r = row r).
+#pragma once
+#include "assign_tc.cuh"
+
+namespace kmb {
+
+template <int BN>
+struct Assign2Cfg {
+    static constexpr int kBChunkBytes = BN * kChunkK * 4;     // one of B_hi / B_lo for one K chunk
+    static constexpr int kBStageBytes = 2 * kBChunkBytes;     // hi + lo
+    static constexpr int kACols = 256;                        // 2 buffers x 2 chunks x (32 hi + 32 lo)
+    static constexpr int kAccCol0 = kACols;
+    static constexpr int kTmemCols = 512;
+    static constexpr int kTailBytes = 2 * BN * 4 + (4 * kMaxStages + 8) * 8 + 16;
+    static int stages(int kc) {
+        int s = (227 * 1024 - 1024 - kTailBytes - kc * kXStageBytes) / kBStageBytes;
+        return s > kMaxStages ? kMaxStages : s;
+    }
+    static int smem_bytes(int kc, int stages) { return 1024 + kc * kXStageBytes + stages * kBStageBytes + kTailBytes; }
+};
+
+template <int BN, int CL>
+__global__ void __launch_bounds__(kAssignThreads, 1)
+assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_bhi,
+                  const __grid_constant__ CUtensorMap tm_blo, const AssignParams p) {
+    using Cfg = Assign2Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+
+    const int S = p.stages;
+    const int NT = p.num_col_tiles;
+    const int KC = p.num_k_chunks;       // <= 8
+    const int G = (KC + 1) >> 1;         // chunk pairs per centroid tile
+    uint8_t *xs = smem;                                  // [KC][128 rows x 128 B], swizzled
+    uint8_t *bs = smem + KC * kXStageBytes;              // [S][B_hi chunk | B_lo chunk]
+    uint8_t *tail = bs + S * Cfg::kBStageBytes;
+    float *cn_s = reinterpret_cast<float *>(tail);       // [2][BN]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(tail + 2 * BN * 4);
+    uint64_t *full = bars;                   // B stage landed
+    uint64_t *empty = bars + kMaxStages;     // B stage consumed by the MMAs of all CL CTAs
+    uint64_t *xfull = bars + 2 * kMaxStages; // X chunk landed
+    uint64_t *xempty = bars + 3 * kMaxStages;// X chunk read for the last time by the transform
+    uint64_t *a_full = bars + 4 * kMaxStages;
+    uint64_t *a_empty = a_full + 2;
+    uint64_t *acc_full = a_full + 4;
+    uint64_t *acc_empty = a_full + 6;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 4 * kMaxStages + 8);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = CL > 1 ? cluster_ctarank() : 0u;
+    // row tiles are dealt to clusters; both CTAs of a cluster always run the same number of tiles
+    // (a tile index beyond the table is a dummy: TMA zero-fills it and nothing is stored)
+    const int tile0 = (blockIdx.x / CL) * CL + rank;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_x);
+        tma_prefetch_desc(&tm_bhi);
+        tma_prefetch_desc(&tm_blo);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < kMaxStages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], CL);
+            mbar_init(&xfull[s], 1);
+            mbar_init(&xempty[s], 128);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&a_full[b], 128);
+            mbar_init(&a_empty[b], 1);
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], 128);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 2) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    if (CL > 1) cluster_sync_all();   // the peer's barriers exist before anything is multicast to them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================ B producer ==================================
+        uint32_t s = 0, ph = 0;
+        for (int base = tile0 - (int)rank; base < p.num_row_tiles; base += gridDim.x) {
+            for (int nt = 0; nt < NT; ++nt) {
+                for (int kc = 0; kc < KC; ++kc) {
+                    mbar_wait(&empty[s], ph ^ 1);
+                    if (elect_one()) {
+                        uint8_t *st = bs + s * Cfg::kBStageBytes;
+                        if (p.knockout & 1) {
+                            mbar_arrive(&full[s]);
+                        } else {
+                            mbar_arrive_expect_tx(&full[s], Cfg::kBStageBytes);  // bytes landing in THIS CTA
+                            if (CL == 1) {
+                                tma_load_2d(&tm_bhi, &full[s], st, kc * kChunkK, nt * BN);
+                                tma_load_2d(&tm_blo, &full[s], st + Cfg::kBChunkBytes, kc * kChunkK, nt * BN);
+                            } else if (rank == 0) {
+                                tma_load_2d_mcast(&tm_bhi, &full[s], st, kc * kChunkK, nt * BN, (uint16_t)0x3);
+                            } else {
+                                tma_load_2d_mcast(&tm_blo, &full[s], st + Cfg::kBChunkBytes, kc * kChunkK, nt * BN,
+                                                  (uint16_t)0x3);
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (++s == (uint32_t)S) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 3) {
+        // ================================ X producer ==================================
+        uint32_t xph = 0;
+        for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x) {
+            for (int kc = 0; kc < KC; ++kc) {
+                mbar_wait(&xempty[kc], xph ^ 1);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(&xfull[kc], kXStageBytes);
+                    tma_load_2d(&tm_x, &xfull[kc], xs + kc * kXStageBytes, kc * kChunkK, rt * kTileM);
+                }
+                __syncwarp();
+            }
+            xph ^= 1;
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ==================================
+        constexpr uint32_t idesc = make_idesc_tf32(kTileM, BN);
+        uint32_t grp = 0, tile = 0, s = 0, ph = 0;
+        long long t_wait_acc = 0, t_wait = 0, t_issue = 0, t_mark = 0;
+        const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
+        for (int base = tile0 - (int)rank; base < p.num_row_tiles; base += gridDim.x) {
+            for (int nt = 0; nt < NT; ++nt, ++tile) {
+                const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
+                if (prof) t_mark = clock64();
+                mbar_wait(&acc_empty[ab], aph ^ 1);
+                if (prof) { const long long t = clock64(); t_wait_acc += t - t_mark; t_mark = t; }
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
+                for (int g = 0; g < G; ++g, ++grp) {
+                    const int nch = (2 * g + 1 < KC) ? 2 : 1;
+                    const uint32_t xb = grp & 1, xph = (grp >> 1) & 1;
+                    uint32_t s1 = s + 1, ph1 = ph;
+                    if (s1 == (uint32_t)S) { s1 = 0; ph1 ^= 1; }
+                    if (nch == 2) mbar_wait3(&a_full[xb], xph, &full[s], ph, &full[s1], ph1);
+                    else mbar_wait2(&a_full[xb], xph, &full[s], ph);
+                    if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
+                    tc_fence_after();
+                    if (elect_one()) {
+#pragma unroll
+                        for (int c = 0; c < 2; ++c) {
+                            if (c < nch) {
+                                const uint32_t sc = c == 0 ? s : s1;
+                                const uint32_t a_hi = tmem_base + xb * 128 + c * 64;
+                                const uint32_t a_lo = a_hi + 32;
+                                const uint32_t bsm = smem_u32(bs + sc * Cfg::kBStageBytes);
+                                const uint64_t dhi = make_kmajor_sw128_desc(bsm);
+                                const uint64_t dlo = make_kmajor_sw128_desc(bsm + Cfg::kBChunkBytes);
+#pragma unroll
+                                for (int ks = 0; ks < kChunkK / 8; ++ks) {
+                                    const uint64_t koff = static_cast<uint64_t>(ks * 2);
+                                    const uint32_t first = (g | c | ks) == 0 ? 0u : 1u;
+                                    mma_tf32_ts(d_tmem, a_lo + ks * 8, dhi + koff, idesc, first);  // small terms first
+                                    mma_tf32_ts(d_tmem, a_hi + ks * 8, dlo + koff, idesc, 1u);
+                                    mma_tf32_ts(d_tmem, a_hi + ks * 8, dhi + koff, idesc, 1u);
+                                }
+                                if (CL == 1) tc_commit(&empty[sc]);
+                                else tc_commit_mcast(&empty[sc], (uint16_t)0x3);  // both CTAs may refill it
+                            }
+                        }
+                        tc_commit(&a_empty[xb]);
+                        if (g == G - 1) tc_commit(&acc_full[ab]);
+                    }
+                    __syncwarp();
+                    if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
+                    s = nch == 2 ? s1 + 1 : s1;
+                    ph = ph1;
+                    if (nch == 2 && s == (uint32_t)S) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+        if (prof && lane == 0) {
+            p.role_prof[0] = t_wait_acc;
+            p.role_prof[1] = t_wait;
+            p.role_prof[2] = 0;
+            p.role_prof[3] = t_issue;
+            p.role_prof[4] = grp;
+        }
+    } else if (warp >= 4 && warp < 8) {
+        // ================================ transform ===================================
+        const int r = threadIdx.x - 128;
+        const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        uint32_t grp = 0, xph = 0;
+        for (int base = tile0 - (int)rank; base < p.num_row_tiles; base += gridDim.x) {
+            for (int nt = 0; nt < NT; ++nt) {
+                for (int g = 0; g < G; ++g, ++grp) {
+                    const int nch = (2 * g + 1 < KC) ? 2 : 1;
+                    const uint32_t xb = grp & 1, aph = (grp >> 1) & 1;
+                    bool waited = false;
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        if (c >= nch) break;
+                        const int kc = 2 * g + c;
+                        if (nt == 0) mbar_wait(&xfull[kc], xph);   // X chunk of this row tile has landed
+                        const uint8_t *xrow = xs + kc * kXStageBytes + r * 128;
+                        float x[32];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float4 v = *reinterpret_cast<const float4 *>(xrow + ((q ^ (r & 7)) << 4));
+                            x[4 * q + 0] = v.x;
+                            x[4 * q + 1] = v.y;
+                            x[4 * q + 2] = v.z;
+                            x[4 * q + 3] = v.w;
+                        }
+                        uint32_t hi[32], lo[32];
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const float h = to_tf32_rna(x[i]);
+                            hi[i] = __float_as_uint(h);
+                            lo[i] = __float_as_uint(to_tf32_rna(x[i] - h));
+                        }
+                        if (nt == NT - 1) mbar_arrive(&xempty[kc]);  // last read of this chunk: may be reloaded
+                        if (!waited) {
+                            mbar_wait(&a_empty[xb], aph ^ 1);
+                            tc_fence_after();
+                            waited = true;
+                        }
+                        if (!(p.knockout & 2)) {
+                            const uint32_t a_addr = tmem_base + lane_addr + xb * 128 + c * 64;
+                            tmem_st32(a_addr, hi);
+                            tmem_st32(a_addr + 32, lo);
+                        }
+                    }
+                    tmem_wait_st();
+                    tc_fence_before();
+                    mbar_arrive(&a_full[xb]);
+                }
+            }
+            xph ^= 1;
+        }
+    } else if (warp >= 8) {
+        // ================================ epilogue ====================================
+        const int r = threadIdx.x - 256;
+        const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        const float cmax = p.cstats[0];
+        uint32_t tile = 0;
+        for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x) {
+            float best = __int_as_float(0x7f800000), second = best, third = best;
+            int bidx = 0, sidx = 0;
+            for (int nt = 0; nt < NT; ++nt, ++tile) {
+                const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
+                float *cn = cn_s + ab * BN;
+                if (r < BN) cn[r] = p.cnorm[nt * BN + r];
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                mbar_wait(&acc_full[ab], aph);
+                tc_fence_after();
+                if (p.knockout & 4) {
+                    mbar_arrive(&acc_empty[ab]);
+                    continue;
+                }
+                const uint32_t acc = tmem_base + lane_addr + Cfg::kAccCol0 + ab * BN;
+                constexpr int GW = BN >= 32 ? 32 : 16;
+#pragma unroll 1
+                for (int c0 = 0; c0 < BN; c0 += GW) {
+                    uint32_t v[GW];
+                    if constexpr (GW == 32) tmem_ld32(acc + c0, v);
+                    else tmem_ld16(acc + c0, v);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < GW; ++i) {
+                        const float sc = __uint_as_float(v[i]) + cn[c0 + i];
+                        if (p.dbg_scores != nullptr && rt * kTileM + r < p.n)
+                            p.dbg_scores[(size_t)(rt * kTileM + r) * p.kpad + nt * BN + c0 + i] = sc;
+                        const int j = nt * BN + c0 + i;
+                        const bool lt1 = sc < best, lt2 = sc < second;
+                        third = fminf(third, fmaxf(sc, second));
+                        sidx = lt1 ? bidx : (lt2 ? j : sidx);
+                        second = fminf(second, fmaxf(sc, best));
+                        bidx = lt1 ? j : bidx;
+                        best = fminf(best, sc);
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&acc_empty[ab]);
+            }
+            const int row = rt * kTileM + r;
+            if (row < p.n) {
+                p.labels[row] = bidx;
+                const float xn = sqrtf(p.xnorm[row]);
+                const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
+                if (second - best <= bound) {
+                    const int pos = atomicAdd(p.flag_count, 1);
+                    if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, (third - best <= bound) ? -1 : sidx);
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (CL > 1) cluster_sync_all();   // no CTA leaves while its peer can still multicast / arrive into it
+    if (warp == 2) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+}  // namespace kmb

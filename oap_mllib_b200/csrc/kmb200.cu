@@ -18,6 +18,7 @@
 
 #include "../../include/kmb200.h"
 #include "assign_tc.cuh"
+#include "assign_tc2.cuh"
 #include "kernels_misc.cuh"
 
 using namespace kmb;
@@ -53,6 +54,15 @@ static double g_eps_scale = 1.0;
 static int g_passes = 3;
 static int g_force_simt = 0;
 static int g_knockout = 0;
+static int g_kernel = 2;   // 2 = X-resident / multicast kernel where it applies (ld <= 256), 1 = first-generation kernel
+static int g_cluster = 2;  // CTAs per cluster sharing the centroid tiles by TMA multicast (1 or 2)
+static void env_overrides() {
+    static bool done = false;
+    if (done) return;
+    done = true;
+    if (const char *e = getenv("KMB200_KERNEL")) g_kernel = atoi(e) == 1 ? 1 : 2;
+    if (const char *e = getenv("KMB200_CLUSTER")) g_cluster = atoi(e) == 1 ? 1 : 2;
+}
 static long long *g_role_prof = nullptr;  // device buffer, allocated by option "role_prof"
 static float *g_dbg_scores = nullptr;  // set only inside kmb200_debug_scores
 
@@ -491,6 +501,65 @@ static int launch_assign_bn(kmb200_table *t) {
     return 0;
 }
 
+template <int BN, int CL>
+static int launch_assign2_bn(kmb200_table *t) {
+    Workspace &w = t->ws;
+    using Cfg = Assign2Cfg<BN>;
+    static bool attr_set[64] = {false};
+    const int kc = t->ld / kChunkK;
+    const int stages = Cfg::stages(kc);
+    const int smem = Cfg::smem_bytes(kc, stages);
+    if (!attr_set[t->device & 63]) {
+        CU_TRY(cudaFuncSetAttribute(assign_tc2_kernel<BN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set[t->device & 63] = true;
+    }
+    AssignParams p;
+    p.cnorm = w.cnorm;
+    p.xnorm = t->xnorm;
+    p.cstats = w.cstats;
+    p.labels = w.labels;
+    p.flag_count = w.flag_count;
+    p.flag_list = w.flag_list;
+    p.flag_cap = (int32_t)t->rows;
+    p.n = (int32_t)t->rows;
+    p.num_row_tiles = (int32_t)((t->rows + kTileM - 1) / kTileM);
+    p.num_col_tiles = w.kpad / BN;
+    p.num_k_chunks = kc;
+    p.stages = stages;
+    p.passes = 3;
+    p.eps = score_eps(t->ld);
+    p.dbg_scores = g_dbg_scores;
+    p.kpad = w.kpad;
+    p.knockout = g_knockout;
+    p.role_prof = g_role_prof;
+    const int clusters = std::min((p.num_row_tiles + CL - 1) / CL, t->num_sms / CL);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(clusters * CL));
+    cfg.blockDim = dim3(kAssignThreads);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = t->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CU_TRY(cudaLaunchKernelEx(&cfg, assign_tc2_kernel<BN, CL>, w.tm_x, w.tm_bhi, w.tm_blo, p));
+    g_prof.kernel_launches++;
+    return 0;
+}
+
+template <int CL>
+static int launch_assign2(kmb200_table *t) {
+    switch (t->ws.bn) {
+        case 16: return launch_assign2_bn<16, CL>(t);
+        case 32: return launch_assign2_bn<32, CL>(t);
+        case 64: return launch_assign2_bn<64, CL>(t);
+        default: return launch_assign2_bn<128, CL>(t);
+    }
+}
+
 static int launch_split(kmb200_table *t) {
     Workspace &w = t->ws;
     CU_TRY(cudaMemsetAsync(w.cstats, 0, 4 * sizeof(float), t->stream));
@@ -509,6 +578,11 @@ static int launch_assign(kmb200_table *t) {
         CU_TRY(cudaGetLastError());
         g_prof.kernel_launches++;
         return 0;
+    }
+    env_overrides();
+    if (g_kernel == 2 && g_passes == 3 && t->ld <= 256) {
+        const int row_tiles = (int)((t->rows + kTileM - 1) / kTileM);
+        return (g_cluster == 2 && row_tiles >= 2) ? launch_assign2<2>(t) : launch_assign2<1>(t);
     }
     switch (w.bn) {
         case 16: return launch_assign_bn<16>(t);
@@ -967,6 +1041,14 @@ extern "C" int kmb200_set_option(const char *name, double value) {
             cudaFree(g_role_prof);
             g_role_prof = nullptr;
         }
+    } else if (!strcmp(name, "kernel")) {
+        if (value != 1 && value != 2) return fail(KMB200_ERR_ARG, "kernel must be 1 or 2");
+        env_overrides();
+        g_kernel = (int)value;
+    } else if (!strcmp(name, "cluster")) {
+        if (value != 1 && value != 2) return fail(KMB200_ERR_ARG, "cluster must be 1 or 2");
+        env_overrides();
+        g_cluster = (int)value;
     } else if (!strcmp(name, "knockout")) {
         g_knockout = (int)value;  // timing experiments only: results are invalid when non-zero
     } else {

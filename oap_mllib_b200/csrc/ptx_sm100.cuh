@@ -48,6 +48,69 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     }
 }
 
+// Two barriers polled together so their try_wait latencies overlap (the MMA queue is shallow: every
+// exposed wait leaves the tensor pipe idle).
+__device__ __forceinline__ void mbar_wait2(uint64_t *bar_a, uint32_t par_a, uint64_t *bar_b, uint32_t par_b) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p, q;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 q, [%3], %4;\n\t"
+            "and.pred p, p, q;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar_a)), "r"(par_a), "r"(smem_u32(bar_b)), "r"(par_b)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void mbar_wait3(uint64_t *bar_a, uint32_t par_a, uint64_t *bar_b, uint32_t par_b,
+                                           uint64_t *bar_c, uint32_t par_c) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p, q, r;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 q, [%3], %4;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 r, [%5], %6;\n\t"
+            "and.pred p, p, q;\n\t"
+            "and.pred p, p, r;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar_a)), "r"(par_a), "r"(smem_u32(bar_b)), "r"(par_b), "r"(smem_u32(bar_c)), "r"(par_c)
+            : "memory");
+    } while (!ok);
+}
+
+// ---------------------------------------------------------------- clusters
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load delivered to the same shared-memory offset (and signalling the same mbarrier offset) in
+// every CTA of the cluster whose bit is set in cta_mask.
+__device__ __forceinline__ void tma_load_2d_mcast(const CUtensorMap *m, uint64_t *bar, void *dst, int32_t c0,
+                                                  int32_t c1, uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, "
+        "{%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(cta_mask)
+        : "memory");
+}
+// tcgen05.commit arriving on the barrier at the same offset in every CTA of cta_mask
+__device__ __forceinline__ void tc_commit_mcast(uint64_t *bar, uint16_t cta_mask) {
+    asm volatile(
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"(cta_mask)
+        : "memory");
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
