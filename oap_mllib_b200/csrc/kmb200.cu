@@ -55,7 +55,7 @@ static int g_passes = 3;
 static int g_force_simt = 0;
 static int g_knockout = 0;
 static int g_kernel = 2;   // 2 = X-resident / multicast kernel where it applies (ld <= 256), 1 = first-generation kernel
-static int g_cluster = 2;  // CTAs per cluster sharing the centroid tiles by TMA multicast (1 or 2)
+static int g_cluster = 2;  // 2 = CTA pairs (tcgen05 cta_group::2, centroid tiles split across the pair), 1 = single CTAs
 static void env_overrides() {
     static bool done = false;
     if (done) return;
@@ -128,6 +128,7 @@ struct Workspace {
     int32_t *flags = nullptr;      // [0] centres that moved > tol, [1] empty clusters
     int64_t max_chunks = 0;
     CUtensorMap tm_x, tm_bhi, tm_blo;
+    CUtensorMap tm_bhi_half, tm_blo_half;  // boxes of bn/2 rows: each CTA of a pair loads half a centroid tile
     // pinned host mirror read once per iteration
     struct Host {
         int32_t flags[2];
@@ -451,6 +452,8 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(make_map(&w.tm_x, t->X, (uint64_t)t->rows, ld, kTileM));
     KM_TRY(make_map(&w.tm_bhi, w.bhi, (uint64_t)w.kpad, ld, (uint32_t)w.bn));
     KM_TRY(make_map(&w.tm_blo, w.blo, (uint64_t)w.kpad, ld, (uint32_t)w.bn));
+    KM_TRY(make_map(&w.tm_bhi_half, w.bhi, (uint64_t)w.kpad, ld, (uint32_t)std::max(w.bn / 2, 8)));
+    KM_TRY(make_map(&w.tm_blo_half, w.blo, (uint64_t)w.kpad, ld, (uint32_t)std::max(w.bn / 2, 8)));
     return 0;
 }
 
@@ -504,7 +507,7 @@ static int launch_assign_bn(kmb200_table *t) {
 template <int BN, int CL>
 static int launch_assign2_bn(kmb200_table *t) {
     Workspace &w = t->ws;
-    using Cfg = Assign2Cfg<BN>;
+    using Cfg = Assign2Cfg<BN, CL>;
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
     const int stages = Cfg::stages(kc);
@@ -545,7 +548,8 @@ static int launch_assign2_bn(kmb200_table *t) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    CU_TRY(cudaLaunchKernelEx(&cfg, assign_tc2_kernel<BN, CL>, w.tm_x, w.tm_bhi, w.tm_blo, p));
+    CU_TRY(cudaLaunchKernelEx(&cfg, assign_tc2_kernel<BN, CL>, w.tm_x, CL == 2 ? w.tm_bhi_half : w.tm_bhi,
+                              CL == 2 ? w.tm_blo_half : w.tm_blo, p));
     g_prof.kernel_launches++;
     return 0;
 }
@@ -553,7 +557,7 @@ static int launch_assign2_bn(kmb200_table *t) {
 template <int CL>
 static int launch_assign2(kmb200_table *t) {
     switch (t->ws.bn) {
-        case 16: return launch_assign2_bn<16, CL>(t);
+        case 16: return launch_assign2_bn<16, 1>(t);   // pair MMAs need N >= 32
         case 32: return launch_assign2_bn<32, CL>(t);
         case 64: return launch_assign2_bn<64, CL>(t);
         default: return launch_assign2_bn<128, CL>(t);

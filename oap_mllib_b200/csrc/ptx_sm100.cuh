@@ -111,6 +111,60 @@ __device__ __forceinline__ void tc_commit_mcast(uint64_t *bar, uint16_t cta_mask
         : "memory");
 }
 
+// ---------------------------------------------------------------- CTA pairs (cta_group::2)
+// One tcgen05.mma drives the tensor cores of both SMs of a TPC: M = 256 (128 rows per CTA, A and
+// D in each CTA's own TMEM at the same address), B split across the pair (each CTA's shared memory
+// holds N/2 rows at the same offset).  Issued by the leader CTA (cluster rank 0) only.
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t *smem_dst) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
+                 "n"(kCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+__device__ __forceinline__ void mma_tf32_ts_pair(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                                 uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// completion of this thread's earlier pair-MMAs -> arrive on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void tc_commit_pair(uint64_t *bar) {
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"((uint16_t)0x3)
+        : "memory");
+}
+// TMA load into THIS CTA's shared memory whose bytes are accounted on the LEADER CTA's mbarrier
+// (same offset; clearing bit 24 of the shared-window address selects rank 0 of the pair).
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap *m, uint64_t *bar, void *dst, int32_t c0,
+                                                 int32_t c1) {
+    const uint32_t leader_bar = smem_u32(bar) & 0xFEFFFFFFu;
+    const uint64_t evict_normal = 0x1000000000000000ull;
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+        "[%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar), "r"(c0), "r"(c1), "l"(evict_normal)
+        : "memory");
+}
+// arrive on the barrier at the same offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+        "r"(rank)
+        : "memory");
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
