@@ -82,13 +82,13 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
             mbar_init(&full[s], CL);       // leader's arrive.expect_tx (+ the peer's plain arrive)
             mbar_init(&empty[s], 1);
             mbar_init(&xfull[s], 1);
-            mbar_init(&xempty[s], 128);
+            mbar_init(&xempty[s], 4);          // one arrive per transform warp
         }
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&a_full[b], 128 * CL);
+            mbar_init(&a_full[b], 4 * CL);    // one arrive per transform warp of every CTA of the pair
             mbar_init(&a_empty[b], 1);
             mbar_init(&acc_full[b], 1);
-            mbar_init(&acc_empty[b], 128 * CL);
+            mbar_init(&acc_empty[b], 4 * CL); // one arrive per epilogue warp of every CTA of the pair
         }
         fence_mbar_init();
     }
@@ -256,7 +256,10 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                             hi[i] = __float_as_uint(h);
                             lo[i] = __float_as_uint(to_tf32_rna(x[i] - h));
                         }
-                        if (nt == NT - 1) mbar_arrive(&xempty[kc]);  // last read of this chunk: may be reloaded
+                        if (nt == NT - 1) {   // last read of this chunk: the X producer may reload it
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&xempty[kc]);
+                        }
                         if (!waited) {
                             mbar_wait(&a_empty[xb], aph ^ 1);
                             tc_fence_after();
@@ -270,8 +273,11 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                     }
                     tmem_wait_st();
                     tc_fence_before();
-                    if (leader) mbar_arrive(&a_full[xb]);
-                    else mbar_arrive_remote(&a_full[xb], 0);
+                    __syncwarp();          // one (possibly remote) arrive per warp: remote arrives are slow
+                    if (lane == 0) {
+                        if (leader) mbar_arrive(&a_full[xb]);
+                        else mbar_arrive_remote(&a_full[xb], 0);
+                    }
                 }
             }
             xph ^= 1;
@@ -317,8 +323,11 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                     }
                 }
                 tc_fence_before();
-                if (leader) mbar_arrive(&acc_empty[ab]);
-                else mbar_arrive_remote(&acc_empty[ab], 0);
+                __syncwarp();
+                if (lane == 0) {
+                    if (leader) mbar_arrive(&acc_empty[ab]);
+                    else mbar_arrive_remote(&acc_empty[ab], 0);
+                }
             }
             const int row = rt * kTileM + r;
             if (row < p.n && !(p.knockout & 4)) {
