@@ -9,8 +9,10 @@
 //     -- each CTA loads and holds only BN/2 of its rows -- so centroid bytes per SM, per L2 read
 //     and per shared-memory read are halved and twice as many stages fit.  Only the leader CTA
 //     issues MMAs; tcgen05.commit multicasts the completion to both CTAs' barriers;
-//   * the TMEM A operand is double-buffered at a granularity of TWO K-chunks (2 x 128 columns) and
-//     the MMA warp polls all barriers of a chunk pair together, so one handshake covers 24 MMAs.
+//   * the TMEM A operand has FOUR single-chunk buffers (4 x 64 columns), so the transform runs up to
+//     three chunks ahead of the MMAs (the commit -> transform -> arrive chain crosses CTAs in pair
+//     mode and is slow), and the MMA warp polls all barriers of a chunk pair together, so one
+//     handshake covers 24 MMAs.
 // Roles (per CTA): warp 0 B producer, warp 1 MMA issuer (leader CTA only), warp 2 TMEM allocator,
 // warp 3 X producer, warps 4-7 transform (thread r = row r), warps 8-11 epilogue (thread r = row r).
 #pragma once
@@ -23,10 +25,10 @@ struct Assign2Cfg {
     static constexpr int kBRows = BN / CL;                    // centroid rows held by one CTA
     static constexpr int kBChunkBytes = kBRows * kChunkK * 4; // one of B_hi / B_lo for one K chunk
     static constexpr int kBStageBytes = 2 * kBChunkBytes;     // hi + lo
-    static constexpr int kACols = 256;                        // 2 buffers x 2 chunks x (32 hi + 32 lo)
+    static constexpr int kACols = 256;                        // 4 buffers x (32 hi + 32 lo)
     static constexpr int kAccCol0 = kACols;
     static constexpr int kTmemCols = 512;
-    static constexpr int kTailBytes = 2 * BN * 4 + (4 * kMaxStages + 8) * 8 + 16;
+    static constexpr int kTailBytes = 2 * BN * 4 + (4 * kMaxStages + 12) * 8 + 16;
     static int stages(int kc) {
         int s = (227 * 1024 - 1024 - kTailBytes - kc * kXStageBytes) / kBStageBytes;
         return s > kMaxStages ? kMaxStages : s;
@@ -57,11 +59,11 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     uint64_t *empty = bars + kMaxStages;     // B stage consumed by the MMAs
     uint64_t *xfull = bars + 2 * kMaxStages; // X chunk landed
     uint64_t *xempty = bars + 3 * kMaxStages;// X chunk read for the last time by the transform
-    uint64_t *a_full = bars + 4 * kMaxStages;   // (leader) A chunk pair written by all CL*128 transform threads
-    uint64_t *a_empty = a_full + 2;
-    uint64_t *acc_full = a_full + 4;
-    uint64_t *acc_empty = a_full + 6;           // (leader) accumulator drained by all CL*128 epilogue threads
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 4 * kMaxStages + 8);
+    uint64_t *a_full = bars + 4 * kMaxStages;   // [4] (leader) A chunk written by every transform warp of the pair
+    uint64_t *a_empty = a_full + 4;             // [4] MMAs reading the A chunk have completed
+    uint64_t *acc_full = a_full + 8;            // [2]
+    uint64_t *acc_empty = a_full + 10;          // [2] (leader) accumulator drained by every epilogue warp of the pair
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 4 * kMaxStages + 12);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -84,9 +86,11 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
             mbar_init(&xfull[s], 1);
             mbar_init(&xempty[s], 4);          // one arrive per transform warp
         }
-        for (int b = 0; b < 2; ++b) {
+        for (int b = 0; b < 4; ++b) {
             mbar_init(&a_full[b], 4 * CL);    // one arrive per transform warp of every CTA of the pair
             mbar_init(&a_empty[b], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
             mbar_init(&acc_full[b], 1);
             mbar_init(&acc_empty[b], 4 * CL); // one arrive per epilogue warp of every CTA of the pair
         }
@@ -151,7 +155,7 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         // ================================ MMA issuer (leader CTA) ======================
         if (leader) {
             constexpr uint32_t idesc = make_idesc_tf32(kTileM * CL, BN);
-            uint32_t grp = 0, tile = 0, s = 0, ph = 0;
+            uint32_t grp = 0, ch = 0, tile = 0, s = 0, ph = 0;
             long long t_wait_acc = 0, t_wait = 0, t_issue = 0, t_mark = 0;
             const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
             for (int base = base0; base < p.num_row_tiles; base += gridDim.x) {
@@ -164,11 +168,12 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                     const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
                     for (int g = 0; g < G; ++g, ++grp) {
                         const int nch = (2 * g + 1 < KC) ? 2 : 1;
-                        const uint32_t xb = grp & 1, xph = (grp >> 1) & 1;
+                        const uint32_t b0 = ch & 3, bp0 = (ch >> 2) & 1;
+                        const uint32_t b1 = (ch + 1) & 3, bp1 = ((ch + 1) >> 2) & 1;
                         uint32_t s1 = s + 1, ph1 = ph;
                         if (s1 == (uint32_t)S) { s1 = 0; ph1 ^= 1; }
-                        if (nch == 2) mbar_wait3(&a_full[xb], xph, &full[s], ph, &full[s1], ph1);
-                        else mbar_wait2(&a_full[xb], xph, &full[s], ph);
+                        if (nch == 2) mbar_wait4(&a_full[b0], bp0, &a_full[b1], bp1, &full[s], ph, &full[s1], ph1);
+                        else mbar_wait2(&a_full[b0], bp0, &full[s], ph);
                         if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
                         tc_fence_after();
                         if (elect_one()) {
@@ -176,7 +181,8 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                             for (int c = 0; c < 2; ++c) {
                                 if (c < nch) {
                                     const uint32_t sc = c == 0 ? s : s1;
-                                    const uint32_t a_hi = tmem_base + xb * 128 + c * 64;
+                                    const uint32_t bb = c == 0 ? b0 : b1;
+                                    const uint32_t a_hi = tmem_base + bb * 64;
                                     const uint32_t a_lo = a_hi + 32;
                                     const uint32_t bsm = smem_u32(bs + sc * Cfg::kBStageBytes);
                                     const uint64_t dhi = make_kmajor_sw128_desc(bsm);
@@ -195,16 +201,18 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                                             mma_tf32_ts_pair(d_tmem, a_hi + ks * 8, dhi + koff, idesc, 1u);
                                         }
                                     }
-                                    if (CL == 1) tc_commit(&empty[sc]);
-                                    else tc_commit_pair(&empty[sc]);   // both CTAs' producers may refill
+                                    if (CL == 1) {
+                                        tc_commit(&empty[sc]);
+                                        tc_commit(&a_empty[bb]);
+                                    } else {          // both CTAs' producers / transforms may proceed
+                                        tc_commit_pair(&empty[sc]);
+                                        tc_commit_pair(&a_empty[bb]);
+                                    }
                                 }
                             }
-                            if (CL == 1) {
-                                tc_commit(&a_empty[xb]);
-                                if (g == G - 1) tc_commit(&acc_full[ab]);
-                            } else {
-                                tc_commit_pair(&a_empty[xb]);
-                                if (g == G - 1) tc_commit_pair(&acc_full[ab]);
+                            if (g == G - 1) {
+                                if (CL == 1) tc_commit(&acc_full[ab]);
+                                else tc_commit_pair(&acc_full[ab]);
                             }
                         }
                         __syncwarp();
@@ -212,6 +220,7 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                         s = nch == 2 ? s1 + 1 : s1;
                         ph = ph1;
                         if (nch == 2 && s == (uint32_t)S) { s = 0; ph ^= 1; }
+                        ch += nch;
                     }
                 }
             }
@@ -227,60 +236,63 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         // ================================ transform ===================================
         const int r = threadIdx.x - 128;
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
-        uint32_t grp = 0, xph = 0;
+        uint32_t ch = 0, xph = 0;
+        long long t_load = 0, t_wait_a = 0, t_store = 0, t_mark = 0;
+        const bool prof = p.role_prof != nullptr && blockIdx.x < 2 && warp == 4;
         for (int base = base0; base < p.num_row_tiles; base += gridDim.x) {
             for (int nt = 0; nt < NT; ++nt) {
-                for (int g = 0; g < G; ++g, ++grp) {
-                    const int nch = (2 * g + 1 < KC) ? 2 : 1;
-                    const uint32_t xb = grp & 1, aph = (grp >> 1) & 1;
-                    bool waited = false;
+                for (int kc = 0; kc < KC; ++kc, ++ch) {
+                    const uint32_t bb = ch & 3, bph = (ch >> 2) & 1;
+                    if (prof) t_mark = clock64();
+                    if (nt == 0) mbar_wait(&xfull[kc], xph);   // X chunk of this row tile has landed
+                    const uint8_t *xrow = xs + kc * kXStageBytes + r * 128;
+                    float x[32];
 #pragma unroll
-                    for (int c = 0; c < 2; ++c) {
-                        if (c >= nch) break;
-                        const int kc = 2 * g + c;
-                        if (nt == 0) mbar_wait(&xfull[kc], xph);   // X chunk of this row tile has landed
-                        const uint8_t *xrow = xs + kc * kXStageBytes + r * 128;
-                        float x[32];
+                    for (int q = 0; q < 8; ++q) {
+                        const float4 v = *reinterpret_cast<const float4 *>(xrow + ((q ^ (r & 7)) << 4));
+                        x[4 * q + 0] = v.x;
+                        x[4 * q + 1] = v.y;
+                        x[4 * q + 2] = v.z;
+                        x[4 * q + 3] = v.w;
+                    }
+                    uint32_t hi[32], lo[32];
 #pragma unroll
-                        for (int q = 0; q < 8; ++q) {
-                            const float4 v = *reinterpret_cast<const float4 *>(xrow + ((q ^ (r & 7)) << 4));
-                            x[4 * q + 0] = v.x;
-                            x[4 * q + 1] = v.y;
-                            x[4 * q + 2] = v.z;
-                            x[4 * q + 3] = v.w;
-                        }
-                        uint32_t hi[32], lo[32];
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            const float h = to_tf32_rna(x[i]);
-                            hi[i] = __float_as_uint(h);
-                            lo[i] = __float_as_uint(to_tf32_rna(x[i] - h));
-                        }
-                        if (nt == NT - 1) {   // last read of this chunk: the X producer may reload it
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(&xempty[kc]);
-                        }
-                        if (!waited) {
-                            mbar_wait(&a_empty[xb], aph ^ 1);
-                            tc_fence_after();
-                            waited = true;
-                        }
-                        if (!(p.knockout & 2)) {
-                            const uint32_t a_addr = tmem_base + lane_addr + xb * 128 + c * 64;
-                            tmem_st32(a_addr, hi);
-                            tmem_st32(a_addr + 32, lo);
-                        }
+                    for (int i = 0; i < 32; ++i) {
+                        const float h = to_tf32_rna(x[i]);
+                        hi[i] = __float_as_uint(h);
+                        lo[i] = __float_as_uint(to_tf32_rna(x[i] - h));
+                    }
+                    if (nt == NT - 1) {   // last read of this chunk: the X producer may reload it
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&xempty[kc]);
+                    }
+                    if (prof) { const long long t = clock64(); t_load += t - t_mark; t_mark = t; }
+                    mbar_wait(&a_empty[bb], bph ^ 1);   // MMAs that read this A buffer have completed
+                    if (prof) { const long long t = clock64(); t_wait_a += t - t_mark; t_mark = t; }
+                    tc_fence_after();
+                    if (!(p.knockout & 2)) {
+                        const uint32_t a_addr = tmem_base + lane_addr + bb * 64;
+                        tmem_st32(a_addr, hi);
+                        tmem_st32(a_addr + 32, lo);
                     }
                     tmem_wait_st();
                     tc_fence_before();
-                    __syncwarp();          // one (possibly remote) arrive per warp: remote arrives are slow
+                    __syncwarp();          // one (possibly remote) arrive per warp
                     if (lane == 0) {
-                        if (leader) mbar_arrive(&a_full[xb]);
-                        else mbar_arrive_remote(&a_full[xb], 0);
+                        if (leader) mbar_arrive(&a_full[bb]);
+                        else mbar_arrive_remote(&a_full[bb], 0);
                     }
+                    if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
                 }
             }
             xph ^= 1;
+        }
+        if (prof && lane == 0) {
+            long long *o = p.role_prof + 5 + 4 * blockIdx.x;
+            o[0] = t_load;
+            o[1] = t_wait_a;
+            o[2] = t_store;
+            o[3] = ch;
         }
     } else if (warp >= 8) {
         // ================================ epilogue ====================================

@@ -1040,8 +1040,13 @@ extern "C" int kmb200_set_option(const char *name, double value) {
             long long h[16];
             CU_TRY(cudaDeviceSynchronize());
             CU_TRY(cudaMemcpy(h, g_role_prof, sizeof(h), cudaMemcpyDeviceToHost));
-            fprintf(stderr, "[kmb200 role_prof] last assign launch, CTA 0 MMA warp: chunks=%lld cycles/chunk: wait_acc=%.1f wait_full=%.1f wait_a=%.1f issue=%.1f\n",
+            fprintf(stderr, "[kmb200 role_prof] last assign launch, CTA 0 MMA warp: units=%lld cycles/unit: wait_acc=%.1f wait_full=%.1f wait_a=%.1f issue=%.1f\n",
                     h[4], (double)h[0] / h[4], (double)h[1] / h[4], (double)h[2] / h[4], (double)h[3] / h[4]);
+            for (int c = 0; c < 2; ++c)
+                if (h[5 + 4 * c + 3] > 0)
+                    fprintf(stderr, "[kmb200 role_prof] CTA %d transform warp: chunks=%lld cycles/chunk: load+split=%.1f wait_a_empty=%.1f store+arrive=%.1f\n",
+                            c, h[8 + 4 * c], (double)h[5 + 4 * c] / h[8 + 4 * c], (double)h[6 + 4 * c] / h[8 + 4 * c],
+                            (double)h[7 + 4 * c] / h[8 + 4 * c]);
             cudaFree(g_role_prof);
             g_role_prof = nullptr;
         }

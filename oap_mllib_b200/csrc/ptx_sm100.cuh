@@ -82,6 +82,27 @@ __device__ __forceinline__ void mbar_wait3(uint64_t *bar_a, uint32_t par_a, uint
     } while (!ok);
 }
 
+__device__ __forceinline__ void mbar_wait4(uint64_t *bar_a, uint32_t par_a, uint64_t *bar_b, uint32_t par_b,
+                                           uint64_t *bar_c, uint32_t par_c, uint64_t *bar_d, uint32_t par_d) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p, q, r, s;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 q, [%3], %4;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 r, [%5], %6;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 s, [%7], %8;\n\t"
+            "and.pred p, p, q;\n\t"
+            "and.pred r, r, s;\n\t"
+            "and.pred p, p, r;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar_a)), "r"(par_a), "r"(smem_u32(bar_b)), "r"(par_b), "r"(smem_u32(bar_c)), "r"(par_c),
+              "r"(smem_u32(bar_d)), "r"(par_d)
+            : "memory");
+    } while (!ok);
+}
+
 // ---------------------------------------------------------------- clusters
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
