@@ -81,18 +81,20 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kMaxStages; ++s) {
-            mbar_init(&full[s], CL);       // leader's arrive.expect_tx (+ the peer's plain arrive)
+            mbar_init(&full[s], 1);        // the (leader's) arrive.expect_tx; both CTAs' bytes are counted on it
             mbar_init(&empty[s], 1);
             mbar_init(&xfull[s], 1);
             mbar_init(&xempty[s], 4);          // one arrive per transform warp
         }
+        // leader: 4 local warps (+ 1 relayed arrive standing for the peer's 4 warps); peer: 4 local warps
+        const uint32_t group_count = (CL > 1 && leader) ? 5 : 4;
         for (int b = 0; b < 4; ++b) {
-            mbar_init(&a_full[b], 4 * CL);    // one arrive per transform warp of every CTA of the pair
+            mbar_init(&a_full[b], group_count);
             mbar_init(&a_empty[b], 1);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&acc_full[b], 1);
-            mbar_init(&acc_empty[b], 4 * CL); // one arrive per epilogue warp of every CTA of the pair
+            mbar_init(&acc_empty[b], group_count);
         }
         fence_mbar_init();
     }
@@ -119,7 +121,6 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                         const int brow = nt * BN + (int)rank * Cfg::kBRows;
                         if (p.knockout & 1) {
                             if (leader) mbar_arrive(&full[s]);
-                            else mbar_arrive_remote(&full[s], 0);
                         } else if (CL == 1) {
                             mbar_arrive_expect_tx(&full[s], Cfg::kBStageBytes);
                             tma_load_2d(&tm_bhi, &full[s], st, kc * kChunkK, brow);
@@ -129,7 +130,8 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                             if (leader) mbar_arrive_expect_tx(&full[s], 2 * Cfg::kBStageBytes);
                             tma_load_2d_pair(&tm_bhi, &full[s], st, kc * kChunkK, brow);
                             tma_load_2d_pair(&tm_blo, &full[s], st + Cfg::kBChunkBytes, kc * kChunkK, brow);
-                            if (!leader) mbar_arrive_remote(&full[s], 0);
+                            // the peer cannot run ahead of the ring (its empty[] comes from the leader's
+                            // MMAs), so its bytes always land in the phase the leader is arming
                         }
                     }
                     __syncwarp();
@@ -231,7 +233,27 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                 p.role_prof[3] = t_issue;
                 p.role_prof[4] = grp;
             }
+        } else {
+            // ---- peer CTA: relay "A chunk written" to the leader.  A remote mbarrier arrive costs
+            // several hundred cycles; doing it here keeps that latency off the transform warps.
+            uint32_t ch = 0;
+            for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
+                for (int nt = 0; nt < NT; ++nt)
+                    for (int kc = 0; kc < KC; ++kc, ++ch) {
+                        mbar_wait(&a_full[ch & 3], (ch >> 2) & 1);
+                        if (lane == 0) mbar_arrive_remote(&a_full[ch & 3], 0);
+                        __syncwarp();
+                    }
         }
+    } else if (warp == 2 && CL > 1 && !leader) {
+        // ---- peer CTA: relay "accumulator drained" to the leader
+        uint32_t tile = 0;
+        for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
+            for (int nt = 0; nt < NT; ++nt, ++tile) {
+                mbar_wait(&acc_empty[tile & 1], (tile >> 1) & 1);
+                if (lane == 0) mbar_arrive_remote(&acc_empty[tile & 1], 0);
+                __syncwarp();
+            }
     } else if (warp >= 4 && warp < 8) {
         // ================================ transform ===================================
         const int r = threadIdx.x - 128;
@@ -256,11 +278,16 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                         x[4 * q + 3] = v.w;
                     }
                     uint32_t hi[32], lo[32];
+                    // Veltkamp split with 2^13 + 1: hi = x rounded to 11 significant bits (exactly a TF32
+                    // value), lo = x - hi exactly; the tensor core drops lo's low 13 bits (|error| <=
+                    // 2^-21 |x|).  All four operations run on the FMA pipe, leaving the ALU pipe (min /
+                    // max / select) to the epilogue warps that share these schedulers.
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
-                        const float h = to_tf32_rna(x[i]);
+                        const float t = __fmul_rn(x[i], 8193.0f);
+                        const float h = __fsub_rn(t, __fsub_rn(t, x[i]));
                         hi[i] = __float_as_uint(h);
-                        lo[i] = __float_as_uint(to_tf32_rna(x[i] - h));
+                        lo[i] = __float_as_uint(__fsub_rn(x[i], h));
                     }
                     if (nt == NT - 1) {   // last read of this chunk: the X producer may reload it
                         __syncwarp();
@@ -278,10 +305,7 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                     tmem_wait_st();
                     tc_fence_before();
                     __syncwarp();          // one (possibly remote) arrive per warp
-                    if (lane == 0) {
-                        if (leader) mbar_arrive(&a_full[bb]);
-                        else mbar_arrive_remote(&a_full[bb], 0);
-                    }
+                    if (lane == 0) mbar_arrive(&a_full[bb]);   // local; the peer's relay warp forwards it
                     if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
                 }
             }
@@ -336,10 +360,7 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) {
-                    if (leader) mbar_arrive(&acc_empty[ab]);
-                    else mbar_arrive_remote(&acc_empty[ab], 0);
-                }
+                if (lane == 0) mbar_arrive(&acc_empty[ab]);    // local; the peer's relay warp forwards it
             }
             const int row = rt * kTileM + r;
             if (row < p.n && !(p.knockout & 4)) {
