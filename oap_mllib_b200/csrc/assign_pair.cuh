@@ -1,0 +1,380 @@
+// CTA-pair assign kernel (ld <= 256, BN >= 32): the production path on B200 for the headline shape.
+// Same arithmetic as assign_tc_kernel (3xTF32, FP32 accumulators in TMEM, top-3 epilogue, first
+// minimum wins).  Structure:
+//   * clusters of two CTAs on one TPC; MMAs are tcgen05.mma.cta_group::2 with M = 256: each CTA owns
+//     128 rows (its X tile resident in shared memory, its A operand and accumulators in its own TMEM),
+//     every centroid tile is SPLIT across the pair (each CTA loads BN/2 rows), so centroid bytes per
+//     SM / per L2 read / per shared-memory read are half those of a single-CTA kernel;
+//   * work is synchronised per GROUP of two K-chunks (24 MMAs): the leader's MMA warp polls the A
+//     slot and both B stages of a group together and signals completion with ONE multicast
+//     tcgen05.commit per group (gdone ring) -- cross-CTA commits and arrives cost hundreds of cycles,
+//     so there is exactly one of each per group on the critical path;
+//   * the peer CTA's transform / epilogue warps arrive on LOCAL barriers; two otherwise idle warps of
+//     the peer relay those to the leader (remote mbarrier arrives), keeping that latency off the
+//     warps that do arithmetic.
+// Roles per CTA: warp 0 B producer, warp 1 MMA issuer (leader) / A relay (peer), warp 2 TMEM
+// allocator, then accumulator relay (peer), warp 3 X producer, warps 4-7 transform (thread r = row r),
+// warps 8-11 epilogue (thread r = row r).
+#pragma once
+#include "assign_tc.cuh"
+
+namespace kmb {
+
+template <int BN>
+struct PairCfg {
+    static constexpr int kBRows = BN / 2;                     // centroid rows held by one CTA
+    static constexpr int kBChunkBytes = kBRows * kChunkK * 4; // one of B_hi / B_lo for one K chunk
+    static constexpr int kBStageBytes = 2 * kBChunkBytes;     // hi + lo
+    static constexpr int kAccCol0 = 256;                      // A: 2 group slots x 2 chunks x (32 hi + 32 lo)
+    static constexpr int kTmemCols = 512;
+    static constexpr int kNumBars = 8 /*full*/ + 8 /*gdone*/ + 8 /*xfull*/ + 8 /*xempty*/ + 2 + 2 + 2;
+    static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16;
+    // B ring: RB group slots of two stages each (RB <= 4)
+    static int group_slots(int kc) {
+        int s = (227 * 1024 - 1024 - kTailBytes - kc * kXStageBytes) / (2 * kBStageBytes);
+        return s > 4 ? 4 : s;
+    }
+    static int smem_bytes(int kc, int rb) { return 1024 + kc * kXStageBytes + rb * 2 * kBStageBytes + kTailBytes; }
+};
+
+// tm_bhi / tm_blo: boxes of BN/2 rows.  p.stages = RB (group slots of the B ring).
+template <int BN>
+__global__ void __launch_bounds__(kAssignThreads, 1)
+assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_bhi,
+                   const __grid_constant__ CUtensorMap tm_blo, const AssignParams p) {
+    using Cfg = PairCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+
+    const int RB = p.stages;             // 2..4 group slots in the B ring
+    const int P = (RB == 3) ? 6 : RB == 4 ? 4 : 2;   // lcm(2, RB): period of the gdone ring
+    const int NT = p.num_col_tiles;
+    const int KC = p.num_k_chunks;       // <= 8
+    const int G = (KC + 1) >> 1;         // groups (chunk pairs) per centroid tile
+    uint8_t *xs = smem;                                  // [KC][128 rows x 128 B], swizzled
+    uint8_t *bs = smem + KC * kXStageBytes;              // [RB][2][B_hi chunk | B_lo chunk] (this CTA's rows)
+    uint8_t *tail = bs + RB * 2 * Cfg::kBStageBytes;
+    float *cn_s = reinterpret_cast<float *>(tail);       // [2][BN]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(tail + 2 * BN * 4);
+    uint64_t *full = bars;            // [8]  (leader) B stage landed in BOTH CTAs
+    uint64_t *gdone = bars + 8;       // [8]  all MMAs of a group completed (multicast commit): its B stages
+                                      //      and its A slot may be overwritten
+    uint64_t *xfull = bars + 16;      // [8]  X chunk landed
+    uint64_t *xempty = bars + 24;     // [8]  X chunk read for the last time by the transform
+    uint64_t *a_full = bars + 32;     // [2]  A slot written (4 local warps; leader: + 1 relayed arrive)
+    uint64_t *acc_full = bars + 34;   // [2]  accumulator tile complete (multicast commit)
+    uint64_t *acc_empty = bars + 36;  // [2]  accumulator drained (4 local warps; leader: + 1 relayed arrive)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    // row tiles are dealt to pairs; both CTAs always run the same number of tiles (a tile index beyond
+    // the table is a dummy: TMA zero-fills it and nothing is stored)
+    const int tile0 = blockIdx.x;
+    const int base0 = tile0 - (int)rank;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_x);
+        tma_prefetch_desc(&tm_bhi);
+        tma_prefetch_desc(&tm_blo);
+    }
+    if (warp == 1 && lane == 0) {
+        const uint32_t group_count = leader ? 5 : 4;
+        for (int s = 0; s < 8; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&gdone[s], 1);
+            mbar_init(&xfull[s], 1);
+            mbar_init(&xempty[s], 4);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&a_full[b], group_count);
+            mbar_init(&acc_full[b], 1);
+            mbar_init(&acc_empty[b], group_count);
+        }
+        fence_mbar_init();
+    }
+    cluster_sync_all();
+    if (warp == 2) tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();               // the peer's barriers and TMEM exist before anything touches them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // "group g - D has completed" on the gdone ring (D = 2 for the A slot, RB for the B slot)
+    auto wait_group_done = [&](uint32_t g, uint32_t D) {
+        if (g >= D) {
+            const uint32_t q = g - D;
+            mbar_wait(&gdone[q % P], (q / P) & 1);
+        }
+    };
+
+    if (warp == 0) {
+        // ================================ B producer ==================================
+        uint32_t grp = 0;
+        for (int base = base0; base < p.num_row_tiles; base += gridDim.x) {
+            for (int nt = 0; nt < NT; ++nt) {
+                for (int g = 0; g < G; ++g, ++grp) {
+                    const int nch = (2 * g + 1 < KC) ? 2 : 1;
+                    const uint32_t slot = grp % RB;
+                    wait_group_done(grp, RB);
+                    if (elect_one()) {
+                        const int brow = nt * BN + (int)rank * Cfg::kBRows;
+                        for (int c = 0; c < 2; ++c) {
+                            const uint32_t s = slot * 2 + c;
+                            uint8_t *st = bs + s * Cfg::kBStageBytes;
+                            const int kc = 2 * g + c;
+                            if (c >= nch || (p.knockout & 1)) {
+                                // an odd chunk count leaves the group's second stage unused: keep its
+                                // barrier phase in step with the slot
+                                if (leader) mbar_arrive(&full[s]);
+                            } else {
+                                // both CTAs' bytes are accounted on the leader's barrier; the peer cannot
+                                // run ahead of the ring (gdone comes from the leader's MMAs), so its bytes
+                                // always land in the phase the leader is arming
+                                if (leader) mbar_arrive_expect_tx(&full[s], 2 * Cfg::kBStageBytes);
+                                tma_load_2d_pair(&tm_bhi, &full[s], st, kc * kChunkK, brow);
+                                tma_load_2d_pair(&tm_blo, &full[s], st + Cfg::kBChunkBytes, kc * kChunkK, brow);
+                            }
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else if (warp == 3) {
+        // ================================ X producer ==================================
+        uint32_t xph = 0;
+        for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x) {
+            for (int kc = 0; kc < KC; ++kc) {
+                mbar_wait(&xempty[kc], xph ^ 1);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(&xfull[kc], kXStageBytes);
+                    tma_load_2d(&tm_x, &xfull[kc], xs + kc * kXStageBytes, kc * kChunkK, rt * kTileM);
+                }
+                __syncwarp();
+            }
+            xph ^= 1;
+        }
+    } else if (warp == 1) {
+        if (leader) {
+            // ================================ MMA issuer ==============================
+            constexpr uint32_t idesc = make_idesc_tf32(2 * kTileM, BN);
+            uint32_t grp = 0, tile = 0;
+            long long t_wait_acc = 0, t_wait = 0, t_issue = 0, t_mark = 0;
+            const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
+            for (int base = base0; base < p.num_row_tiles; base += gridDim.x) {
+                for (int nt = 0; nt < NT; ++nt, ++tile) {
+                    const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
+                    if (prof) t_mark = clock64();
+                    mbar_wait(&acc_empty[ab], aph ^ 1);
+                    if (prof) { const long long t = clock64(); t_wait_acc += t - t_mark; t_mark = t; }
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
+                    for (int g = 0; g < G; ++g, ++grp) {
+                        const int nch = (2 * g + 1 < KC) ? 2 : 1;
+                        const uint32_t aslot = grp & 1, aph2 = (grp >> 1) & 1;
+                        const uint32_t bslot = grp % RB, bph = (grp / RB) & 1;
+                        const uint32_t s0 = bslot * 2, s1 = s0 + 1;
+                        mbar_wait3(&a_full[aslot], aph2, &full[s0], bph, &full[s1], bph);
+                        if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
+                        tc_fence_after();
+                        if (elect_one()) {
+#pragma unroll
+                            for (int c = 0; c < 2; ++c) {
+                                if (c < nch) {
+                                    const uint32_t a_hi = tmem_base + aslot * 128 + c * 64;
+                                    const uint32_t a_lo = a_hi + 32;
+                                    const uint32_t bsm = smem_u32(bs + (s0 + c) * Cfg::kBStageBytes);
+                                    const uint64_t dhi = make_kmajor_sw128_desc(bsm);
+                                    const uint64_t dlo = make_kmajor_sw128_desc(bsm + Cfg::kBChunkBytes);
+#pragma unroll
+                                    for (int ks = 0; ks < kChunkK / 8; ++ks) {
+                                        const uint64_t koff = static_cast<uint64_t>(ks * 2);
+                                        const uint32_t first = (g | c | ks) == 0 ? 0u : 1u;
+                                        mma_tf32_ts_pair(d_tmem, a_lo + ks * 8, dhi + koff, idesc, first);  // small terms first
+                                        mma_tf32_ts_pair(d_tmem, a_hi + ks * 8, dlo + koff, idesc, 1u);
+                                        mma_tf32_ts_pair(d_tmem, a_hi + ks * 8, dhi + koff, idesc, 1u);
+                                    }
+                                }
+                            }
+                            tc_commit_pair(&gdone[grp % P]);                 // ONE cross-CTA signal per group
+                            if (g == G - 1) tc_commit_pair(&acc_full[ab]);
+                        }
+                        __syncwarp();
+                        if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
+                    }
+                }
+            }
+            if (prof && lane == 0) {
+                p.role_prof[0] = t_wait_acc;
+                p.role_prof[1] = t_wait;
+                p.role_prof[2] = 0;
+                p.role_prof[3] = t_issue;
+                p.role_prof[4] = grp;
+            }
+        } else {
+            // ---- peer CTA: relay "A slot written" to the leader
+            uint32_t grp = 0;
+            for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
+                for (int nt = 0; nt < NT; ++nt)
+                    for (int g = 0; g < G; ++g, ++grp) {
+                        mbar_wait(&a_full[grp & 1], (grp >> 1) & 1);
+                        if (lane == 0) mbar_arrive_remote(&a_full[grp & 1], 0);
+                        __syncwarp();
+                    }
+        }
+    } else if (warp == 2) {
+        if (!leader) {
+            // ---- peer CTA: relay "accumulator drained" to the leader
+            uint32_t tile = 0;
+            for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
+                for (int nt = 0; nt < NT; ++nt, ++tile) {
+                    mbar_wait(&acc_empty[tile & 1], (tile >> 1) & 1);
+                    if (lane == 0) mbar_arrive_remote(&acc_empty[tile & 1], 0);
+                    __syncwarp();
+                }
+        }
+    } else if (warp >= 4 && warp < 8) {
+        // ================================ transform ===================================
+        const int r = threadIdx.x - 128;
+        const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        uint32_t grp = 0, xph = 0;
+        long long t_load = 0, t_wait_a = 0, t_store = 0, t_mark = 0;
+        const bool prof = p.role_prof != nullptr && blockIdx.x < 2 && warp == 4;
+        for (int base = base0; base < p.num_row_tiles; base += gridDim.x) {
+            for (int nt = 0; nt < NT; ++nt) {
+                for (int g = 0; g < G; ++g, ++grp) {
+                    const int nch = (2 * g + 1 < KC) ? 2 : 1;
+                    const uint32_t aslot = grp & 1;
+                    bool waited = false;
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        if (c >= nch) break;
+                        const int kc = 2 * g + c;
+                        if (prof) t_mark = clock64();
+                        if (nt == 0) mbar_wait(&xfull[kc], xph);   // X chunk of this row tile has landed
+                        const uint8_t *xrow = xs + kc * kXStageBytes + r * 128;
+                        float x[32];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float4 v = *reinterpret_cast<const float4 *>(xrow + ((q ^ (r & 7)) << 4));
+                            x[4 * q + 0] = v.x;
+                            x[4 * q + 1] = v.y;
+                            x[4 * q + 2] = v.z;
+                            x[4 * q + 3] = v.w;
+                        }
+                        uint32_t hi[32], lo[32];
+                        // Veltkamp split with 2^13 + 1: hi = x rounded to 11 significant bits (exactly a
+                        // TF32 value), lo = x - hi exactly; the tensor core drops lo's low 13 bits (|error|
+                        // <= 2^-21 |x|).  All on the FMA pipe: the ALU pipe (min / max / select) belongs to
+                        // the epilogue warps that share these schedulers.
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const float t = __fmul_rn(x[i], 8193.0f);
+                            const float h = __fsub_rn(t, __fsub_rn(t, x[i]));
+                            hi[i] = __float_as_uint(h);
+                            lo[i] = __float_as_uint(__fsub_rn(x[i], h));
+                        }
+                        if (nt == NT - 1) {   // last read of this chunk: the X producer may reload it
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&xempty[kc]);
+                        }
+                        if (prof) { const long long t = clock64(); t_load += t - t_mark; t_mark = t; }
+                        if (!waited) {
+                            wait_group_done(grp, 2);   // MMAs that read this A slot have completed
+                            tc_fence_after();
+                            waited = true;
+                        }
+                        if (prof) { const long long t = clock64(); t_wait_a += t - t_mark; t_mark = t; }
+                        if (!(p.knockout & 2)) {
+                            const uint32_t a_addr = tmem_base + lane_addr + aslot * 128 + c * 64;
+                            tmem_st32(a_addr, hi);
+                            tmem_st32(a_addr + 32, lo);
+                        }
+                        if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
+                    }
+                    if (prof) t_mark = clock64();
+                    tmem_wait_st();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&a_full[aslot]);   // local; the peer's relay warp forwards it
+                    if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
+                }
+            }
+            xph ^= 1;
+        }
+        if (prof && lane == 0) {
+            long long *o = p.role_prof + 5 + 4 * blockIdx.x;
+            o[0] = t_load;
+            o[1] = t_wait_a;
+            o[2] = t_store;
+            o[3] = grp;
+        }
+    } else if (warp >= 8) {
+        // ================================ epilogue ====================================
+        const int r = threadIdx.x - 256;
+        const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        const float cmax = p.cstats[0];
+        uint32_t tile = 0;
+        for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x) {
+            float best = __int_as_float(0x7f800000), second = best, third = best;
+            int bidx = 0, sidx = 0;
+            for (int nt = 0; nt < NT; ++nt, ++tile) {
+                const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
+                float *cn = cn_s + ab * BN;
+                if (r < BN) cn[r] = p.cnorm[nt * BN + r];
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                mbar_wait(&acc_full[ab], aph);
+                tc_fence_after();
+                if (!(p.knockout & 4)) {
+                    const uint32_t acc = tmem_base + lane_addr + Cfg::kAccCol0 + ab * BN;
+#pragma unroll 1
+                    for (int c0 = 0; c0 < BN; c0 += 32) {
+                        uint32_t v[32];
+                        tmem_ld32(acc + c0, v);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const float sc = __uint_as_float(v[i]) + cn[c0 + i];
+                            if (p.dbg_scores != nullptr && rt * kTileM + r < p.n)
+                                p.dbg_scores[(size_t)(rt * kTileM + r) * p.kpad + nt * BN + c0 + i] = sc;
+                            // running top-3 values with the indices of the best two; strict '<' keeps
+                            // the lowest index among equal scores
+                            const int j = nt * BN + c0 + i;
+                            const bool lt1 = sc < best, lt2 = sc < second;
+                            third = fminf(third, fmaxf(sc, second));
+                            sidx = lt1 ? bidx : (lt2 ? j : sidx);
+                            second = fminf(second, fmaxf(sc, best));
+                            bidx = lt1 ? j : bidx;
+                            best = fminf(best, sc);
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_empty[ab]);    // local; the peer's relay warp forwards it
+            }
+            const int row = rt * kTileM + r;
+            if (row < p.n && !(p.knockout & 4)) {
+                p.labels[row] = bidx;
+                const float xn = sqrtf(p.xnorm[row]);
+                const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
+                if (second - best <= bound) {
+                    const int pos = atomicAdd(p.flag_count, 1);
+                    if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, (third - best <= bound) ? -1 : sidx);
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();               // no CTA leaves while its peer can still arrive on its barriers
+    if (warp == 2) tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+}
+
+}  // namespace kmb

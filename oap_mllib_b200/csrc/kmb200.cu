@@ -19,6 +19,7 @@
 #include "../../include/kmb200.h"
 #include "assign_tc.cuh"
 #include "assign_tc2.cuh"
+#include "assign_pair.cuh"
 #include "kernels_misc.cuh"
 
 using namespace kmb;
@@ -554,6 +555,66 @@ static int launch_assign2_bn(kmb200_table *t) {
     return 0;
 }
 
+template <int BN>
+static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
+    Workspace &w = t->ws;
+    using Cfg = PairCfg<BN>;
+    static bool attr_set[64] = {false};
+    const int kc = t->ld / kChunkK;
+    const int rb = Cfg::group_slots(kc);
+    *applicable = rb >= 2;
+    if (rb < 2) return 0;
+    const int smem = Cfg::smem_bytes(kc, rb);
+    if (!attr_set[t->device & 63]) {
+        CU_TRY(cudaFuncSetAttribute(assign_pair_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set[t->device & 63] = true;
+    }
+    AssignParams p;
+    p.cnorm = w.cnorm;
+    p.xnorm = t->xnorm;
+    p.cstats = w.cstats;
+    p.labels = w.labels;
+    p.flag_count = w.flag_count;
+    p.flag_list = w.flag_list;
+    p.flag_cap = (int32_t)t->rows;
+    p.n = (int32_t)t->rows;
+    p.num_row_tiles = (int32_t)((t->rows + kTileM - 1) / kTileM);
+    p.num_col_tiles = w.kpad / BN;
+    p.num_k_chunks = kc;
+    p.stages = rb;
+    p.passes = 3;
+    p.eps = score_eps(t->ld);
+    p.dbg_scores = g_dbg_scores;
+    p.kpad = w.kpad;
+    p.knockout = g_knockout;
+    p.role_prof = g_role_prof;
+    const int pairs = std::min((p.num_row_tiles + 1) / 2, t->num_sms / 2);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(pairs * 2));
+    cfg.blockDim = dim3(kAssignThreads);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = t->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CU_TRY(cudaLaunchKernelEx(&cfg, assign_pair_kernel<BN>, w.tm_x, w.tm_bhi_half, w.tm_blo_half, p));
+    g_prof.kernel_launches++;
+    return 0;
+}
+
+static int launch_assign_pair(kmb200_table *t, bool *applicable) {
+    switch (t->ws.bn) {
+        case 32: return launch_assign_pair_bn<32>(t, applicable);
+        case 64: return launch_assign_pair_bn<64>(t, applicable);
+        case 128: return launch_assign_pair_bn<128>(t, applicable);
+        default: *applicable = false; return 0;   // pair MMAs need N >= 32
+    }
+}
+
 template <int CL>
 static int launch_assign2(kmb200_table *t) {
     switch (t->ws.bn) {
@@ -586,7 +647,14 @@ static int launch_assign(kmb200_table *t) {
     env_overrides();
     if (g_kernel == 2 && g_passes == 3 && t->ld <= 256) {
         const int row_tiles = (int)((t->rows + kTileM - 1) / kTileM);
-        return (g_cluster == 2 && row_tiles >= 2) ? launch_assign2<2>(t) : launch_assign2<1>(t);
+        if (g_cluster == 2 && row_tiles >= 2) {
+            bool applicable = false;
+            const int rc = launch_assign_pair(t, &applicable);
+            if (rc != 0 || applicable) return rc;
+        } else if (g_cluster == 3 && row_tiles >= 2) {
+            return launch_assign2<2>(t);   // earlier pair variant with per-chunk commits (experiments)
+        }
+        return launch_assign2<1>(t);
     }
     switch (w.bn) {
         case 16: return launch_assign_bn<16>(t);
@@ -1055,7 +1123,7 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         env_overrides();
         g_kernel = (int)value;
     } else if (!strcmp(name, "cluster")) {
-        if (value != 1 && value != 2) return fail(KMB200_ERR_ARG, "cluster must be 1 or 2");
+        if (value != 1 && value != 2 && value != 3) return fail(KMB200_ERR_ARG, "cluster must be 1, 2 or 3");
         env_overrides();
         g_cluster = (int)value;
     } else if (!strcmp(name, "knockout")) {

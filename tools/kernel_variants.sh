@@ -1,7 +1,9 @@
 #!/bin/bash
 # assign-kernel variants timed on the same workload (C3 shape, ROWS rows)
 ROWS=${ROWS:-20000000}
-for v in "kernel=1" "kernel=2 cluster=1" "kernel=2 cluster=2"; do
+VARIANTS=${VARIANTS:-"kernel=1|kernel=2 cluster=1|kernel=2 cluster=3|kernel=2 cluster=2"}
+IFS='|' read -ra VS <<< "$VARIANTS"
+for v in "${VS[@]}"; do
   echo "== $v"
   opts=""; for o in $v; do opts="$opts --option $o"; done
   timeout -k 5 150 python bench.py --rows $ROWS --steps 3 --warmup 3 --no-e2e --no-cpu $opts --option role_prof=1 2>&1 | grep -E "role_prof|^\{|rror" | python -c "
