@@ -82,7 +82,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         tma_prefetch_desc(&tm_blo);
     }
     if (warp == 1 && lane == 0) {
-        const uint32_t group_count = leader ? 5 : 4;
+        // leader: its 4 warps + the peer's 4 warps (direct remote arrives) or + 1 relayed arrive (knockout bit 16)
+        const uint32_t group_count = leader ? ((p.knockout & 16) ? 5 : 8) : 4;
         for (int s = 0; s < 8; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&gdone[s], 1);
@@ -202,6 +203,10 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                                 }
                             }
                             tc_commit_pair(&gdone[grp % P]);                 // ONE cross-CTA signal per group
+                            if (p.knockout & 8) {   // experiment: what does an extra multicast commit cost?
+                                tc_commit_pair(&gdone[7]);   // gdone[6..7] are never waited on (P <= 6)
+                                tc_commit_pair(&gdone[7]);   // gdone[6..7] are never waited on (P <= 6)
+                            }
                             if (g == G - 1) tc_commit_pair(&acc_full[ab]);
                         }
                         __syncwarp();
@@ -216,8 +221,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 p.role_prof[3] = t_issue;
                 p.role_prof[4] = grp;
             }
-        } else {
-            // ---- peer CTA: relay "A slot written" to the leader
+        } else if (p.knockout & 16) {
+            // ---- peer CTA: relay "A slot written" to the leader (experiment; default = direct arrives)
             uint32_t grp = 0;
             for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
                 for (int nt = 0; nt < NT; ++nt)
@@ -228,8 +233,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     }
         }
     } else if (warp == 2) {
-        if (!leader) {
-            // ---- peer CTA: relay "accumulator drained" to the leader
+        if (!leader && (p.knockout & 16)) {
+            // ---- peer CTA: relay "accumulator drained" to the leader (experiment)
             uint32_t tile = 0;
             for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
                 for (int nt = 0; nt < NT; ++nt, ++tile) {
@@ -301,7 +306,10 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     tmem_wait_st();
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&a_full[aslot]);   // local; the peer's relay warp forwards it
+                    if (lane == 0) {
+                        if (leader || (p.knockout & 16)) mbar_arrive(&a_full[aslot]);
+                        else mbar_arrive_remote(&a_full[aslot], 0);   // blocks this warp for a few hundred cycles; it has the slack
+                    }
                     if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
                 }
             }
@@ -356,7 +364,10 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&acc_empty[ab]);    // local; the peer's relay warp forwards it
+                if (lane == 0) {
+                    if (leader || (p.knockout & 16)) mbar_arrive(&acc_empty[ab]);
+                    else mbar_arrive_remote(&acc_empty[ab], 0);
+                }
             }
             const int row = rt * kTileM + r;
             if (row < p.n && !(p.knockout & 4)) {
