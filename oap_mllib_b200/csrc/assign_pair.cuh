@@ -82,8 +82,9 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         tma_prefetch_desc(&tm_blo);
     }
     if (warp == 1 && lane == 0) {
-        // leader: its 4 warps + the peer's 4 warps (direct remote arrives) or + 1 relayed arrive (knockout bit 16)
-        const uint32_t group_count = leader ? ((p.knockout & 16) ? 5 : 8) : 4;
+        // leader: its 4 warps + 1 relayed arrive standing for the peer's 4 warps (experiment bit 16: the peer's
+        // 4 warps arrive remotely themselves)
+        const uint32_t group_count = leader ? ((p.knockout & 16) ? 8 : 5) : 4;
         for (int s = 0; s < 8; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&gdone[s], 1);
@@ -221,25 +222,33 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 p.role_prof[3] = t_issue;
                 p.role_prof[4] = grp;
             }
-        } else if (p.knockout & 16) {
-            // ---- peer CTA: relay "A slot written" to the leader (experiment; default = direct arrives)
+        } else if (!(p.knockout & 16)) {
+            // ---- peer CTA: relay "A slot written" to the leader.  The transform warps already ordered
+            // their TMEM stores (tcgen05.wait::st + fence) before the local arrive this warp waits on,
+            // so the forwarded arrive carries no data of its own and can be relaxed
             uint32_t grp = 0;
             for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
                 for (int nt = 0; nt < NT; ++nt)
                     for (int g = 0; g < G; ++g, ++grp) {
                         mbar_wait(&a_full[grp & 1], (grp >> 1) & 1);
-                        if (lane == 0) mbar_arrive_remote(&a_full[grp & 1], 0);
+                        if (lane == 0) {
+                            if (p.knockout & 32) mbar_arrive_remote(&a_full[grp & 1], 0);
+                            else mbar_arrive_remote_relaxed(&a_full[grp & 1], 0);
+                        }
                         __syncwarp();
                     }
         }
     } else if (warp == 2) {
-        if (!leader && (p.knockout & 16)) {
-            // ---- peer CTA: relay "accumulator drained" to the leader (experiment)
+        if (!leader && !(p.knockout & 16)) {
+            // ---- peer CTA: relay "accumulator drained" to the leader
             uint32_t tile = 0;
             for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
                 for (int nt = 0; nt < NT; ++nt, ++tile) {
                     mbar_wait(&acc_empty[tile & 1], (tile >> 1) & 1);
-                    if (lane == 0) mbar_arrive_remote(&acc_empty[tile & 1], 0);
+                    if (lane == 0) {
+                        if (p.knockout & 32) mbar_arrive_remote(&acc_empty[tile & 1], 0);
+                        else mbar_arrive_remote_relaxed(&acc_empty[tile & 1], 0);
+                    }
                     __syncwarp();
                 }
         }
@@ -307,8 +316,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) {
-                        if (leader || (p.knockout & 16)) mbar_arrive(&a_full[aslot]);
-                        else mbar_arrive_remote(&a_full[aslot], 0);   // blocks this warp for a few hundred cycles; it has the slack
+                        if (leader || !(p.knockout & 16)) mbar_arrive(&a_full[aslot]);   // the peer's relay warp forwards it
+                        else mbar_arrive_remote(&a_full[aslot], 0);
                     }
                     if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
                 }
@@ -365,7 +374,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    if (leader || (p.knockout & 16)) mbar_arrive(&acc_empty[ab]);
+                    if (leader || !(p.knockout & 16)) mbar_arrive(&acc_empty[ab]);
                     else mbar_arrive_remote(&acc_empty[ab], 0);
                 }
             }

@@ -176,6 +176,16 @@ __device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap *m, uint64_t 
         "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar), "r"(c0), "r"(c1), "l"(evict_normal)
         : "memory");
 }
+// Same, without the cluster-scope release (which costs several hundred cycles): for relays that only
+// forward an event whose data was already made visible by the local producers' own fences.
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint64_t *bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+        "r"(rank)
+        : "memory");
+}
 // arrive on the barrier at the same offset in CTA `rank` of the cluster
 __device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t rank) {
     asm volatile(
