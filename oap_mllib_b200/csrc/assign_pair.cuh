@@ -13,12 +13,14 @@
 //     the peer relay those to the leader (remote mbarrier arrives), keeping that latency off the
 //     warps that do arithmetic.
 // Roles per CTA: warp 0 B producer, warp 1 MMA issuer (leader) / A relay (peer), warp 2 TMEM
-// allocator, then accumulator relay (peer), warp 3 X producer, warps 4-7 transform (thread r = row r),
-// warps 8-11 epilogue (thread r = row r).
+// allocator, then accumulator relay (peer), warp 3 X producer, warps 4-7 transform of the first chunk of
+// every group and warps 12-15 of the second (thread r = row r), warps 8-11 epilogue (thread r = row r).
 #pragma once
 #include "assign_tc.cuh"
 
 namespace kmb {
+
+constexpr int kPairThreads = 512;
 
 template <int BN>
 struct PairCfg {
@@ -39,7 +41,7 @@ struct PairCfg {
 
 // tm_bhi / tm_blo: boxes of BN/2 rows.  p.stages = RB (group slots of the B ring).
 template <int BN>
-__global__ void __launch_bounds__(kAssignThreads, 1)
+__global__ void __launch_bounds__(kPairThreads, 1)
 assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_bhi,
                    const __grid_constant__ CUtensorMap tm_blo, const AssignParams p) {
     using Cfg = PairCfg<BN>;
@@ -85,6 +87,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         // leader: its 4 warps + 1 relayed arrive standing for the peer's 4 warps (experiment bit 16: the peer's
         // 4 warps arrive remotely themselves)
         const uint32_t group_count = leader ? ((p.knockout & 16) ? 8 : 5) : 4;
+        const uint32_t a_count = group_count + 4;   // two transform warpgroups write every A slot
         for (int s = 0; s < 8; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&gdone[s], 1);
@@ -92,7 +95,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             mbar_init(&xempty[s], 4);
         }
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&a_full[b], group_count);
+            mbar_init(&a_full[b], (p.knockout & 16) ? 16u * leader + 8u * !leader : a_count);
             mbar_init(&acc_full[b], 1);
             mbar_init(&acc_empty[b], group_count);
         }
@@ -252,9 +255,11 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     __syncwarp();
                 }
         }
-    } else if (warp >= 4 && warp < 8) {
+    } else if ((warp >= 4 && warp < 8) || warp >= 12) {
         // ================================ transform ===================================
-        const int r = threadIdx.x - 128;
+        // two warpgroups: warps 4-7 convert the first chunk of every group, warps 12-15 the second
+        const int mychunk = warp >= 12 ? 1 : 0;
+        const int r = threadIdx.x & 127;
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
         uint32_t grp = 0, xph = 0;
         long long t_load = 0, t_wait_a = 0, t_store = 0, t_mark = 0;
@@ -265,8 +270,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     const int nch = (2 * g + 1 < KC) ? 2 : 1;
                     const uint32_t aslot = grp & 1;
                     bool waited = false;
-#pragma unroll
-                    for (int c = 0; c < 2; ++c) {
+                    for (int c = mychunk; c <= mychunk; ++c) {
                         if (c >= nch) break;
                         const int kc = 2 * g + c;
                         if (prof) t_mark = clock64();
@@ -331,7 +335,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             o[2] = t_store;
             o[3] = grp;
         }
-    } else if (warp >= 8) {
+    } else if (warp >= 8 && warp < 12) {
         // ================================ epilogue ====================================
         const int r = threadIdx.x - 256;
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;

@@ -591,7 +591,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     const int pairs = std::min((p.num_row_tiles + 1) / 2, t->num_sms / 2);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(pairs * 2));
-    cfg.blockDim = dim3(kAssignThreads);
+    cfg.blockDim = dim3(kPairThreads);
     cfg.dynamicSmemBytes = (size_t)smem;
     cfg.stream = t->stream;
     cudaLaunchAttribute attr[1];
