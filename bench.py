@@ -253,8 +253,8 @@ def run_ours(args, rank, local_rank, world):
             tr = json.load(f)
         key = f"{args.workload}_n{world}"
         if key in tr and tr[key].get("rows") == n_local:
-            traffic = tr[key]["assign_tc_dram_bytes_per_launch"]
-    roofline = {"bound": "tensor", "kernel": "assign_tc_kernel", "achieved": achieved, "peak": tf32_peak,
+            traffic = tr[key]["assign_dram_bytes_per_launch"]
+    roofline = {"bound": "tensor", "kernel": "assign_pair_kernel (tcgen05 cta_group::2) / assign_tc_kernel for d > 256", "achieved": achieved, "peak": tf32_peak,
                 "unit": "TFLOP/s", "frac": achieved / tf32_peak, "traffic": traffic,
                 "peak_source": f"0.5 x bf16_tflops_sustained of {peaks['source']} MEASURED_PEAKS.json "
                                "(TF32 = half the bf16 rate); kernel timed inside a long step",

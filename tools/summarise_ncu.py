@@ -56,12 +56,12 @@ with open(os.path.join(out, f"{tag}_ncu_full_summary.csv"), "w") as f:
     for r in rr[2:]:
         w.writerow([r[i] for i in cols])
         name = r[h.index("Kernel Name")]
-        if "assign_tc" in name:
+        if "assign_pair" in name or "assign_tc" in name:
             def val(metric):
                 i = h.index(metric)
                 mult = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(units[i], 1)
                 return float(r[i]) * mult
-            traffic = {"assign_tc_dram_bytes_per_launch": val("dram__bytes_read.sum") + val("dram__bytes_write.sum"),
+            traffic = {"assign_dram_bytes_per_launch": val("dram__bytes_read.sum") + val("dram__bytes_write.sum"),
                        "rows": 100_000_000, "source": f"profiles/{tag}_ncu_full_summary.csv (ncu --set full)"}
 if traffic:
     tp = os.path.join(out, "traffic.json")
