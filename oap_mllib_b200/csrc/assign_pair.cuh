@@ -16,6 +16,8 @@
 // allocator, then accumulator relay (peer), warp 3 X producer, warps 4-7 transform of the first chunk of
 // every group and warps 12-15 of the second (thread r = row r), warps 8-11 epilogue (thread r = row r).
 #pragma once
+#include <cuda_bf16.h>
+
 #include "assign_tc.cuh"
 
 namespace kmb {
@@ -40,7 +42,12 @@ struct PairCfg {
 };
 
 // tm_bhi / tm_blo: boxes of BN/2 rows.  p.stages = RB (group slots of the B ring).
-template <int BN>
+// BF16C: the two correction products of the 3xTF32 scheme (x_lo.w_hi and x_hi.w_lo, each ~2^-11 of
+// the main product) are computed by ONE BF16 MMA chain instead of two TF32 ones: A chunk = [hi TF32 x 32
+// | bf16(x_lo) x 32 | bf16(x) x 32] (still 64 TMEM columns), tm_blo then maps the BF16 operand
+// [bf16(w_hi) x 32 | bf16(w_lo) x 32] per chunk.  8 instead of 12 MMAs per chunk; the extra rounding
+// (<= 2^-18 relative) is part of the score bound.
+template <int BN, bool BF16C>
 __global__ void __launch_bounds__(kPairThreads, 1)
 assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_bhi,
                    const __grid_constant__ CUtensorMap tm_blo, const AssignParams p) {
@@ -142,7 +149,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                                 // always land in the phase the leader is arming
                                 if (leader) mbar_arrive_expect_tx(&full[s], 2 * Cfg::kBStageBytes);
                                 tma_load_2d_pair(&tm_bhi, &full[s], st, kc * kChunkK, brow);
-                                tma_load_2d_pair(&tm_blo, &full[s], st + Cfg::kBChunkBytes, kc * kChunkK, brow);
+                                tma_load_2d_pair(&tm_blo, &full[s], st + Cfg::kBChunkBytes, kc * (BF16C ? 2 * kChunkK : kChunkK), brow);
                             }
                         }
                     }
@@ -168,6 +175,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         if (leader) {
             // ================================ MMA issuer ==============================
             constexpr uint32_t idesc = make_idesc_tf32(2 * kTileM, BN);
+            constexpr uint32_t idesc16 = make_idesc_bf16(2 * kTileM, BN);
             uint32_t grp = 0, tile = 0;
             long long t_wait_acc = 0, t_wait = 0, t_issue = 0, t_mark = 0;
             const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
@@ -196,13 +204,24 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                                     const uint32_t bsm = smem_u32(bs + (s0 + c) * Cfg::kBStageBytes);
                                     const uint64_t dhi = make_kmajor_sw128_desc(bsm);
                                     const uint64_t dlo = make_kmajor_sw128_desc(bsm + Cfg::kBChunkBytes);
+                                    if constexpr (BF16C) {
+                                        // corrections first (small terms): K = 64 BF16 values = 4 instructions
 #pragma unroll
-                                    for (int ks = 0; ks < kChunkK / 8; ++ks) {
-                                        const uint64_t koff = static_cast<uint64_t>(ks * 2);
-                                        const uint32_t first = (g | c | ks) == 0 ? 0u : 1u;
-                                        mma_tf32_ts_pair(d_tmem, a_lo + ks * 8, dhi + koff, idesc, first);  // small terms first
-                                        mma_tf32_ts_pair(d_tmem, a_hi + ks * 8, dlo + koff, idesc, 1u);
-                                        mma_tf32_ts_pair(d_tmem, a_hi + ks * 8, dhi + koff, idesc, 1u);
+                                        for (int ks = 0; ks < 4; ++ks)
+                                            mma_bf16_ts_pair(d_tmem, a_lo + ks * 8, dlo + static_cast<uint64_t>(ks * 2), idesc16,
+                                                             (g | c | ks) == 0 ? 0u : 1u);
+#pragma unroll
+                                        for (int ks = 0; ks < kChunkK / 8; ++ks)
+                                            mma_tf32_ts_pair(d_tmem, a_hi + ks * 8, dhi + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                                    } else {
+#pragma unroll
+                                        for (int ks = 0; ks < kChunkK / 8; ++ks) {
+                                            const uint64_t koff = static_cast<uint64_t>(ks * 2);
+                                            const uint32_t first = (g | c | ks) == 0 ? 0u : 1u;
+                                            mma_tf32_ts_pair(d_tmem, a_lo + ks * 8, dhi + koff, idesc, first);  // small terms first
+                                            mma_tf32_ts_pair(d_tmem, a_hi + ks * 8, dlo + koff, idesc, 1u);
+                                            mma_tf32_ts_pair(d_tmem, a_hi + ks * 8, dhi + koff, idesc, 1u);
+                                        }
                                     }
                                 }
                             }
@@ -296,6 +315,18 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                             const float h = __fsub_rn(t, __fsub_rn(t, x[i]));
                             hi[i] = __float_as_uint(h);
                             lo[i] = __float_as_uint(__fsub_rn(x[i], h));
+                        }
+                        if constexpr (BF16C) {
+                            // pack [bf16(x_lo) x 32 | bf16(x) x 32] into lo[0..31]: element 2i in the low half
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                const __nv_bfloat162 a2 = __floats2bfloat162_rn(__uint_as_float(lo[2 * i]), __uint_as_float(lo[2 * i + 1]));
+                                const __nv_bfloat162 b2 = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
+                                lo[i] = *reinterpret_cast<const uint32_t *>(&a2);
+                                x[i] = __uint_as_float(*reinterpret_cast<const uint32_t *>(&b2));
+                            }
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) lo[16 + i] = __float_as_uint(x[i]);
                         }
                         if (nt == NT - 1) {   // last read of this chunk: the X producer may reload it
                             __syncwarp();

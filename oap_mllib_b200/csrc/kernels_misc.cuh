@@ -2,6 +2,7 @@
 // of near-tie rows, label bucketing, per-cluster FP64 accumulation, finalize / convergence, the
 // empty-cluster candidate search and the synthetic-blob generator.
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -66,9 +67,12 @@ __global__ void rownorm_kernel(const float *__restrict__ X, float *__restrict__ 
 // One CTA per padded centroid row j.  For j < k: B_hi/B_lo = TF32 round-to-nearest split of -2*c_j,
 // cnorm = ||c_j||^2 (FP64 sum, rounded to FP32), cstats[0] = max ||c_j|| (atomicMax on the bits of
 // a non-negative float).  For j >= k: zero rows and cnorm = +inf so the column never wins.
+// bcorr (BF16, [kpad x 2*ld]) is the B operand of the BF16 correction MMAs: for every 32-column chunk
+// 64 values per centre, [bf16(hi) x 32 | bf16(lo) x 32], so that one 128-byte row pairs with the A
+// chunk [bf16(x_lo) x 32 | bf16(x) x 32] and sums x_lo.w_hi + x.w_lo.
 __global__ void split_centers_kernel(const double *__restrict__ cent, float *__restrict__ bhi,
-                                     float *__restrict__ blo, float *__restrict__ cnorm, float *cstats, int k,
-                                     int ld) {
+                                     float *__restrict__ blo, __nv_bfloat16 *__restrict__ bcorr,
+                                     float *__restrict__ cnorm, float *cstats, int k, int ld) {
     const int j = blockIdx.x;
     __shared__ double red[32];
     double acc = 0.0;
@@ -88,6 +92,9 @@ __global__ void split_centers_kernel(const double *__restrict__ cent, float *__r
         }
         bhi[(size_t)j * ld + c] = h;
         blo[(size_t)j * ld + c] = l;
+        const size_t cb = (size_t)j * 2 * ld + (size_t)(c >> 5) * 64 + (c & 31);
+        bcorr[cb] = __float2bfloat16_rn(h);
+        bcorr[cb + 32] = __float2bfloat16_rn(l);
     }
     acc = warp_sum(acc);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;

@@ -156,6 +156,16 @@ __device__ __forceinline__ void mma_tf32_ts_pair(uint32_t tmem_d, uint32_t tmem_
         "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// same with BF16 operands (K = 16 per instruction; A: two K values per 32-bit TMEM column)
+__device__ __forceinline__ void mma_bf16_ts_pair(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                                 uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // completion of this thread's earlier pair-MMAs -> arrive on the barrier at this offset in BOTH CTAs
 __device__ __forceinline__ void tc_commit_pair(uint64_t *bar) {
     asm volatile(
@@ -318,6 +328,19 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(uint32_t m, uint32_t n) {
            | (2u << 10)         // B format TF32
            | ((n >> 3) << 17)   // N / 8
            | ((m >> 4) << 24);  // M / 16
+}
+
+// Instruction descriptor for kind::f16 with BF16 operands, FP32 accumulate, both K-major.
+__host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t m, uint32_t n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+        "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
 }
 
 __device__ __forceinline__ float to_tf32_rna(float x) {
