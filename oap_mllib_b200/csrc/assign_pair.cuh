@@ -373,8 +373,16 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         const float cmax = p.cstats[0];
         uint32_t tile = 0;
         for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x) {
-            float best = __int_as_float(0x7f800000), second = best, third = best;
-            int bidx = 0, sidx = 0;
+            // Four independent running top-3 sets (columns i mod 4): the update of one set is a serial
+            // chain of min/max/select, four chains give the ALU pipe independent work.  Inside a set the
+            // columns arrive in ascending order, so strict '<' keeps the lowest index; the sets are
+            // merged once per row tile with an explicit (value, index) tie rule.
+            constexpr int NS = 4;
+            const float inf = __int_as_float(0x7f800000);
+            float best[NS], second[NS], third[NS];
+            int bidx[NS], sidx[NS];
+#pragma unroll
+            for (int q = 0; q < NS; ++q) { best[q] = second[q] = third[q] = inf; bidx[q] = sidx[q] = 0; }
             for (int nt = 0; nt < NT; ++nt, ++tile) {
                 const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
                 float *cn = cn_s + ab * BN;
@@ -391,18 +399,17 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                         tmem_wait_ld();
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
+                            const int q = i & (NS - 1);
                             const float sc = __uint_as_float(v[i]) + cn[c0 + i];
                             if (p.dbg_scores != nullptr && rt * kTileM + r < p.n)
                                 p.dbg_scores[(size_t)(rt * kTileM + r) * p.kpad + nt * BN + c0 + i] = sc;
-                            // running top-3 values with the indices of the best two; strict '<' keeps
-                            // the lowest index among equal scores
                             const int j = nt * BN + c0 + i;
-                            const bool lt1 = sc < best, lt2 = sc < second;
-                            third = fminf(third, fmaxf(sc, second));
-                            sidx = lt1 ? bidx : (lt2 ? j : sidx);
-                            second = fminf(second, fmaxf(sc, best));
-                            bidx = lt1 ? j : bidx;
-                            best = fminf(best, sc);
+                            const bool lt1 = sc < best[q], lt2 = sc < second[q];
+                            third[q] = fminf(third[q], fmaxf(sc, second[q]));
+                            sidx[q] = lt1 ? bidx[q] : (lt2 ? j : sidx[q]);
+                            second[q] = fminf(second[q], fmaxf(sc, best[q]));
+                            bidx[q] = lt1 ? j : bidx[q];
+                            best[q] = fminf(best[q], sc);
                         }
                     }
                 }
@@ -413,14 +420,28 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     else mbar_arrive_remote(&acc_empty[ab], 0);
                 }
             }
+            // merge sets 1..3 into set 0: lower value first, equal values -> lower index first
+            float mb = best[0], ms = second[0], mt = third[0];
+            int mbi = bidx[0], msi = sidx[0];
+            auto insert = [&](float v, int j, bool has_index) {
+                if (has_index && (v < mb || (v == mb && j < mbi))) { mt = ms; ms = mb; msi = mbi; mb = v; mbi = j; }
+                else if (has_index && (v < ms || (v == ms && j < msi))) { mt = ms; ms = v; msi = j; }
+                else if (v < mt) mt = v;
+            };
+#pragma unroll
+            for (int q = 1; q < NS; ++q) {
+                insert(best[q], bidx[q], true);
+                insert(second[q], sidx[q], true);
+                insert(third[q], 0, false);   // can only ever become the merged third value
+            }
             const int row = rt * kTileM + r;
             if (row < p.n && !(p.knockout & 4)) {
-                p.labels[row] = bidx;
+                p.labels[row] = mbi;
                 const float xn = sqrtf(p.xnorm[row]);
                 const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
-                if (second - best <= bound) {
+                if (ms - mb <= bound) {
                     const int pos = atomicAdd(p.flag_count, 1);
-                    if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, (third - best <= bound) ? -1 : sidx);
+                    if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, (mt - mb <= bound) ? -1 : msi);
                 }
             }
         }
