@@ -329,6 +329,7 @@ def run_ours(args, rank, local_rank, world):
             "tflops_algorithmic": 2.0 * rows * d * k / (ms_per_step * 1e-3) / 1e12,
             "wall_ms_per_step": wall_ms / args.steps, "phases_ms_per_step": phases,
             "rechecked_rows_per_step": prof["rechecked_rows"] / args.steps,
+            "full_rechecks_per_step": prof["full_rechecks"] / args.steps,
             "final_cost": cost, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)

@@ -114,6 +114,7 @@ typedef struct {
     int32_t kernel_launches;   /* kernels of this library launched                           */
     int64_t rechecked_rows;    /* rows whose top-2 gap was inside the error bound (FP64 re-check) */
     int32_t empty_cluster_events;
+    int64_t full_rechecks;     /* of those, rows that needed all k centres re-scored (third centre inside the bound) */
     float total_ms;            /* first kernel of the first iteration -> end of the last         */
     float assign_ms;           /* tcgen05 distance GEMM + argmin epilogue                        */
     float recheck_ms;          /* FP64 re-evaluation of near-tie rows                            */

@@ -20,7 +20,7 @@ class Kmb200Error(RuntimeError):
 
 class Profile(C.Structure):
     _fields_ = [("iterations", C.c_int32), ("kernel_launches", C.c_int32), ("rechecked_rows", C.c_int64),
-                ("empty_cluster_events", C.c_int32), ("total_ms", C.c_float), ("assign_ms", C.c_float),
+                ("empty_cluster_events", C.c_int32), ("full_rechecks", C.c_int64), ("total_ms", C.c_float), ("assign_ms", C.c_float),
                 ("recheck_ms", C.c_float), ("bucket_ms", C.c_float), ("accumulate_ms", C.c_float),
                 ("allreduce_ms", C.c_float), ("finalize_ms", C.c_float)]
 

@@ -31,7 +31,7 @@ struct PairCfg {
     static constexpr int kBStageBytes = 2 * kBChunkBytes;     // hi + lo
     static constexpr int kAccCol0 = 256;                      // A: 2 group slots x 2 chunks x (32 hi + 32 lo)
     static constexpr int kTmemCols = 512;
-    static constexpr int kNumBars = 8 /*full*/ + 8 /*gdone*/ + 8 /*xfull*/ + 8 /*xempty*/ + 2 + 2 + 2;
+    static constexpr int kNumBars = 8 /*full*/ + 8 /*gdone*/ + 8 /*xfull*/ + 8 /*xempty*/ + 4 + 2 + 2;
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16;
     // B ring: RB group slots of two stages each (RB <= 4)
     static int group_slots(int kc) {
@@ -71,9 +71,9 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                                       //      and its A slot may be overwritten
     uint64_t *xfull = bars + 16;      // [8]  X chunk landed
     uint64_t *xempty = bars + 24;     // [8]  X chunk read for the last time by the transform
-    uint64_t *a_full = bars + 32;     // [2]  A slot written (4 local warps; leader: + 1 relayed arrive)
-    uint64_t *acc_full = bars + 34;   // [2]  accumulator tile complete (multicast commit)
-    uint64_t *acc_empty = bars + 36;  // [2]  accumulator drained (4 local warps; leader: + 1 relayed arrive)
+    uint64_t *a_full = bars + 32;     // [4]  chunk c of A slot s written: index 2*s + c (4 local warps; leader: + 1 relayed arrive)
+    uint64_t *acc_full = bars + 36;   // [2]  accumulator tile complete (multicast commit)
+    uint64_t *acc_empty = bars + 38;  // [2]  accumulator drained (4 local warps; leader: + 1 relayed arrive)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
 
     const int warp = threadIdx.x >> 5;
@@ -94,15 +94,14 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         // leader: its 4 warps + 1 relayed arrive standing for the peer's 4 warps (experiment bit 16: the peer's
         // 4 warps arrive remotely themselves)
         const uint32_t group_count = leader ? ((p.knockout & 16) ? 8 : 5) : 4;
-        const uint32_t a_count = group_count + 4;   // two transform warpgroups write every A slot
         for (int s = 0; s < 8; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&gdone[s], 1);
             mbar_init(&xfull[s], 1);
             mbar_init(&xempty[s], 4);
         }
+        for (int b = 0; b < 4; ++b) mbar_init(&a_full[b], group_count);   // one transform warpgroup per chunk
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&a_full[b], (p.knockout & 16) ? 16u * leader + 8u * !leader : a_count);
             mbar_init(&acc_full[b], 1);
             mbar_init(&acc_empty[b], group_count);
         }
@@ -192,12 +191,19 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                         const uint32_t aslot = grp & 1, aph2 = (grp >> 1) & 1;
                         const uint32_t bslot = grp % RB, bph = (grp / RB) & 1;
                         const uint32_t s0 = bslot * 2, s1 = s0 + 1;
-                        mbar_wait3(&a_full[aslot], aph2, &full[s0], bph, &full[s1], bph);
+                        // chunk 1's A operand is only needed after chunk 0's MMAs have been issued: waiting
+                        // for it separately gives the second transform warpgroup half a group more time
+                        mbar_wait3(&a_full[aslot * 2], aph2, &full[s0], bph, &full[s1], bph);
                         if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
                         tc_fence_after();
-                        if (elect_one()) {
 #pragma unroll
-                            for (int c = 0; c < 2; ++c) {
+                        for (int c = 0; c < 2; ++c) {
+                            if (c == 1) {
+                                mbar_wait(&a_full[aslot * 2 + 1], aph2);
+                                if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
+                                tc_fence_after();
+                            }
+                            if (elect_one()) {
                                 if (c < nch) {
                                     const uint32_t a_hi = tmem_base + aslot * 128 + c * 64;
                                     const uint32_t a_lo = a_hi + 32;
@@ -224,16 +230,14 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                                         }
                                     }
                                 }
+                                if (c == 1) {
+                                    tc_commit_pair(&gdone[grp % P]);                 // ONE cross-CTA signal per group
+                                    if (g == G - 1) tc_commit_pair(&acc_full[ab]);
+                                }
                             }
-                            tc_commit_pair(&gdone[grp % P]);                 // ONE cross-CTA signal per group
-                            if (p.knockout & 8) {   // experiment: what does an extra multicast commit cost?
-                                tc_commit_pair(&gdone[7]);   // gdone[6..7] are never waited on (P <= 6)
-                                tc_commit_pair(&gdone[7]);   // gdone[6..7] are never waited on (P <= 6)
-                            }
-                            if (g == G - 1) tc_commit_pair(&acc_full[ab]);
+                            __syncwarp();
+                            if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
                         }
-                        __syncwarp();
-                        if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
                     }
                 }
             }
@@ -252,12 +256,15 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
                 for (int nt = 0; nt < NT; ++nt)
                     for (int g = 0; g < G; ++g, ++grp) {
-                        mbar_wait(&a_full[grp & 1], (grp >> 1) & 1);
-                        if (lane == 0) {
-                            if (p.knockout & 32) mbar_arrive_remote(&a_full[grp & 1], 0);
-                            else mbar_arrive_remote_relaxed(&a_full[grp & 1], 0);
+                        for (int c = 0; c < 2; ++c) {
+                            uint64_t *bar = &a_full[(grp & 1) * 2 + c];
+                            mbar_wait(bar, (grp >> 1) & 1);
+                            if (lane == 0) {
+                                if (p.knockout & 32) mbar_arrive_remote(bar, 0);
+                                else mbar_arrive_remote_relaxed(bar, 0);
+                            }
+                            __syncwarp();
                         }
-                        __syncwarp();
                     }
         }
     } else if (warp == 2) {
@@ -351,8 +358,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) {
-                        if (leader || !(p.knockout & 16)) mbar_arrive(&a_full[aslot]);   // the peer's relay warp forwards it
-                        else mbar_arrive_remote(&a_full[aslot], 0);
+                        if (leader || !(p.knockout & 16)) mbar_arrive(&a_full[aslot * 2 + mychunk]);   // the peer's relay warp forwards it
+                        else mbar_arrive_remote(&a_full[aslot * 2 + mychunk], 0);
                     }
                     if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
                 }
@@ -439,10 +446,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 p.labels[row] = mbi;
                 const float xn = sqrtf(p.xnorm[row]);
                 const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
-                if (ms - mb <= bound) {
-                    const int pos = atomicAdd(p.flag_count, 1);
-                    if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, (mt - mb <= bound) ? -1 : msi);
-                }
+                if (ms - mb <= bound) flag_row(p, row, msi, mt - mb <= bound);
             }
         }
     }

@@ -50,7 +50,7 @@ struct AssignParams {
     const float *xnorm;    // [n]     ||x_i||^2
     const float *cstats;   // [0] = max_j ||c_j||
     int32_t *labels;       // [n]
-    int32_t *flag_count;   // number of near-tie rows appended to flag_list
+    int32_t *flag_count;   // [0] (row, runner-up) entries at the front of flag_list, [1] full-scan entries at its back
     int2 *flag_list;       // [flag_cap] (row, runner-up centre) or (row, -1) when a third centre is inside the bound too
     int32_t flag_cap;
     int32_t n;             // rows in the table
@@ -65,6 +65,20 @@ struct AssignParams {
     long long *role_prof;  // optional cycle counters of the MMA-issuer warp of CTA 0 (diagnostics), else nullptr
     int32_t knockout;      // debugging only: 1 = no TMA, 2 = no transform work, 4 = no epilogue work (results invalid)
 };
+
+// Near-tie bookkeeping shared by the assign kernels: rows whose winner must be decided in FP64.
+// (row, runner-up) entries grow from the front of flag_list (flag_count[0]); rows with a third centre
+// inside the bound need all k centres re-scored and are listed from the BACK (flag_count[1]), so the
+// two kinds can be processed by differently shaped kernels.
+__device__ __forceinline__ void flag_row(const AssignParams &p, int row, int runner, bool need_full) {
+    if (need_full) {
+        const int pos = atomicAdd(p.flag_count + 1, 1);
+        if (pos < p.flag_cap) p.flag_list[p.flag_cap - 1 - pos] = make_int2(row, -1);
+    } else {
+        const int pos = atomicAdd(p.flag_count, 1);
+        if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, runner);
+    }
+}
 
 template <int BN>
 __global__ void __launch_bounds__(kAssignThreads, 1)
@@ -299,10 +313,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                 p.labels[row] = bidx;
                 const float xn = sqrtf(p.xnorm[row]);
                 const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
-                if (second - best <= bound) {
-                    const int pos = atomicAdd(p.flag_count, 1);
-                    if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, (third - best <= bound) ? -1 : sidx);
-                }
+                if (second - best <= bound) flag_row(p, row, sidx, third - best <= bound);
             }
         }
     }

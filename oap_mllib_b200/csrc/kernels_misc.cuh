@@ -196,6 +196,40 @@ __global__ void recheck_kernel(const float *__restrict__ X, const double *__rest
     }
 }
 
+// Full re-score of the rows listed at the BACK of flag_list (entries cap-1, cap-2, ...): one CTA of 8
+// warps per row, warp w scores centres w, w+8, ... in FP64, then the 8 partial winners are merged
+// (lower score first, equal scores -> lower index).
+__global__ void __launch_bounds__(256)
+recheck_full_kernel(const float *__restrict__ X, const double *__restrict__ cent, const int2 *__restrict__ list,
+                    const int32_t *__restrict__ full_count, int32_t list_cap, int k, int ld,
+                    int32_t *__restrict__ labels) {
+    __shared__ double s_best[8];
+    __shared__ int s_idx[8];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int count = *full_count;
+    if (count > list_cap) count = list_cap;
+    for (int e = blockIdx.x; e < count; e += gridDim.x) {
+        const int row = list[list_cap - 1 - e].x;
+        const float *xrow = X + (size_t)row * ld;
+        double best = INFINITY;
+        int bidx = 0x7fffffff;
+        for (int j = w; j < k; j += 8) {
+            const double sc = exact_score(xrow, cent + (size_t)j * ld, ld, lane);
+            if (sc < best) { best = sc; bidx = j; }
+        }
+        if (lane == 0) { s_best[w] = best; s_idx[w] = bidx; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double b = s_best[0];
+            int bi = s_idx[0];
+            for (int q = 1; q < 8; ++q)
+                if (s_best[q] < b || (s_best[q] == b && s_idx[q] < bi)) { b = s_best[q]; bi = s_idx[q]; }
+            labels[row] = bi;
+        }
+        __syncthreads();
+    }
+}
+
 // ------------------------------------------------------------------ bucketing rows by label
 // counts[j] = number of local rows with label j.
 __global__ void label_hist_kernel(const int32_t *__restrict__ labels, int64_t n, int k, int32_t *counts) {

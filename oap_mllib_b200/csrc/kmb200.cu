@@ -138,7 +138,7 @@ struct Workspace {
     struct Host {
         int32_t flags[2];
         int32_t flag_count;
-        int32_t pad;
+        int32_t full_count;
         double cost;
     } *host = nullptr;
 };
@@ -699,7 +699,10 @@ static int launch_recheck(kmb200_table *t) {
     recheck_kernel<<<t->num_sms * 4, 256, 0, t->stream>>>(t->X, w.cent, w.flag_list, w.flag_count, (int32_t)t->rows,
                                                          t->rows, w.k, t->ld, w.labels);
     CU_TRY(cudaGetLastError());
-    g_prof.kernel_launches++;
+    recheck_full_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, w.cent, w.flag_list, w.flag_count + 1,
+                                                              (int32_t)t->rows, w.k, t->ld, w.labels);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches += 2;
     return 0;
 }
 
@@ -952,7 +955,7 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
         // exactly, so the converged flag (and the rare empty-cluster count) is read every time
         CU_TRY(cudaMemcpyAsync(&w.host->cost, w.red + (size_t)k * t->ld + k, sizeof(double), cudaMemcpyDeviceToHost, st));
         CU_TRY(cudaMemcpyAsync(w.host->flags, w.flags, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        CU_TRY(cudaMemcpyAsync(&w.host->flag_count, w.flag_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaMemcpyAsync(&w.host->flag_count, w.flag_count, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         CU_TRY(cudaStreamSynchronize(st));
         cost = w.host->cost;
         int moved = w.host->flags[0];
@@ -960,7 +963,8 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
         std::swap(w.cent, w.cent2);
         KM_TRY(launch_split(t));  // TF32 split + norms of the new centres for the next assignment
         if (timed) CU_TRY(cudaEventRecord(ev[6], st));
-        g_prof.rechecked_rows += g_force_simt ? 0 : std::min<int64_t>(w.host->flag_count, t->rows);
+        g_prof.rechecked_rows += g_force_simt ? 0 : std::min<int64_t>((int64_t)w.host->flag_count + w.host->full_count, t->rows);
+        g_prof.full_rechecks += g_force_simt ? 0 : w.host->full_count;
         converged = tol >= 0.0 && moved == 0;
     }
     KM_TRY(download_centers(t, out_centers, k, d));
@@ -1017,13 +1021,14 @@ extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *c
         CU_TRY(cudaMemcpyAsync(labels_host, w.labels, (size_t)t->rows * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     std::vector<double> tail((size_t)k + 1);
     CU_TRY(cudaMemcpyAsync(tail.data(), w.red + (size_t)k * t->ld, ((size_t)k + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
-    CU_TRY(cudaMemcpyAsync(&w.host->flag_count, w.flag_count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(&w.host->flag_count, w.flag_count, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     CU_TRY(cudaStreamSynchronize(st));
     if (sizes_host)
         for (int j = 0; j < k; ++j) sizes_host[j] = (int64_t)llround(tail[j]);
     if (cost_host) *cost_host = tail[k];
     g_prof.iterations = 1;
-    g_prof.rechecked_rows = g_force_simt ? 0 : std::min<int64_t>(w.host->flag_count, t->rows);
+    g_prof.rechecked_rows = g_force_simt ? 0 : std::min<int64_t>((int64_t)w.host->flag_count + w.host->full_count, t->rows);
+    g_prof.full_rechecks = g_force_simt ? 0 : w.host->full_count;
     cudaEventElapsedTime(&g_prof.assign_ms, ev[0], ev[1]);
     cudaEventElapsedTime(&g_prof.recheck_ms, ev[1], ev[2]);
     cudaEventElapsedTime(&g_prof.bucket_ms, ev[2], ev[3]);

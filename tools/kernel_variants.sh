@@ -11,7 +11,7 @@ import sys, json
 for line in sys.stdin:
     if line.startswith('{'):
         d = json.loads(line)
-        print({k: round(v, 2) for k, v in d['phases_ms_per_step'].items()}, 'rechecked', d['rechecked_rows_per_step'], 'exec TF/s', round(3 * d['roofline']['achieved'], 1), 'cost', d['final_cost'])
+        print({k: round(v, 2) for k, v in d['phases_ms_per_step'].items()}, 'rechecked', d['rechecked_rows_per_step'], 'full', d.get('full_rechecks_per_step'), 'exec TF/s', round(3 * d['roofline']['achieved'], 1), 'cost', d['final_cost'])
     else:
         print(line.strip())
 "
