@@ -354,6 +354,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                         if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
                     }
                     if (prof) t_mark = clock64();
+                    if (!waited) wait_group_done(grp, 2);   // no chunk to convert (odd chunk count): still keep in
+                                                            // step with the MMAs, or the arrive below overruns the barrier
                     tmem_wait_st();
                     tc_fence_before();
                     __syncwarp();
