@@ -448,7 +448,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 p.labels[row] = mbi;
                 const float xn = sqrtf(p.xnorm[row]);
                 const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
-                if (ms - mb <= bound) flag_row(p, row, msi, mt - mb <= bound);
+                if (ms - mb <= bound) flag_row(p, row, mbi, msi, mt - mb <= bound);
             }
         }
     }

@@ -70,13 +70,14 @@ struct AssignParams {
 // (row, runner-up) entries grow from the front of flag_list (flag_count[0]); rows with a third centre
 // inside the bound need all k centres re-scored and are listed from the BACK (flag_count[1]), so the
 // two kinds can be processed by differently shaped kernels.
-__device__ __forceinline__ void flag_row(const AssignParams &p, int row, int runner, bool need_full) {
+__device__ __forceinline__ void flag_row(const AssignParams &p, int row, int winner, int runner, bool need_full) {
     if (need_full) {
         const int pos = atomicAdd(p.flag_count + 1, 1);
         if (pos < p.flag_cap) p.flag_list[p.flag_cap - 1 - pos] = make_int2(row, -1);
     } else {
         const int pos = atomicAdd(p.flag_count, 1);
-        if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, runner);
+        // both centre indices fit 16 bits (k <= 65536): the re-check then needs no dependent label load
+        if (pos < p.flag_cap) p.flag_list[pos] = make_int2(row, (winner << 16) | runner);
     }
 }
 
@@ -313,7 +314,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                 p.labels[row] = bidx;
                 const float xn = sqrtf(p.xnorm[row]);
                 const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
-                if (second - best <= bound) flag_row(p, row, sidx, third - best <= bound);
+                if (second - best <= bound) flag_row(p, row, bidx, sidx, third - best <= bound);
             }
         }
     }

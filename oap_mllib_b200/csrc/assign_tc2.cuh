@@ -367,7 +367,7 @@ assign_tc2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                 p.labels[row] = bidx;
                 const float xn = sqrtf(p.xnorm[row]);
                 const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
-                if (second - best <= bound) flag_row(p, row, sidx, third - best <= bound);
+                if (second - best <= bound) flag_row(p, row, bidx, sidx, third - best <= bound);
             }
         }
     }

@@ -156,9 +156,38 @@ __global__ void recheck_kernel(const float *__restrict__ X, const double *__rest
         }
         const float *xrow = X + row * ld;
         if (runner >= 0) {
-            const int cur = labels[row];
-            const double s_cur = exact_score(xrow, cent + (size_t)cur * ld, ld, lane);
-            const double s_run = exact_score(xrow, cent + (size_t)runner * ld, ld, lane);
+            // entry.y = (winner << 16) | runner-up, both chosen by the tensor-core epilogue
+            const int cur = (runner >> 16) & 0xffff;
+            runner &= 0xffff;
+            const double *cc = cent + (size_t)cur * ld, *cr = cent + (size_t)runner * ld;
+            double s_cur, s_run;
+            if (per_lane <= 8) {
+                // all loads of the row and of both centres are issued before any arithmetic
+                float xv[8];
+                double cv[8], rv[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const bool on = i < per_lane;
+                    xv[i] = on ? __ldg(xrow + i * 32 + lane) : 0.f;
+                    cv[i] = on ? __ldg(cc + i * 32 + lane) : 0.0;
+                    rv[i] = on ? __ldg(cr + i * 32 + lane) : 0.0;
+                }
+                double d0 = 0.0, n0 = 0.0, d1 = 0.0, n1 = 0.0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const double xd = (double)xv[i];
+                    d0 = fma(xd, cv[i], d0);
+                    n0 = fma(cv[i], cv[i], n0);
+                    d1 = fma(xd, rv[i], d1);
+                    n1 = fma(rv[i], rv[i], n1);
+                }
+                d0 = warp_sum(d0); n0 = warp_sum(n0); d1 = warp_sum(d1); n1 = warp_sum(n1);
+                s_cur = n0 - 2.0 * d0;
+                s_run = n1 - 2.0 * d1;
+            } else {
+                s_cur = exact_score(xrow, cc, ld, lane);
+                s_run = exact_score(xrow, cr, ld, lane);
+            }
             const bool take = s_run < s_cur || (s_run == s_cur && runner < cur);
             if (lane == 0 && take) labels[row] = runner;
             continue;

@@ -108,6 +108,9 @@ def test_kat_array_input_float_vs_double(m):
     (5000, 3, 2),         # d padded 3 -> 32
     (4097, 33, 17),       # ragged rows, d padded 33 -> 64, k padded 17 -> 32
     (1000, 100, 129),     # k just over one centroid tile
+    (20000, 24, 40),      # one K chunk (odd) in the CTA-pair kernel
+    (9000, 96, 70),       # three K chunks: the last chunk pair is half empty
+    (3000, 160, 50),      # five K chunks
 ])
 def test_fit_parity_blobs(m, n, d, k):
     X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + d + k)
