@@ -155,7 +155,7 @@ __global__ void recheck_kernel(const float *__restrict__ X, const double *__rest
             runner = e.y;
         }
         const float *xrow = X + row * ld;
-        if (runner >= 0) {
+        if (runner != -1) {   // (-1 cannot be a packed pair: winner != runner)
             // entry.y = (winner << 16) | runner-up, both chosen by the tensor-core epilogue
             const int cur = (runner >> 16) & 0xffff;
             runner &= 0xffff;
