@@ -225,37 +225,52 @@ __global__ void recheck_kernel(const float *__restrict__ X, const double *__rest
     }
 }
 
-// Full re-score of the rows listed at the BACK of flag_list (entries cap-1, cap-2, ...): one CTA of 8
-// warps per row, warp w scores centres w, w+8, ... in FP64, then the 8 partial winners are merged
-// (lower score first, equal scores -> lower index).
+// Full re-score of the rows listed at the BACK of flag_list (entries cap-1, cap-2, ...): a CTA of 8
+// warps takes 8 rows, one per warp, and all warps walk the k centres in the same order, so a centre
+// row fetched from L2 by one warp is an L1 hit for the other seven (k*ld*8 bytes per row would
+// otherwise come from L2 for every single row).  FP64, first minimum wins.
 __global__ void __launch_bounds__(256)
 recheck_full_kernel(const float *__restrict__ X, const double *__restrict__ cent, const int2 *__restrict__ list,
                     const int32_t *__restrict__ full_count, int32_t list_cap, int k, int ld,
                     int32_t *__restrict__ labels) {
-    __shared__ double s_best[8];
-    __shared__ int s_idx[8];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     int count = *full_count;
     if (count > list_cap) count = list_cap;
-    for (int e = blockIdx.x; e < count; e += gridDim.x) {
+    const int per_lane = ld >> 5;
+    for (int e0 = blockIdx.x * 8; e0 < count; e0 += gridDim.x * 8) {
+        const int e = e0 + w;
+        if (e >= count) continue;
         const int row = list[list_cap - 1 - e].x;
         const float *xrow = X + (size_t)row * ld;
         double best = INFINITY;
-        int bidx = 0x7fffffff;
-        for (int j = w; j < k; j += 8) {
-            const double sc = exact_score(xrow, cent + (size_t)j * ld, ld, lane);
-            if (sc < best) { best = sc; bidx = j; }
+        int bidx = 0;
+        if (per_lane <= 8) {
+            double xr[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xr[i] = i < per_lane ? (double)__ldg(xrow + i * 32 + lane) : 0.0;
+            for (int j = 0; j < k; ++j) {
+                const double *cj = cent + (size_t)j * ld;
+                double dot = 0.0, cn = 0.0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (i < per_lane) {
+                        const double c = cj[i * 32 + lane];   // plain load: keep it in L1 for the sibling warps
+                        dot = fma(xr[i], c, dot);
+                        cn = fma(c, c, cn);
+                    }
+                }
+                dot = warp_sum(dot);
+                cn = warp_sum(cn);
+                const double sc = cn - 2.0 * dot;
+                if (sc < best) { best = sc; bidx = j; }
+            }
+        } else {
+            for (int j = 0; j < k; ++j) {
+                const double sc = exact_score(xrow, cent + (size_t)j * ld, ld, lane);
+                if (sc < best) { best = sc; bidx = j; }
+            }
         }
-        if (lane == 0) { s_best[w] = best; s_idx[w] = bidx; }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            double b = s_best[0];
-            int bi = s_idx[0];
-            for (int q = 1; q < 8; ++q)
-                if (s_best[q] < b || (s_best[q] == b && s_idx[q] < bi)) { b = s_best[q]; bi = s_idx[q]; }
-            labels[row] = bi;
-        }
-        __syncthreads();
+        if (lane == 0) labels[row] = bidx;
     }
 }
 
