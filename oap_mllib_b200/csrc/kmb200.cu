@@ -56,6 +56,7 @@ static int g_passes = 3;
 static int g_force_simt = 0;
 static int g_knockout = 0;
 static int g_kernel = 2;   // 2 = X-resident / multicast kernel where it applies (ld <= 256), 1 = first-generation kernel
+static int g_rb_cap = 4;   // experiments: cap on the B-ring group slots of the pair kernel
 static int g_corr = 1;     // pair kernel: 1 = BF16 correction MMAs (2 pass-equivalents), 0 = TF32 corrections (3 passes)
 static int g_cluster = 2;  // 2 = CTA pairs (tcgen05 cta_group::2, centroid tiles split across the pair), 1 = single CTAs
 static void env_overrides() {
@@ -587,7 +588,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     using Cfg = PairCfg<BN>;
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
-    const int rb = Cfg::group_slots(kc);
+    const int rb = std::min(Cfg::group_slots(kc), g_rb_cap);
     *applicable = rb >= 2;
     if (rb < 2) return 0;
     const int smem = Cfg::smem_bytes(kc, rb);
@@ -1156,6 +1157,8 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         if (value != 1 && value != 2) return fail(KMB200_ERR_ARG, "kernel must be 1 or 2");
         env_overrides();
         g_kernel = (int)value;
+    } else if (!strcmp(name, "rb_cap")) {
+        g_rb_cap = (int)value;
     } else if (!strcmp(name, "bf16_corr")) {
         g_corr = value != 0;
     } else if (!strcmp(name, "cluster")) {
