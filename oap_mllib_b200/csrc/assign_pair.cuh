@@ -31,7 +31,7 @@ struct PairCfg {
     static constexpr int kBStageBytes = 2 * kBChunkBytes;     // hi + lo
     static constexpr int kAccCol0 = 256;                      // A: 2 group slots x 2 chunks x (32 hi + 32 lo)
     static constexpr int kTmemCols = 512;
-    static constexpr int kNumBars = 8 /*full*/ + 8 /*gdone*/ + 8 /*xfull*/ + 8 /*xempty*/ + 4 + 2 + 2;
+    static constexpr int kNumBars = 8 /*full*/ + 8 /*gdone*/ + 8 /*xfull*/ + 8 /*xempty*/ + 4 /*a_full*/ + 4 /*cdone*/ + 2 + 2;
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16;
     // B ring: RB group slots of two stages each (RB <= 4)
     static int group_slots(int kc) {
@@ -72,8 +72,9 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
     uint64_t *xfull = bars + 16;      // [8]  X chunk landed
     uint64_t *xempty = bars + 24;     // [8]  X chunk read for the last time by the transform
     uint64_t *a_full = bars + 32;     // [4]  chunk c of A slot s written: index 2*s + c (4 local warps; leader: + 1 relayed arrive)
-    uint64_t *acc_full = bars + 36;   // [2]  accumulator tile complete (multicast commit)
-    uint64_t *acc_empty = bars + 38;  // [2]  accumulator drained (4 local warps; leader: + 1 relayed arrive)
+    uint64_t *cdone = bars + 36;      // [4]  MMAs that read chunk c of A slot s have completed (multicast commit)
+    uint64_t *acc_full = bars + 40;   // [2]  accumulator tile complete (multicast commit)
+    uint64_t *acc_empty = bars + 42;  // [2]  accumulator drained (4 local warps; leader: + 1 relayed arrive)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
 
     const int warp = threadIdx.x >> 5;
@@ -91,16 +92,19 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         tma_prefetch_desc(&tm_blo);
     }
     if (warp == 1 && lane == 0) {
-        // leader: its 4 warps + 1 relayed arrive standing for the peer's 4 warps (experiment bit 16: the peer's
-        // 4 warps arrive remotely themselves)
-        const uint32_t group_count = leader ? ((p.knockout & 16) ? 8 : 5) : 4;
+        // leader: its 4 warps + the peer's 4 warps, which arrive remotely (relaxed: their TMEM stores / loads
+        // were already ordered by tcgen05.wait + fence); experiment bit 16: one relayed arrive instead
+        const uint32_t group_count = leader ? ((p.knockout & 16) ? 5 : 8) : 4;
         for (int s = 0; s < 8; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&gdone[s], 1);
             mbar_init(&xfull[s], 1);
             mbar_init(&xempty[s], 4);
         }
-        for (int b = 0; b < 4; ++b) mbar_init(&a_full[b], group_count);   // one transform warpgroup per chunk
+        for (int b = 0; b < 4; ++b) {
+            mbar_init(&a_full[b], group_count);   // one transform warpgroup per chunk
+            mbar_init(&cdone[b], 1);
+        }
         for (int b = 0; b < 2; ++b) {
             mbar_init(&acc_full[b], 1);
             mbar_init(&acc_empty[b], group_count);
@@ -230,8 +234,9 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                                         }
                                     }
                                 }
+                                tc_commit_pair(&cdone[aslot * 2 + c]);   // this chunk's A buffer may be rewritten
                                 if (c == 1) {
-                                    tc_commit_pair(&gdone[grp % P]);                 // ONE cross-CTA signal per group
+                                    tc_commit_pair(&gdone[grp % P]);                 // both B stages of the group are free
                                     if (g == G - 1) tc_commit_pair(&acc_full[ab]);
                                 }
                             }
@@ -248,8 +253,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 p.role_prof[3] = t_issue;
                 p.role_prof[4] = grp;
             }
-        } else if (!(p.knockout & 16)) {
-            // ---- peer CTA: relay "A slot written" to the leader.  The transform warps already ordered
+        } else if (p.knockout & 16) {
+            // ---- (experiment) peer CTA: relay "A slot written" to the leader.  The transform warps already ordered
             // their TMEM stores (tcgen05.wait::st + fence) before the local arrive this warp waits on,
             // so the forwarded arrive carries no data of its own and can be relaxed
             uint32_t grp = 0;
@@ -268,7 +273,7 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                     }
         }
     } else if (warp == 2) {
-        if (!leader && !(p.knockout & 16)) {
+        if (!leader && (p.knockout & 16)) {
             // ---- peer CTA: relay "accumulator drained" to the leader
             uint32_t tile = 0;
             for (int base = base0; base < p.num_row_tiles; base += gridDim.x)
@@ -341,7 +346,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                         }
                         if (prof) { const long long t = clock64(); t_load += t - t_mark; t_mark = t; }
                         if (!waited) {
-                            wait_group_done(grp, 2);   // MMAs that read this A slot have completed
+                            // the MMAs that read this chunk buffer two groups ago have completed
+                            mbar_wait(&cdone[aslot * 2 + mychunk], ((grp >> 1) & 1) ^ 1);
                             tc_fence_after();
                             waited = true;
                         }
@@ -354,14 +360,15 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                         if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
                     }
                     if (prof) t_mark = clock64();
-                    if (!waited) wait_group_done(grp, 2);   // no chunk to convert (odd chunk count): still keep in
-                                                            // step with the MMAs, or the arrive below overruns the barrier
+                    if (!waited)   // no chunk to convert (odd chunk count): still keep in step with the MMAs, or the
+                                   // arrive below overruns the barrier
+                        mbar_wait(&cdone[aslot * 2 + mychunk], ((grp >> 1) & 1) ^ 1);
                     tmem_wait_st();
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) {
-                        if (leader || !(p.knockout & 16)) mbar_arrive(&a_full[aslot * 2 + mychunk]);   // the peer's relay warp forwards it
-                        else mbar_arrive_remote(&a_full[aslot * 2 + mychunk], 0);
+                        if (leader || (p.knockout & 16)) mbar_arrive(&a_full[aslot * 2 + mychunk]);
+                        else mbar_arrive_remote_relaxed(&a_full[aslot * 2 + mychunk], 0);
                     }
                     if (prof) { const long long t = clock64(); t_store += t - t_mark; t_mark = t; }
                 }
@@ -425,8 +432,8 @@ assign_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    if (leader || !(p.knockout & 16)) mbar_arrive(&acc_empty[ab]);
-                    else mbar_arrive_remote(&acc_empty[ab], 0);
+                    if (leader || (p.knockout & 16)) mbar_arrive(&acc_empty[ab]);
+                    else mbar_arrive_remote_relaxed(&acc_empty[ab], 0);
                 }
             }
             // merge sets 1..3 into set 0: lower value first, equal values -> lower index first
