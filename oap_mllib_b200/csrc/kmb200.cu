@@ -20,6 +20,7 @@
 #include "assign_tc.cuh"
 #include "assign_tc2.cuh"
 #include "assign_pair.cuh"
+#include "assign_pair_ss.cuh"
 #include "kernels_misc.cuh"
 
 using namespace kmb;
@@ -56,6 +57,7 @@ static int g_passes = 3;
 static int g_force_simt = 0;
 static int g_knockout = 0;
 static int g_kernel = 2;   // 2 = X-resident / multicast kernel where it applies (ld <= 256), 1 = first-generation kernel
+static int g_ss = 1;       // pair kernel: 1 = main product reads X from shared memory (SS), corrections only in TMEM
 static int g_rb_cap = 4;   // experiments: cap on the B-ring group slots of the pair kernel
 static int g_corr = 1;     // pair kernel: 1 = BF16 correction MMAs (2 pass-equivalents), 0 = TF32 corrections (3 passes)
 static int g_cluster = 2;  // 2 = CTA pairs (tcgen05 cta_group::2, centroid tiles split across the pair), 1 = single CTAs
@@ -582,10 +584,15 @@ static int launch_assign2_bn(kmb200_table *t) {
     return 0;
 }
 
-template <int BN, bool BF16C>
+template <int BN, int V>   // V: 0 = TF32 corrections (3 passes), 1 = BF16 corrections, A in TMEM, 2 = BF16 corrections, main A from smem
 static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
+    constexpr bool BF16C = V != 0;
     Workspace &w = t->ws;
-    using Cfg = PairCfg<BN>;
+    using Cfg = PairCfg<BN>;   // same shared-memory geometry for all variants
+    auto kernel = [] {
+        if constexpr (V == 2) return assign_pair_ss_kernel<BN>;
+        else return assign_pair_kernel<BN, BF16C>;
+    }();
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
     const int rb = std::min(Cfg::group_slots(kc), g_rb_cap);
@@ -593,7 +600,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     if (rb < 2) return 0;
     const int smem = Cfg::smem_bytes(kc, rb);
     if (!attr_set[t->device & 63]) {
-        CU_TRY(cudaFuncSetAttribute(assign_pair_kernel<BN, BF16C>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set[t->device & 63] = true;
     }
     AssignParams p;
@@ -630,7 +637,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    CU_TRY(cudaLaunchKernelEx(&cfg, assign_pair_kernel<BN, BF16C>, w.tm_x, w.tm_bhi_half,
+    CU_TRY(cudaLaunchKernelEx(&cfg, kernel, w.tm_x, w.tm_bhi_half,
                               BF16C ? w.tm_bcorr_half : w.tm_blo_half, p));
     g_prof.kernel_launches++;
     return 0;
@@ -638,9 +645,13 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
 
 static int launch_assign_pair(kmb200_table *t, bool *applicable) {
     switch (t->ws.bn) {
-        case 32: return g_corr ? launch_assign_pair_bn<32, true>(t, applicable) : launch_assign_pair_bn<32, false>(t, applicable);
-        case 64: return g_corr ? launch_assign_pair_bn<64, true>(t, applicable) : launch_assign_pair_bn<64, false>(t, applicable);
-        case 128: return g_corr ? launch_assign_pair_bn<128, true>(t, applicable) : launch_assign_pair_bn<128, false>(t, applicable);
+#define KMB_PAIR(BN_) \
+    return !g_corr ? launch_assign_pair_bn<BN_, 0>(t, applicable) \
+                   : g_ss ? launch_assign_pair_bn<BN_, 2>(t, applicable) : launch_assign_pair_bn<BN_, 1>(t, applicable)
+        case 32: KMB_PAIR(32);
+        case 64: KMB_PAIR(64);
+        case 128: KMB_PAIR(128);
+#undef KMB_PAIR
         default: *applicable = false; return 0;   // pair MMAs need N >= 32
     }
 }
@@ -1157,6 +1168,8 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         if (value != 1 && value != 2) return fail(KMB200_ERR_ARG, "kernel must be 1 or 2");
         env_overrides();
         g_kernel = (int)value;
+    } else if (!strcmp(name, "ss")) {
+        g_ss = value != 0;
     } else if (!strcmp(name, "rb_cap")) {
         g_rb_cap = (int)value;
     } else if (!strcmp(name, "bf16_corr")) {
