@@ -43,8 +43,8 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
 
-    const int RB = p.stages;             // 2..4 group slots in the B ring
-    const int P = (RB == 3) ? 6 : RB == 4 ? 4 : 2;   // lcm(2, RB): period of the gdone ring
+    const int RB = p.stages;             // 2 or 4 group slots in the B ring
+    constexpr int P = 4;                 // period of the gdone ring: covers the B ring (RB) and the 4 A group slots
     const int NT = p.num_col_tiles;
     const int KC = p.num_k_chunks;       // <= 8
     const int G = (KC + 1) >> 1;         // groups (chunk pairs) per centroid tile
@@ -59,7 +59,7 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
     uint64_t *xfull = bars + 16;      // [8]  X chunk landed
     uint64_t *xempty = bars + 24;     // [8]  X chunk read for the last time by the transform
     uint64_t *a_full = bars + 32;     // [8]  correction chunk buffer written (leader: its 4 warps + the peer's 4 warps)
-    uint64_t *cdone = bars + 40;      // [8]  MMAs that read the chunk buffer have completed (multicast commit)
+    // (bars + 40 .. 47 unused)
     uint64_t *acc_full = bars + 48;   // [2]  accumulator tile complete (multicast commit)
     uint64_t *acc_empty = bars + 50;  // [2]  accumulator drained (leader: its 4 warps + the peer's 4 warps)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
@@ -88,10 +88,7 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
             mbar_init(&xfull[s], 1);
             mbar_init(&xempty[s], 5);   // the 4 transform warps that read the chunk + the commit of the MMAs that read it
         }
-        for (int b = 0; b < 8; ++b) {
-            mbar_init(&a_full[b], group_count);   // one transform warpgroup per chunk
-            mbar_init(&cdone[b], 1);
-        }
+        for (int b = 0; b < 8; ++b) mbar_init(&a_full[b], group_count);   // one transform warpgroup per chunk
         for (int b = 0; b < 2; ++b) {
             mbar_init(&acc_full[b], 1);
             mbar_init(&acc_empty[b], group_count);
@@ -106,7 +103,7 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    // "group g - D has completed" on the gdone ring (D = 2 for the A slot, RB for the B slot)
+    // "group g - D has completed" on the gdone ring (D = 4 for the correction buffers, RB for the B slot)
     auto wait_group_done = [&](uint32_t g, uint32_t D) {
         if (g >= D) {
             const uint32_t q = g - D;
@@ -180,26 +177,20 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
                     for (int g = 0; g < G; ++g, ++grp) {
                         const int nch = (2 * g + 1 < KC) ? 2 : 1;
                         // running chunk index (two per group, the second may be a phantom): buffer n % 8
-                        const uint32_t n0 = grp * 2, b0 = n0 & 7, bp0 = (n0 >> 3) & 1;
-                        const uint32_t b1 = (n0 + 1) & 7, bp1 = ((n0 + 1) >> 3) & 1;
+                        const uint32_t n0 = grp * 2, b0 = n0 & 7, b1 = b0 + 1, bp = (n0 >> 3) & 1;
                         const uint32_t bslot = grp % RB, bph = (grp / RB) & 1;
                         const uint32_t s0 = bslot * 2, s1 = s0 + 1;
-                        // chunk 1's correction operand is only needed after chunk 0's MMAs have been issued
-                        mbar_wait3(&a_full[b0], bp0, &full[s0], bph, &full[s1], bph);
+                        // ONE poll for the whole group: the MMA queue is only a few instructions deep, so
+                        // every cycle this warp spends between two issue bursts is a cycle the tensor pipe idles
+                        mbar_wait4(&a_full[b0], bp, &a_full[b1], bp, &full[s0], bph, &full[s1], bph);
                         if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
                         tc_fence_after();
+                        if (elect_one()) {
 #pragma unroll
-                        for (int c = 0; c < 2; ++c) {
-                            const uint32_t bb = c == 0 ? b0 : b1;
-                            if (c == 1) {
-                                mbar_wait(&a_full[b1], bp1);
-                                if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
-                                tc_fence_after();
-                            }
-                            if (elect_one()) {
-                                const int kc = 2 * g + c;
+                            for (int c = 0; c < 2; ++c) {
                                 if (c < nch) {
-                                    const uint32_t a_corr = tmem_base + bb * 32;
+                                    const int kc = 2 * g + c;
+                                    const uint32_t a_corr = tmem_base + (b0 + c) * 32;
                                     const uint32_t bsm = smem_u32(bs + (s0 + c) * Cfg::kBStageBytes);
                                     const uint64_t dhi = make_kmajor_sw128_desc(bsm);
                                     const uint64_t dco = make_kmajor_sw128_desc(bsm + Cfg::kBChunkBytes);
@@ -216,15 +207,12 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
                                         mma_tf32_ss_pair(d_tmem, dx + static_cast<uint64_t>(ks * 2), dhi + static_cast<uint64_t>(ks * 2), idesc, 1u);
                                     if (nt == NT - 1) tc_commit_pair(&xempty[kc]);   // last MMAs that read this X chunk
                                 }
-                                tc_commit_pair(&cdone[bb]);   // this chunk's correction buffer may be rewritten
-                                if (c == 1) {
-                                    tc_commit_pair(&gdone[grp % P]);                 // both B stages of the group are free
-                                    if (g == G - 1) tc_commit_pair(&acc_full[ab]);
-                                }
                             }
-                            __syncwarp();
-                            if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
+                            tc_commit_pair(&gdone[grp & 3]);   // the group's B stages and correction buffers are free
+                            if (g == G - 1) tc_commit_pair(&acc_full[ab]);
                         }
+                        __syncwarp();
+                        if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
                     }
                 }
             }
@@ -249,7 +237,7 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
             for (int nt = 0; nt < NT; ++nt) {
                 for (int g = 0; g < G; ++g, ++grp) {
                     const int nch = (2 * g + 1 < KC) ? 2 : 1;
-                    const uint32_t n = grp * 2 + mychunk, bb = n & 7, bph = (n >> 3) & 1;   // running chunk index
+                    const uint32_t n = grp * 2 + mychunk, bb = n & 7;   // running chunk index
                     uint32_t corr[32];
                     const int kc = 2 * g + mychunk;
                     if (prof) t_mark = clock64();
@@ -282,9 +270,9 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
                         }
                     }
                     if (prof) { const long long t = clock64(); t_load += t - t_mark; t_mark = t; }
-                    // the MMAs that read this buffer 8 chunks ago have completed (also keeps an idle warpgroup --
-                    // odd chunk count -- in step with the MMAs, or its arrive below would overrun the barrier)
-                    mbar_wait(&cdone[bb], bph ^ 1);
+                    // the MMAs of the group that used this buffer 4 groups ago have completed (also keeps an idle
+                    // warpgroup -- odd chunk count -- in step with the MMAs, or its arrive below would overrun)
+                    wait_group_done(grp, 4);
                     tc_fence_after();
                     if (prof) { const long long t = clock64(); t_wait_a += t - t_mark; t_mark = t; }
                     if (mychunk < nch && !(p.knockout & 2)) tmem_st32(tmem_base + lane_addr + bb * 32, corr);

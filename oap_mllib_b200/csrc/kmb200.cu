@@ -595,7 +595,8 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     }();
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
-    const int rb = std::min(Cfg::group_slots(kc), g_rb_cap);
+    int rb = std::min(Cfg::group_slots(kc), g_rb_cap);
+    if (V == 2 && rb == 3) rb = 2;   // the SS kernel's completion ring has period 4: 2 or 4 group slots
     *applicable = rb >= 2;
     if (rb < 2) return 0;
     const int smem = Cfg::smem_bytes(kc, rb);
