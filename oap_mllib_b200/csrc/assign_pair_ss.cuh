@@ -34,7 +34,8 @@ struct PairSsCfg {
 
 // tm_bhi: FP32 [kpad x ld], tm_blo: the BF16 correction operand [kpad x 2*ld]; boxes of BN/2 rows.
 // p.stages = RB (group slots of the B ring).
-template <int BN>
+// DBG: also dump every score to p.dbg_scores (tests only; costs epilogue instructions).
+template <int BN, bool DBG>
 __global__ void __launch_bounds__(kPairThreads, 1)
 assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_bhi,
                    const __grid_constant__ CUtensorMap tm_blo, const AssignParams p) {
@@ -330,8 +331,10 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
                         for (int i = 0; i < 32; ++i) {
                             const int q = i & (NS - 1);
                             const float sc = __uint_as_float(v[i]) + cn[c0 + i];
-                            if (p.dbg_scores != nullptr && rt * kTileM + r < p.n)
-                                p.dbg_scores[(size_t)(rt * kTileM + r) * p.kpad + nt * BN + c0 + i] = sc;
+                            if constexpr (DBG) {
+                                if (rt * kTileM + r < p.n)
+                                    p.dbg_scores[(size_t)(rt * kTileM + r) * p.kpad + nt * BN + c0 + i] = sc;
+                            }
                             const int j = nt * BN + c0 + i;
                             const bool lt1 = sc < best[q], lt2 = sc < second[q];
                             third[q] = fminf(third[q], fmaxf(sc, second[q]));

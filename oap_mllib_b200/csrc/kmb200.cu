@@ -586,17 +586,18 @@ static int launch_assign2_bn(kmb200_table *t) {
 
 template <int BN, int V>   // V: 0 = TF32 corrections (3 passes), 1 = BF16 corrections, A in TMEM, 2 = BF16 corrections, main A from smem
 static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
-    constexpr bool BF16C = V != 0;
+    constexpr bool BF16C = V != 0;   // V == 3: V == 2 plus the score dump used by kmb200_debug_scores
     Workspace &w = t->ws;
     using Cfg = PairCfg<BN>;   // same shared-memory geometry for all variants
     auto kernel = [] {
-        if constexpr (V == 2) return assign_pair_ss_kernel<BN>;
+        if constexpr (V == 2) return assign_pair_ss_kernel<BN, false>;
+        else if constexpr (V == 3) return assign_pair_ss_kernel<BN, true>;
         else return assign_pair_kernel<BN, BF16C>;
     }();
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
     int rb = std::min(Cfg::group_slots(kc), g_rb_cap);
-    if (V == 2 && rb == 3) rb = 2;   // the SS kernel's completion ring has period 4: 2 or 4 group slots
+    if (V >= 2 && rb == 3) rb = 2;   // the SS kernel's completion ring has period 4: 2 or 4 group slots
     *applicable = rb >= 2;
     if (rb < 2) return 0;
     const int smem = Cfg::smem_bytes(kc, rb);
@@ -648,7 +649,8 @@ static int launch_assign_pair(kmb200_table *t, bool *applicable) {
     switch (t->ws.bn) {
 #define KMB_PAIR(BN_) \
     return !g_corr ? launch_assign_pair_bn<BN_, 0>(t, applicable) \
-                   : g_ss ? launch_assign_pair_bn<BN_, 2>(t, applicable) : launch_assign_pair_bn<BN_, 1>(t, applicable)
+                   : !g_ss ? launch_assign_pair_bn<BN_, 1>(t, applicable) \
+                   : g_dbg_scores ? launch_assign_pair_bn<BN_, 3>(t, applicable) : launch_assign_pair_bn<BN_, 2>(t, applicable)
         case 32: KMB_PAIR(32);
         case 64: KMB_PAIR(64);
         case 128: KMB_PAIR(128);
