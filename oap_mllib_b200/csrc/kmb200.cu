@@ -324,6 +324,10 @@ static int append_rows(kmb200_table *t, int64_t row0, const T *rows, int64_t nro
     if (sizeof(T) == sizeof(float)) {
         // FP32 input lands directly in the table (strided copy when the row is padded)
         const int64_t max_h = 1 << 20;
+        if (t->ld == t->d) {
+            CU_TRY(cudaMemcpyAsync(t->X + row0 * t->ld, rows, (size_t)nrows * t->d * sizeof(float), cudaMemcpyHostToDevice,
+                                   t->stream));
+        } else
         for (int64_t r = 0; r < nrows; r += max_h) {
             const int64_t h = std::min(max_h, nrows - r);
             CU_TRY(cudaMemcpy2DAsync(t->X + (row0 + r) * t->ld, (size_t)t->ld * 4, rows + r * t->d, (size_t)t->d * 4,
