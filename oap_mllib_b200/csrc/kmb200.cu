@@ -21,6 +21,7 @@
 #include "assign_tc2.cuh"
 #include "assign_pair.cuh"
 #include "assign_pair_ss.cuh"
+#include "fused_smallk.cuh"
 #include "kernels_misc.cuh"
 
 using namespace kmb;
@@ -57,6 +58,7 @@ static int g_passes = 3;
 static int g_force_simt = 0;
 static int g_knockout = 0;
 static int g_kernel = 2;   // 2 = X-resident / multicast kernel where it applies (ld <= 256), 1 = first-generation kernel
+static int g_fused = 1;    // 1 = one-pass CUDA-core kernel when k*ld is small (HBM-bound regime)
 static int g_ss = 1;       // pair kernel: 1 = main product reads X from shared memory (SS), corrections only in TMEM
 static int g_rb_cap = 4;   // experiments: cap on the B-ring group slots of the pair kernel
 static int g_corr = 1;     // pair kernel: 1 = BF16 correction MMAs (2 pass-equivalents), 0 = TF32 corrections (3 passes)
@@ -133,6 +135,8 @@ struct Workspace {
     int32_t *counts = nullptr, *offsets = nullptr, *cursor = nullptr, *chunk_off = nullptr;
     double *part = nullptr, *cpart = nullptr, *red = nullptr, *costj = nullptr;
     int32_t *flags = nullptr;      // [0] centres that moved > tol, [1] empty clusters
+    double *fused_part = nullptr;  // per-CTA partials of the one-pass small-k kernel
+    int fused_ctas = 0;
     int64_t max_chunks = 0;
     CUtensorMap tm_x, tm_bhi, tm_blo;
     CUtensorMap tm_bcorr_half;             // BF16 [kpad x 2*ld], box 64 values (128 bytes) x bn/2 rows
@@ -161,7 +165,7 @@ struct kmb200_table {
 
 static void ws_free(Workspace &w) {
     void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
-                    w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags};
+                    w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (w.host) cudaFreeHost(w.host);
@@ -477,6 +481,8 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(dmalloc(&w.red, (size_t)k * ld + k + 1));
     KM_TRY(dmalloc(&w.costj, (size_t)k));
     KM_TRY(dmalloc(&w.flags, 4));
+    w.fused_ctas = t->num_sms * 2;   // 2 CTAs of 256 threads fit one SM (registers)
+    KM_TRY(dmalloc(&w.fused_part, (size_t)w.fused_ctas * ((size_t)k * ld + k + 1)));
     CU_TRY(cudaMallocHost(reinterpret_cast<void **>(&w.host), sizeof(Workspace::Host)));
     KM_TRY(make_map(&w.tm_x, t->X, (uint64_t)t->rows, ld, kTileM));
     KM_TRY(make_map(&w.tm_bhi, w.bhi, (uint64_t)w.kpad, ld, (uint32_t)w.bn));
@@ -671,6 +677,44 @@ static int launch_assign2(kmb200_table *t) {
         case 64: return launch_assign2_bn<64, CL>(t);
         default: return launch_assign2_bn<128, CL>(t);
     }
+}
+
+static bool fused_applies(const kmb200_table *t) {
+    const Workspace &w = t->ws;
+    return g_fused && !g_force_simt && (t->ld == 32 || t->ld == 64) && (int64_t)w.k * t->ld <= kFusedMaxKLd;
+}
+
+// One read of X: labels, [sums | counts | cost] in w.red.  flag_count[0] receives the number of rows
+// re-scored in FP64 (as a 64-bit counter spanning flag_count[0..1]).
+static int launch_fused(kmb200_table *t) {
+    Workspace &w = t->ws;
+    const int k = w.k, ld = t->ld;
+    const size_t smem = fused_smem_bytes(k, ld);
+    static bool attr_set[64][2] = {{false}};
+    CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
+    const float eps = (float)(g_eps_scale * ldexp((double)ld + 4.0, -24));   // FP32 FMA chain of ld terms
+    auto *counter = reinterpret_cast<unsigned long long *>(w.flag_count);
+    if (ld == 32) {
+        if (!attr_set[t->device & 63][0]) {
+            CU_TRY(cudaFuncSetAttribute(fused_smallk_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            attr_set[t->device & 63][0] = true;
+        }
+        fused_smallk_kernel<32><<<w.fused_ctas, kFusedWarps * 32, smem, t->stream>>>(t->X, w.cent, w.cstats, t->rows, k, eps,
+                                                                                    w.labels, w.fused_part, counter);
+    } else {
+        if (!attr_set[t->device & 63][1]) {
+            CU_TRY(cudaFuncSetAttribute(fused_smallk_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            attr_set[t->device & 63][1] = true;
+        }
+        fused_smallk_kernel<64><<<w.fused_ctas, kFusedWarps * 32, smem, t->stream>>>(t->X, w.cent, w.cstats, t->rows, k, eps,
+                                                                                    w.labels, w.fused_part, counter);
+    }
+    CU_TRY(cudaGetLastError());
+    const int psize1 = k * ld + k + 1;
+    fused_reduce_kernel<<<(psize1 + 255) / 256, 256, 0, t->stream>>>(w.fused_part, w.fused_ctas, psize1, w.red);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches += 2;
+    return 0;
 }
 
 static int launch_split(kmb200_table *t) {
@@ -951,18 +995,28 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
     double cost = 0.0;
     int it = 0;
     bool converged = false;
+    const bool fused = fused_applies(t);
     const int P = g_events.per_iter;
     for (it = 0; it < max_iter && !converged; ++it) {
         const bool timed = it < g_events.cap_iters;
         cudaEvent_t *ev = timed ? &g_events.ev[(size_t)it * P] : nullptr;
         if (timed) CU_TRY(cudaEventRecord(ev[0], st));
-        KM_TRY(launch_assign(t));
-        if (timed) CU_TRY(cudaEventRecord(ev[1], st));
-        KM_TRY(launch_recheck(t));
-        if (timed) CU_TRY(cudaEventRecord(ev[2], st));
-        KM_TRY(launch_bucket(t));
-        if (timed) CU_TRY(cudaEventRecord(ev[3], st));
-        KM_TRY(launch_accumulate(t));
+        if (fused) {
+            KM_TRY(launch_fused(t));   // distances + argmin + sums + cost in one read of X
+            if (timed) {
+                CU_TRY(cudaEventRecord(ev[1], st));
+                CU_TRY(cudaEventRecord(ev[2], st));
+                CU_TRY(cudaEventRecord(ev[3], st));
+            }
+        } else {
+            KM_TRY(launch_assign(t));
+            if (timed) CU_TRY(cudaEventRecord(ev[1], st));
+            KM_TRY(launch_recheck(t));
+            if (timed) CU_TRY(cudaEventRecord(ev[2], st));
+            KM_TRY(launch_bucket(t));
+            if (timed) CU_TRY(cudaEventRecord(ev[3], st));
+            KM_TRY(launch_accumulate(t));
+        }
         if (timed) CU_TRY(cudaEventRecord(ev[4], st));
         KM_TRY(do_allreduce(t, comm));
         if (timed) CU_TRY(cudaEventRecord(ev[5], st));
@@ -982,8 +1036,12 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
         std::swap(w.cent, w.cent2);
         KM_TRY(launch_split(t));  // TF32 split + norms of the new centres for the next assignment
         if (timed) CU_TRY(cudaEventRecord(ev[6], st));
-        g_prof.rechecked_rows += g_force_simt ? 0 : std::min<int64_t>((int64_t)w.host->flag_count + w.host->full_count, t->rows);
-        g_prof.full_rechecks += g_force_simt ? 0 : w.host->full_count;
+        if (fused) {
+            g_prof.rechecked_rows += w.host->flag_count;   // low word of the 64-bit counter (exact below 2^31)
+        } else {
+            g_prof.rechecked_rows += g_force_simt ? 0 : std::min<int64_t>((int64_t)w.host->flag_count + w.host->full_count, t->rows);
+            g_prof.full_rechecks += g_force_simt ? 0 : w.host->full_count;
+        }
         converged = tol >= 0.0 && moved == 0;
     }
     KM_TRY(download_centers(t, out_centers, k, d));
@@ -1025,14 +1083,22 @@ extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *c
     cudaEvent_t *ev = &g_events.ev[0];
     KM_TRY(upload_centers(t, centers, k, d));
     KM_TRY(launch_split(t));
+    const bool fused = fused_applies(t);
     CU_TRY(cudaEventRecord(ev[0], st));
-    KM_TRY(launch_assign(t));
-    CU_TRY(cudaEventRecord(ev[1], st));
-    KM_TRY(launch_recheck(t));
-    CU_TRY(cudaEventRecord(ev[2], st));
-    KM_TRY(launch_bucket(t));
-    CU_TRY(cudaEventRecord(ev[3], st));
-    KM_TRY(launch_accumulate(t));
+    if (fused) {
+        KM_TRY(launch_fused(t));
+        CU_TRY(cudaEventRecord(ev[1], st));
+        CU_TRY(cudaEventRecord(ev[2], st));
+        CU_TRY(cudaEventRecord(ev[3], st));
+    } else {
+        KM_TRY(launch_assign(t));
+        CU_TRY(cudaEventRecord(ev[1], st));
+        KM_TRY(launch_recheck(t));
+        CU_TRY(cudaEventRecord(ev[2], st));
+        KM_TRY(launch_bucket(t));
+        CU_TRY(cudaEventRecord(ev[3], st));
+        KM_TRY(launch_accumulate(t));
+    }
     CU_TRY(cudaEventRecord(ev[4], st));
     KM_TRY(do_allreduce(t, comm));
     CU_TRY(cudaEventRecord(ev[5], st));
@@ -1046,8 +1112,12 @@ extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *c
         for (int j = 0; j < k; ++j) sizes_host[j] = (int64_t)llround(tail[j]);
     if (cost_host) *cost_host = tail[k];
     g_prof.iterations = 1;
-    g_prof.rechecked_rows = g_force_simt ? 0 : std::min<int64_t>((int64_t)w.host->flag_count + w.host->full_count, t->rows);
-    g_prof.full_rechecks = g_force_simt ? 0 : w.host->full_count;
+    if (fused) {
+        g_prof.rechecked_rows = w.host->flag_count;
+    } else {
+        g_prof.rechecked_rows = g_force_simt ? 0 : std::min<int64_t>((int64_t)w.host->flag_count + w.host->full_count, t->rows);
+        g_prof.full_rechecks = g_force_simt ? 0 : w.host->full_count;
+    }
     cudaEventElapsedTime(&g_prof.assign_ms, ev[0], ev[1]);
     cudaEventElapsedTime(&g_prof.recheck_ms, ev[1], ev[2]);
     cudaEventElapsedTime(&g_prof.bucket_ms, ev[2], ev[3]);
@@ -1175,6 +1245,8 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         if (value != 1 && value != 2) return fail(KMB200_ERR_ARG, "kernel must be 1 or 2");
         env_overrides();
         g_kernel = (int)value;
+    } else if (!strcmp(name, "fused")) {
+        g_fused = value != 0;
     } else if (!strcmp(name, "ss")) {
         g_ss = value != 0;
     } else if (!strcmp(name, "rb_cap")) {
