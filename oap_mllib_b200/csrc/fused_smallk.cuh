@@ -21,7 +21,7 @@ constexpr int kFusedWarps = 8;
 constexpr int kFusedMaxKLd = 1024;   // k * ld <= 1024: 8 KB of FP64 partials per warp
 
 __host__ __device__ inline size_t fused_smem_bytes(int k, int ld) {
-    const size_t cen = (size_t)k * ld * 4 + (size_t)k * 4;              // FP32 centres + norms
+    const size_t cen = (size_t)(k + 1) * ld * 4 + (size_t)(k + 4) * 4;  // FP32 centres + norms (padded to even k)
     const size_t tile = (size_t)kFusedWarps * 32 * (ld + 4) * 4;        // per-warp X tile, padded rows
     const size_t part = (size_t)kFusedWarps * ((size_t)k * ld + k) * 8; // per-warp FP64 sums + counts
     return cen + tile + part + 64;
@@ -34,18 +34,20 @@ fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent
                     unsigned long long *__restrict__ recheck_counter) {
     extern __shared__ __align__(16) uint8_t fsm[];
     constexpr int STRIDE = LD + 4;   // floats per tile row (16-byte aligned, spreads the banks)
-    float *c32 = reinterpret_cast<float *>(fsm);                 // [k][LD]
-    float *cn32 = c32 + (size_t)k * LD;                          // [k]
-    float *tiles = cn32 + ((k + 3) & ~3);                        // [warps][32][STRIDE]
+    const int k2 = (k + 1) & ~1;                                 // centre table padded to an even count
+    float *c32 = reinterpret_cast<float *>(fsm);                 // [k2][LD]
+    float *cn32 = c32 + (size_t)k2 * LD;                         // [k2]
+    float *tiles = cn32 + ((k2 + 3) & ~3);                       // [warps][32][STRIDE]
     double *parts = reinterpret_cast<double *>(tiles + (size_t)kFusedWarps * 32 * STRIDE);   // [warps][k*LD + k]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int psize = k * LD + k;
 
-    for (int i = threadIdx.x; i < k * LD; i += blockDim.x) c32[i] = (float)cent[i];
-    for (int j = threadIdx.x; j < k; j += blockDim.x) {
+    for (int i = threadIdx.x; i < k2 * LD; i += blockDim.x) c32[i] = i < k * LD ? (float)cent[i] : 0.f;
+    for (int j = threadIdx.x; j < k2; j += blockDim.x) {
         double s = 0.0;
-        for (int c = 0; c < LD; ++c) s += cent[(size_t)j * LD + c] * cent[(size_t)j * LD + c];
-        cn32[j] = (float)s;
+        if (j < k)
+            for (int c = 0; c < LD; ++c) s += cent[(size_t)j * LD + c] * cent[(size_t)j * LD + c];
+        cn32[j] = j < k ? (float)s : __int_as_float(0x7f800000);
     }
     double *mypart = parts + (size_t)w * psize;
     for (int i = lane; i < psize; i += 32) mypart[i] = 0.0;
@@ -83,20 +85,28 @@ fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent
         for (int c = 0; c < LD; ++c) xn = fmaf(x[c], x[c], xn);
         float best = __int_as_float(0x7f800000), second = best;
         int bidx = 0;
-        for (int j = 0; j < k; ++j) {
+        // two centres per iteration (four independent packed-FMA chains); c32 / cn32 are padded to an even k
+        for (int j = 0; j < k; j += 2) {
             const float4 *cj = reinterpret_cast<const float4 *>(c32 + (size_t)j * LD);
-            // packed FP32x2 FMAs (sm_100): two independent chains of two lanes each
-            float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
+            const float4 *ck = cj + VPR;
+            float2 a01 = make_float2(0.f, 0.f), a23 = a01, b01 = a01, b23 = a01;
 #pragma unroll
             for (int q = 0; q < VPR; ++q) {
-                const float4 cv = cj[q];   // broadcast
-                a01 = __ffma2_rn(make_float2(x[4 * q], x[4 * q + 1]), make_float2(cv.x, cv.y), a01);
-                a23 = __ffma2_rn(make_float2(x[4 * q + 2], x[4 * q + 3]), make_float2(cv.z, cv.w), a23);
+                const float4 cv = cj[q], dv = ck[q];   // broadcasts
+                const float2 x01 = make_float2(x[4 * q], x[4 * q + 1]), x23 = make_float2(x[4 * q + 2], x[4 * q + 3]);
+                a01 = __ffma2_rn(x01, make_float2(cv.x, cv.y), a01);
+                a23 = __ffma2_rn(x23, make_float2(cv.z, cv.w), a23);
+                b01 = __ffma2_rn(x01, make_float2(dv.x, dv.y), b01);
+                b23 = __ffma2_rn(x23, make_float2(dv.z, dv.w), b23);
             }
-            const float sc = fmaf(-2.0f, (a01.x + a01.y) + (a23.x + a23.y), cn32[j]);
-            second = fminf(second, fmaxf(sc, best));
-            if (sc < best) bidx = j;   // strict: lowest index wins ties
-            best = fminf(best, sc);
+            const float s0 = fmaf(-2.0f, (a01.x + a01.y) + (a23.x + a23.y), cn32[j]);
+            const float s1 = fmaf(-2.0f, (b01.x + b01.y) + (b23.x + b23.y), cn32[j + 1]);   // +inf norm for a padding centre
+            second = fminf(second, fmaxf(s0, best));
+            if (s0 < best) bidx = j;       // strict: lowest index wins ties
+            best = fminf(best, s0);
+            second = fminf(second, fmaxf(s1, best));
+            if (s1 < best) bidx = j + 1;
+            best = fminf(best, s1);
         }
         // ---- 3. near-tie: decide in FP64 over all centres (rare)
         const float bound = 2.0f * eps * (2.0f * sqrtf(xn) * cmax + cmax * cmax);
@@ -131,13 +141,25 @@ fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent
             cost += (double)d0 + (double)d1;
             labels[row0 + lane] = bidx;
         }
-        // ---- 5. accumulate: lanes own columns, rows are visited one after another (no conflicts)
-        for (int r = 0; r < nrows; ++r) {
-            const int l = __shfl_sync(0xffffffffu, bidx, r);
+        // ---- 5. accumulate: lanes own columns; rows with the same label are summed in registers first, so the
+        //         shared-memory partial of a cluster is updated once per batch, not once per row
+        unsigned remaining = nrows == 32 ? 0xffffffffu : ((1u << nrows) - 1u);
+        while (remaining) {
+            const int r0 = __ffs(remaining) - 1;
+            const int l = __shfl_sync(0xffffffffu, bidx, r0);
+            unsigned grp = __ballot_sync(0xffffffffu, bidx == l) & remaining;
+            remaining &= ~grp;
             double *dst = mypart + (size_t)l * LD;
-#pragma unroll
-            for (int c = lane; c < LD; c += 32) dst[c] += (double)tile[r * STRIDE + c];
-            if (lane == 0) mypart[(size_t)k * LD + l] += 1.0;
+            if (lane == 0) mypart[(size_t)k * LD + l] += (double)__popc(grp);
+            double s0 = 0.0, s1 = 0.0;
+            while (grp) {
+                const int r = __ffs(grp) - 1;
+                grp &= grp - 1;
+                s0 += (double)tile[r * STRIDE + lane];
+                if (LD > 32) s1 += (double)tile[r * STRIDE + 32 + lane];
+            }
+            dst[lane] += s0;
+            if (LD > 32) dst[32 + lane] += s1;
         }
         __syncwarp();
     }

@@ -188,6 +188,27 @@ def test_force_simt_path_agrees(m):
     assert abs(a[1] - b[1]) <= 1e-9 * b[1]
 
 
+@pytest.mark.parametrize("options", [
+    {"kernel": 1},                        # first-generation streaming kernel (the only one for d > 256)
+    {"cluster": 1},                       # single-CTA resident-X kernel
+    {"bf16_corr": 0},                     # CTA pairs, plain 3xTF32
+    {"ss": 0},                            # CTA pairs, BF16 corrections, A operand entirely in TMEM
+    {"fused": 0},                         # tensor-core path even where the one-pass small-k kernel applies
+])
+def test_every_kernel_variant_keeps_parity(m, options):
+    """The dispatcher picks one kernel per shape; the others stay selectable and must give the same fit."""
+    cases = [(30000, 256, 300), (50000, 32, 16)] if "fused" in options else [(30000, 256, 300), (9000, 96, 70)]
+    try:
+        for name, val in options.items():
+            m._lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
+        for n, d, k in cases:
+            X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + k)
+            check_fit_parity(m, X, ko.row_init_centers(X, k), tol=1e-4, max_iter=5)
+    finally:
+        for name, val in {"kernel": 2, "cluster": 2, "bf16_corr": 1, "ss": 1, "fused": 1}.items():
+            m._lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
+
+
 def test_empty_cluster_substitution(m):
     X = np.array([[0.0, 0], [1, 0], [0, 1], [10, 10], [11, 10]])
     init = np.array([[0.0, 0], [10, 10], [100, 100]])
