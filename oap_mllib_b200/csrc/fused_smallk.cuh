@@ -18,6 +18,12 @@
 namespace kmb {
 
 constexpr int kFusedWarps = 8;
+// Centres of the current iteration in constant memory (FP32, padded to KP rows; norm = +inf for padding):
+// with the centre loop fully unrolled they become immediate constant-bank operands of the FMAs, so the
+// distance phase touches neither shared memory nor the load/store unit.  Refreshed (device-to-device) by
+// the host wrapper before every launch.
+__constant__ float kc_cent[1024];
+__constant__ float kc_norm[32];
 constexpr int kFusedMaxKLd = 1024;   // k * ld <= 1024: 8 KB of FP64 partials per warp
 
 __host__ __device__ inline size_t fused_smem_bytes(int k, int ld) {
@@ -27,14 +33,14 @@ __host__ __device__ inline size_t fused_smem_bytes(int k, int ld) {
     return cen + tile + part + 64;
 }
 
-template <int LD>
+template <int LD, int KP>
 __global__ void __launch_bounds__(kFusedWarps * 32)
 fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent, const float *__restrict__ cstats,
                     int64_t n, int k, float eps, int32_t *__restrict__ labels, double *__restrict__ cta_part,
                     unsigned long long *__restrict__ recheck_counter) {
     extern __shared__ __align__(16) uint8_t fsm[];
     constexpr int STRIDE = LD + 4;   // floats per tile row (16-byte aligned, spreads the banks)
-    const int k2 = (k + 1) & ~1;                                 // centre table padded to an even count
+    const int k2 = k;
     float *c32 = reinterpret_cast<float *>(fsm);                 // [k2][LD]
     float *cn32 = c32 + (size_t)k2 * LD;                         // [k2]
     float *tiles = cn32 + ((k2 + 3) & ~3);                       // [warps][32][STRIDE]
@@ -85,28 +91,21 @@ fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent
         for (int c = 0; c < LD; ++c) xn = fmaf(x[c], x[c], xn);
         float best = __int_as_float(0x7f800000), second = best;
         int bidx = 0;
-        // two centres per iteration (four independent packed-FMA chains); c32 / cn32 are padded to an even k
-        for (int j = 0; j < k; j += 2) {
-            const float4 *cj = reinterpret_cast<const float4 *>(c32 + (size_t)j * LD);
-            const float4 *ck = cj + VPR;
-            float2 a01 = make_float2(0.f, 0.f), a23 = a01, b01 = a01, b23 = a01;
+        // fully unrolled over the KP padded centres: every kc_cent[...] below is an immediate constant operand
 #pragma unroll
-            for (int q = 0; q < VPR; ++q) {
-                const float4 cv = cj[q], dv = ck[q];   // broadcasts
-                const float2 x01 = make_float2(x[4 * q], x[4 * q + 1]), x23 = make_float2(x[4 * q + 2], x[4 * q + 3]);
-                a01 = __ffma2_rn(x01, make_float2(cv.x, cv.y), a01);
-                a23 = __ffma2_rn(x23, make_float2(cv.z, cv.w), a23);
-                b01 = __ffma2_rn(x01, make_float2(dv.x, dv.y), b01);
-                b23 = __ffma2_rn(x23, make_float2(dv.z, dv.w), b23);
+        for (int j = 0; j < KP; ++j) {
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int c = 0; c < LD; c += 4) {
+                a0 = fmaf(x[c], kc_cent[j * LD + c], a0);
+                a1 = fmaf(x[c + 1], kc_cent[j * LD + c + 1], a1);
+                a2 = fmaf(x[c + 2], kc_cent[j * LD + c + 2], a2);
+                a3 = fmaf(x[c + 3], kc_cent[j * LD + c + 3], a3);
             }
-            const float s0 = fmaf(-2.0f, (a01.x + a01.y) + (a23.x + a23.y), cn32[j]);
-            const float s1 = fmaf(-2.0f, (b01.x + b01.y) + (b23.x + b23.y), cn32[j + 1]);   // +inf norm for a padding centre
-            second = fminf(second, fmaxf(s0, best));
-            if (s0 < best) bidx = j;       // strict: lowest index wins ties
-            best = fminf(best, s0);
-            second = fminf(second, fmaxf(s1, best));
-            if (s1 < best) bidx = j + 1;
-            best = fminf(best, s1);
+            const float sc = fmaf(-2.0f, (a0 + a1) + (a2 + a3), kc_norm[j]);   // +inf norm for a padding centre
+            second = fminf(second, fmaxf(sc, best));
+            if (sc < best) bidx = j;       // strict: lowest index wins ties
+            best = fminf(best, sc);
         }
         // ---- 3. near-tie: decide in FP64 over all centres (rare)
         const float bound = 2.0f * eps * (2.0f * sqrtf(xn) * cmax + cmax * cmax);
@@ -128,19 +127,8 @@ fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent
             bidx = di;
             ++rechecked;
         }
-        // ---- 4. direct-form cost of the row against its centre (FP32 differences, FP64 sum)
-        if (lane < nrows) {
-            const float *cl = c32 + (size_t)bidx * LD;
-            float d0 = 0.f, d1 = 0.f;
-#pragma unroll
-            for (int c = 0; c < LD; c += 2) {
-                const float e0 = x[c] - cl[c], e1 = x[c + 1] - cl[c + 1];
-                d0 = fmaf(e0, e0, d0);
-                d1 = fmaf(e1, e1, d1);
-            }
-            cost += (double)d0 + (double)d1;
-            labels[row0 + lane] = bidx;
-        }
+        // ---- 4. label store (coalesced)
+        if (lane < nrows) labels[row0 + lane] = bidx;
         // ---- 5. accumulate: lanes own columns; rows with the same label are summed in registers first, so the
         //         shared-memory partial of a cluster is updated once per batch, not once per row
         unsigned remaining = nrows == 32 ? 0xffffffffu : ((1u << nrows) - 1u);
@@ -151,15 +139,26 @@ fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent
             remaining &= ~grp;
             double *dst = mypart + (size_t)l * LD;
             if (lane == 0) mypart[(size_t)k * LD + l] += (double)__popc(grp);
+            // lanes own columns: column sums in FP64, direct-form cost (x - c)^2 in FP32 per group of <= 32 rows
+            const float c0 = c32[(size_t)l * LD + lane];
+            const float c1 = LD > 32 ? c32[(size_t)l * LD + 32 + lane] : 0.f;
             double s0 = 0.0, s1 = 0.0;
+            float q0 = 0.f, q1 = 0.f;
             while (grp) {
                 const int r = __ffs(grp) - 1;
                 grp &= grp - 1;
-                s0 += (double)tile[r * STRIDE + lane];
-                if (LD > 32) s1 += (double)tile[r * STRIDE + 32 + lane];
+                const float v0 = tile[r * STRIDE + lane];
+                s0 += (double)v0;
+                q0 = fmaf(v0 - c0, v0 - c0, q0);
+                if (LD > 32) {
+                    const float v1 = tile[r * STRIDE + 32 + lane];
+                    s1 += (double)v1;
+                    q1 = fmaf(v1 - c1, v1 - c1, q1);
+                }
             }
             dst[lane] += s0;
             if (LD > 32) dst[32 + lane] += s1;
+            cost += (double)q0 + (double)q1;
         }
         __syncwarp();
     }

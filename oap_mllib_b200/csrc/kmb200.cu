@@ -679,41 +679,62 @@ static int launch_assign2(kmb200_table *t) {
     }
 }
 
+static int fused_kp(int k) { return k <= 8 ? 8 : k <= 16 ? 16 : 32; }
 static bool fused_applies(const kmb200_table *t) {
     const Workspace &w = t->ws;
-    return g_fused && !g_force_simt && (t->ld == 32 || t->ld == 64) && (int64_t)w.k * t->ld <= kFusedMaxKLd;
+    return g_fused && !g_force_simt && (t->ld == 32 || t->ld == 64) && w.k <= 32 &&
+           (int64_t)fused_kp(w.k) * t->ld <= kFusedMaxKLd;
 }
 
-// One read of X: labels, [sums | counts | cost] in w.red.  flag_count[0] receives the number of rows
-// re-scored in FP64 (as a 64-bit counter spanning flag_count[0..1]).
+// FP32 copy of the centres padded to KP rows (+inf norm for padding), staged in device memory and then
+// copied device-to-device into the kernel's __constant__ tables.
+__global__ void fused_prepare_kernel(const double *__restrict__ cent, int k, int kp, int ld, float *__restrict__ c32,
+                                     float *__restrict__ n32) {
+    for (int i = threadIdx.x; i < kp * ld; i += blockDim.x) c32[i] = i < k * ld ? (float)cent[i] : 0.f;
+    for (int j = threadIdx.x; j < 32; j += blockDim.x) {
+        double s = 0.0;
+        if (j < k)
+            for (int c = 0; c < ld; ++c) s += cent[(size_t)j * ld + c] * cent[(size_t)j * ld + c];
+        n32[j] = j < k ? (float)s : __int_as_float(0x7f800000);
+    }
+}
+
+template <int LD, int KP>
+static int launch_fused_inst(kmb200_table *t, float eps) {
+    Workspace &w = t->ws;
+    static bool attr_set[64] = {false};
+    if (!attr_set[t->device & 63]) {
+        CU_TRY(cudaFuncSetAttribute(fused_smallk_kernel<LD, KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set[t->device & 63] = true;
+    }
+    auto *counter = reinterpret_cast<unsigned long long *>(w.flag_count);
+    fused_smallk_kernel<LD, KP><<<w.fused_ctas, kFusedWarps * 32, fused_smem_bytes(w.k, LD), t->stream>>>(
+        t->X, w.cent, w.cstats, t->rows, w.k, eps, w.labels, w.fused_part, counter);
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+
+// One read of X: labels, [sums | counts | cost] in w.red.  flag_count[0..1] holds (as one 64-bit counter) the
+// number of rows re-scored in FP64.
 static int launch_fused(kmb200_table *t) {
     Workspace &w = t->ws;
-    const int k = w.k, ld = t->ld;
-    const size_t smem = fused_smem_bytes(k, ld);
-    static bool attr_set[64][2] = {{false}};
+    const int k = w.k, ld = t->ld, kp = fused_kp(k);
     CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
     const float eps = (float)(g_eps_scale * ldexp((double)ld + 4.0, -24));   // FP32 FMA chain of ld terms
-    auto *counter = reinterpret_cast<unsigned long long *>(w.flag_count);
-    if (ld == 32) {
-        if (!attr_set[t->device & 63][0]) {
-            CU_TRY(cudaFuncSetAttribute(fused_smallk_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            attr_set[t->device & 63][0] = true;
-        }
-        fused_smallk_kernel<32><<<w.fused_ctas, kFusedWarps * 32, smem, t->stream>>>(t->X, w.cent, w.cstats, t->rows, k, eps,
-                                                                                    w.labels, w.fused_part, counter);
-    } else {
-        if (!attr_set[t->device & 63][1]) {
-            CU_TRY(cudaFuncSetAttribute(fused_smallk_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            attr_set[t->device & 63][1] = true;
-        }
-        fused_smallk_kernel<64><<<w.fused_ctas, kFusedWarps * 32, smem, t->stream>>>(t->X, w.cent, w.cstats, t->rows, k, eps,
-                                                                                    w.labels, w.fused_part, counter);
-    }
+    // stage FP32 centres in the (otherwise unused here) bhi buffer, then refresh the constant tables
+    float *stage_c = w.bhi, *stage_n = w.cnorm;
+    fused_prepare_kernel<<<1, 256, 0, t->stream>>>(w.cent, k, kp, ld, stage_c, stage_n);
     CU_TRY(cudaGetLastError());
+    CU_TRY(cudaMemcpyToSymbolAsync(kc_cent, stage_c, (size_t)kp * ld * sizeof(float), 0, cudaMemcpyDeviceToDevice, t->stream));
+    CU_TRY(cudaMemcpyToSymbolAsync(kc_norm, stage_n, 32 * sizeof(float), 0, cudaMemcpyDeviceToDevice, t->stream));
+    int rc = 0;
+    if (ld == 32) rc = kp == 8 ? launch_fused_inst<32, 8>(t, eps) : kp == 16 ? launch_fused_inst<32, 16>(t, eps) : launch_fused_inst<32, 32>(t, eps);
+    else rc = kp == 8 ? launch_fused_inst<64, 8>(t, eps) : launch_fused_inst<64, 16>(t, eps);
+    KM_TRY(rc);
     const int psize1 = k * ld + k + 1;
     fused_reduce_kernel<<<(psize1 + 255) / 256, 256, 0, t->stream>>>(w.fused_part, w.fused_ctas, psize1, w.red);
     CU_TRY(cudaGetLastError());
-    g_prof.kernel_launches += 2;
+    g_prof.kernel_launches += 3;
     return 0;
 }
 
