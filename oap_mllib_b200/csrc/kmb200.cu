@@ -136,6 +136,7 @@ struct Workspace {
     double *part = nullptr, *cpart = nullptr, *red = nullptr, *costj = nullptr;
     int32_t *flags = nullptr;      // [0] centres that moved > tol, [1] empty clusters
     double *fused_part = nullptr;  // per-CTA partials of the one-pass small-k kernel
+    float *fused_stage = nullptr;  // FP32 centres (1024) + norms (32) on their way to constant memory
     int fused_ctas = 0;
     int64_t max_chunks = 0;
     CUtensorMap tm_x, tm_bhi, tm_blo;
@@ -165,7 +166,7 @@ struct kmb200_table {
 
 static void ws_free(Workspace &w) {
     void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
-                    w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part};
+                    w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (w.host) cudaFreeHost(w.host);
@@ -483,6 +484,7 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(dmalloc(&w.flags, 4));
     w.fused_ctas = t->num_sms * 2;   // 2 CTAs of 256 threads fit one SM (registers)
     KM_TRY(dmalloc(&w.fused_part, (size_t)w.fused_ctas * ((size_t)k * ld + k + 1)));
+    KM_TRY(dmalloc(&w.fused_stage, 1024 + 32));
     CU_TRY(cudaMallocHost(reinterpret_cast<void **>(&w.host), sizeof(Workspace::Host)));
     KM_TRY(make_map(&w.tm_x, t->X, (uint64_t)t->rows, ld, kTileM));
     KM_TRY(make_map(&w.tm_bhi, w.bhi, (uint64_t)w.kpad, ld, (uint32_t)w.bn));
@@ -721,8 +723,7 @@ static int launch_fused(kmb200_table *t) {
     const int k = w.k, ld = t->ld, kp = fused_kp(k);
     CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
     const float eps = (float)(g_eps_scale * ldexp((double)ld + 4.0, -24));   // FP32 FMA chain of ld terms
-    // stage FP32 centres in the (otherwise unused here) bhi buffer, then refresh the constant tables
-    float *stage_c = w.bhi, *stage_n = w.cnorm;
+    float *stage_c = w.fused_stage, *stage_n = w.fused_stage + 1024;
     fused_prepare_kernel<<<1, 256, 0, t->stream>>>(w.cent, k, kp, ld, stage_c, stage_n);
     CU_TRY(cudaGetLastError());
     CU_TRY(cudaMemcpyToSymbolAsync(kc_cent, stage_c, (size_t)kp * ld * sizeof(float), 0, cudaMemcpyDeviceToDevice, t->stream));
