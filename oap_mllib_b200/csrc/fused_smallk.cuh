@@ -34,7 +34,7 @@ __host__ __device__ inline size_t fused_smem_bytes(int k, int ld) {
 }
 
 template <int LD, int KP>
-__global__ void __launch_bounds__(kFusedWarps * 32, LD == 32 ? 3 : 2)
+__global__ void __launch_bounds__(kFusedWarps * 32)
 fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent, const float *__restrict__ cstats,
                     int64_t n, int k, float eps, int32_t *__restrict__ labels, double *__restrict__ cta_part,
                     unsigned long long *__restrict__ recheck_counter) {

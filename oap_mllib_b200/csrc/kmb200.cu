@@ -482,7 +482,7 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(dmalloc(&w.red, (size_t)k * ld + k + 1));
     KM_TRY(dmalloc(&w.costj, (size_t)k));
     KM_TRY(dmalloc(&w.flags, 4));
-    w.fused_ctas = t->num_sms * (t->ld == 32 ? 3 : 2);   // resident CTAs per SM (registers / shared memory)
+    w.fused_ctas = t->num_sms * 2;   // 2 CTAs of 256 threads fit one SM (registers)
     KM_TRY(dmalloc(&w.fused_part, (size_t)w.fused_ctas * ((size_t)k * ld + k + 1)));
     KM_TRY(dmalloc(&w.fused_stage, 1024 + 32));
     CU_TRY(cudaMallocHost(reinterpret_cast<void **>(&w.host), sizeof(Workspace::Host)));
