@@ -15,6 +15,8 @@
 
 namespace kmb {
 
+constexpr int kPairSsThreads = 640;   // + warps 16-19: second epilogue warpgroup
+
 template <int BN>
 struct PairSsCfg {
     static constexpr int kBRows = BN / 2;                     // centroid rows held by one CTA
@@ -23,7 +25,8 @@ struct PairSsCfg {
     static constexpr int kAccCol0 = 256;                      // A corrections: 8 chunk buffers x 32 columns
     static constexpr int kTmemCols = 512;
     static constexpr int kNumBars = 8 /*full*/ + 8 /*gdone*/ + 8 /*xfull*/ + 8 /*xempty*/ + 8 /*a_full*/ + 8 /*cdone*/ + 2 + 2;
-    static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16;
+    static constexpr int kXchgBytes = 2 * 128 * 5 * 4;         // top-3 sets handed from epilogue warpgroup 1 to 0
+    static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16 + kXchgBytes;
     // B ring: RB group slots of two stages each (RB <= 4)
     static int group_slots(int kc) {
         int s = (227 * 1024 - 1024 - kTailBytes - kc * kXStageBytes) / (2 * kBStageBytes);
@@ -36,7 +39,7 @@ struct PairSsCfg {
 // p.stages = RB (group slots of the B ring).
 // DBG: also dump every score to p.dbg_scores (tests only; costs epilogue instructions).
 template <int BN, bool DBG>
-__global__ void __launch_bounds__(kPairThreads, 1)
+__global__ void __launch_bounds__(kPairSsThreads, 1)
 assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_bhi,
                    const __grid_constant__ CUtensorMap tm_blo, const AssignParams p) {
     using Cfg = PairSsCfg<BN>;
@@ -64,6 +67,7 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
     uint64_t *acc_full = bars + 48;   // [2]  accumulator tile complete (multicast commit)
     uint64_t *acc_empty = bars + 50;  // [2]  accumulator drained (leader: its 4 warps + the peer's 4 warps)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
+    uint32_t *xchg = tmem_slot + 4;   // [2][5][128]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -83,6 +87,7 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
         // leader: its 4 warps + the peer's 4 warps, which arrive remotely (relaxed: their TMEM stores / loads
         // were already ordered by tcgen05.wait + fence); no relay warps in this variant
         const uint32_t group_count = leader ? 8 : 4;
+        const uint32_t drain_count = leader ? 16 : 8;   // two epilogue warpgroups per CTA
         for (int s = 0; s < 8; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&gdone[s], 1);
@@ -92,7 +97,7 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
         for (int b = 0; b < 8; ++b) mbar_init(&a_full[b], group_count);   // one transform warpgroup per chunk
         for (int b = 0; b < 2; ++b) {
             mbar_init(&acc_full[b], 1);
-            mbar_init(&acc_empty[b], group_count);
+            mbar_init(&acc_empty[b], drain_count);
         }
         fence_mbar_init();
     }
@@ -225,7 +230,7 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
                 p.role_prof[4] = grp;
             }
         }
-    } else if ((warp >= 4 && warp < 8) || warp >= 12) {
+    } else if ((warp >= 4 && warp < 8) || (warp >= 12 && warp < 16)) {
         // ================================ transform ===================================
         // two warpgroups: warps 4-7 convert the first chunk of every group, warps 12-15 the second
         const int mychunk = warp >= 12 ? 1 : 0;
@@ -296,13 +301,19 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
             o[2] = t_store;
             o[3] = grp;
         }
-    } else if (warp >= 8 && warp < 12) {
+    } else if ((warp >= 8 && warp < 12) || warp >= 16) {
         // ================================ epilogue ====================================
-        const int r = threadIdx.x - 256;
+        // Two warpgroups: each drains half of the columns of every accumulator tile (the running top-3 update is
+        // a latency-bound chain; one warpgroup alone drained a tile more slowly than the tensor pipe filled it).
+        const int eg = warp >= 16 ? 1 : 0;
+        const int r = threadIdx.x & 127;
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+        constexpr int HALF = BN >= 64 ? BN / 2 : BN;      // columns per warpgroup (BN = 32: warpgroup 1 only syncs)
+        const int col0 = eg * HALF;
+        const bool has_cols = col0 < BN;
         const float cmax = p.cstats[0];
-        uint32_t tile = 0;
-        for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x) {
+        uint32_t tile = 0, rtn = 0;
+        for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x, ++rtn) {
             // Four independent running top-3 sets (columns i mod 4): the update of one set is a serial
             // chain of min/max/select, four chains give the ALU pipe independent work.  Inside a set the
             // columns arrive in ascending order, so strict '<' keeps the lowest index; the sets are
@@ -316,14 +327,14 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
             for (int nt = 0; nt < NT; ++nt, ++tile) {
                 const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
                 float *cn = cn_s + ab * BN;
-                if (r < BN) cn[r] = p.cnorm[nt * BN + r];
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (eg == 0 && r < BN) cn[r] = p.cnorm[nt * BN + r];
+                asm volatile("bar.sync 1, 256;" ::: "memory");   // both epilogue warpgroups
                 mbar_wait(&acc_full[ab], aph);
                 tc_fence_after();
-                if (!(p.knockout & 4)) {
+                if (has_cols && !(p.knockout & 4)) {
                     const uint32_t acc = tmem_base + lane_addr + Cfg::kAccCol0 + ab * BN;
 #pragma unroll 1
-                    for (int c0 = 0; c0 < BN; c0 += 32) {
+                    for (int c0 = col0; c0 < col0 + HALF; c0 += 32) {
                         uint32_t v[32];
                         tmem_ld32(acc + c0, v);
                         tmem_wait_ld();
@@ -366,12 +377,27 @@ assign_pair_ss_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_con
                 insert(second[q], sidx[q], true);
                 insert(third[q], 0, false);   // can only ever become the merged third value
             }
-            const int row = rt * kTileM + r;
-            if (row < p.n && !(p.knockout & 4)) {
-                p.labels[row] = mbi;
-                const float xn = sqrtf(p.xnorm[row]);
-                const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
-                if (ms - mb <= bound) flag_row(p, row, mbi, msi, mt - mb <= bound);
+            // warpgroup 1 hands its set to warpgroup 0 (double-buffered by row-tile parity)
+            uint32_t *xb = xchg + (rtn & 1) * 5 * 128;
+            if (eg == 1) {
+                xb[0 * 128 + r] = __float_as_uint(mb);
+                xb[1 * 128 + r] = __float_as_uint(ms);
+                xb[2 * 128 + r] = __float_as_uint(mt);
+                xb[3 * 128 + r] = (uint32_t)mbi;
+                xb[4 * 128 + r] = (uint32_t)msi;
+            }
+            asm volatile("bar.sync 2, 256;" ::: "memory");
+            if (eg == 0) {
+                insert(__uint_as_float(xb[0 * 128 + r]), (int)xb[3 * 128 + r], true);
+                insert(__uint_as_float(xb[1 * 128 + r]), (int)xb[4 * 128 + r], true);
+                insert(__uint_as_float(xb[2 * 128 + r]), 0, false);
+                const int row = rt * kTileM + r;
+                if (row < p.n && !(p.knockout & 4)) {
+                    p.labels[row] = mbi;
+                    const float xn = sqrtf(p.xnorm[row]);
+                    const float bound = 2.0f * p.eps * (2.0f * xn * cmax + cmax * cmax);
+                    if (ms - mb <= bound) flag_row(p, row, mbi, msi, mt - mb <= bound);
+                }
             }
         }
     }

@@ -14,6 +14,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/kmb200.h"
@@ -600,7 +601,7 @@ template <int BN, int V>   // V: 0 = TF32 corrections (3 passes), 1 = BF16 corre
 static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     constexpr bool BF16C = V != 0;   // V == 3: V == 2 plus the score dump used by kmb200_debug_scores
     Workspace &w = t->ws;
-    using Cfg = PairCfg<BN>;   // same shared-memory geometry for all variants
+    using Cfg = std::conditional_t<(V >= 2), PairSsCfg<BN>, PairCfg<BN>>;
     auto kernel = [] {
         if constexpr (V == 2) return assign_pair_ss_kernel<BN, false>;
         else if constexpr (V == 3) return assign_pair_ss_kernel<BN, true>;
@@ -641,7 +642,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     const int pairs = std::min((p.num_row_tiles + 1) / 2, t->num_sms / 2);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(pairs * 2));
-    cfg.blockDim = dim3(kPairThreads);
+    cfg.blockDim = dim3(V >= 2 ? kPairSsThreads : kPairThreads);
     cfg.dynamicSmemBytes = (size_t)smem;
     cfg.stream = t->stream;
     cudaLaunchAttribute attr[1];
