@@ -111,6 +111,8 @@ def test_kat_array_input_float_vs_double(m):
     (20000, 24, 40),      # one K chunk (odd) in the CTA-pair kernel
     (9000, 96, 70),       # three K chunks: the last chunk pair is half empty
     (3000, 160, 50),      # five K chunks
+    (30000, 32, 13000),   # k beyond the shared-memory histogram limit of the bucketing kernels
+    (4000, 512, 5000),    # C4 shape: d = 512 (first-generation kernel), many centroid tiles
 ])
 def test_fit_parity_blobs(m, n, d, k):
     X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + d + k)
