@@ -766,8 +766,6 @@ static int launch_assign(kmb200_table *t) {
             bool applicable = false;
             const int rc = launch_assign_pair(t, &applicable);
             if (rc != 0 || applicable) return rc;
-        } else if (g_cluster == 3 && row_tiles >= 2) {
-            return launch_assign2<2>(t);   // earlier pair variant with per-chunk commits (experiments)
         }
         return launch_assign2<1>(t);
     }
@@ -1277,7 +1275,7 @@ extern "C" int kmb200_set_option(const char *name, double value) {
     } else if (!strcmp(name, "bf16_corr")) {
         g_corr = value != 0;
     } else if (!strcmp(name, "cluster")) {
-        if (value != 1 && value != 2 && value != 3) return fail(KMB200_ERR_ARG, "cluster must be 1, 2 or 3");
+        if (value != 1 && value != 2) return fail(KMB200_ERR_ARG, "cluster must be 1 or 2");
         env_overrides();
         g_cluster = (int)value;
     } else if (!strcmp(name, "knockout")) {

@@ -281,15 +281,20 @@ class KMeansModel:
             raise RuntimeError("No training summary available for this KMeansModel")
         return self._summary
 
+    def _assign(self, table: Table):
+        labels = np.empty(table.rows, dtype=np.int32)
+        k, d = self._centers.shape
+        sizes = np.empty(k, dtype=np.int64)
+        check(lib().kmb200_assign(table.handle, None, _ptr(self._centers), k, d, _ptr(labels), _ptr(sizes), None))
+        return labels, sizes
+
     def transform(self, data) -> np.ndarray:
         """Cluster index of every row, computed on the GPU (kmb200_assign) instead of the JVM UDF
         pass of KMeans.scala:134-142."""
         own = not isinstance(data, Table)
         table = OneDAL.vectorsToMergedNumericTables(data) if own else data
         try:
-            labels = np.empty(table.rows, dtype=np.int32)
-            k, d = self._centers.shape
-            check(lib().kmb200_assign(table.handle, None, _ptr(self._centers), k, d, _ptr(labels), None, None))
+            labels, _ = self._assign(table)
         finally:
             if own:
                 table.release()
@@ -382,8 +387,7 @@ class KMeans:
             impl = KMeansDALImpl(self.k, self.maxIter, self.tol, self.distanceMeasure, centers, 1, 1)
             parent = impl.train(table)
             model = KMeansModel(parent.clusterCenters, parent.trainingCost, parent.numIter)
-            labels = model.transform(table)
-            sizes = np.bincount(labels, minlength=centers.shape[0])
+            labels, sizes = model._assign(table)     # summary pass on the GPU (labels + cluster sizes)
             model._summary = KMeansSummary(labels, sizes, centers.shape[0], parent.numIter, parent.trainingCost)
         finally:
             table.release()
