@@ -98,6 +98,19 @@ def test_kat_array_input_float_vs_double(m):
     assert abs(c64 - c32) <= kat["expect"]["cost_abs_tol"]
 
 
+def test_committed_oracle_fixtures(m):
+    """GPU fit against the numbers committed in tests/golden/oracle_fixtures.npz (made by
+    tests/golden/make_oracle_fixtures.py), not against a live oracle run."""
+    import os
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "oracle_fixtures.npz"))
+    for i, (n, d, k, seed, iters) in enumerate(fx["cases"].tolist()):
+        X, _, _ = ko.gaussian_blobs(n, d, k, seed=seed)
+        c, cost, it = gpu_fit(m, X, ko.row_init_centers(X, k), tol=1e-4, max_iter=iters)
+        assert it == int(fx[f"iters_{i}"])
+        assert_centers_close(c, fx[f"centers_{i}"], CENTER_RTOL)
+        assert abs(cost - float(fx[f"cost_{i}"])) <= COST_RTOL * float(fx[f"cost_{i}"])
+
+
 # ------------------------------------------------------------------ seeded blobs, scaled-down configs
 @pytest.mark.parametrize("n,d,k", [
     (20000, 16, 10),      # small

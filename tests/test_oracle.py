@@ -112,3 +112,16 @@ def test_multi_rank_merge_equals_single_rank():
     assert a[2] == b[2]
     np.testing.assert_allclose(a[0], b[0], rtol=1e-12)
     assert abs(a[1] - b[1]) <= 1e-10 * a[1]
+
+
+def test_oracle_reproduces_committed_fixtures():
+    """tests/golden/oracle_fixtures.npz pins the oracle: same seeded inputs, same centres / cost / iterations."""
+    import os
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "oracle_fixtures.npz"))
+    for i, (n, d, k, seed, iters) in enumerate(fx["cases"].tolist()):
+        X, _, _ = ko.gaussian_blobs(n, d, k, seed=seed)
+        np.testing.assert_allclose(X.astype(np.float64).sum(0), fx[f"xsum_{i}"], rtol=1e-12)
+        C, cost, it = ko.lloyd(X.astype(np.float64), ko.row_init_centers(X, k), 1e-4, iters)
+        assert it == int(fx[f"iters_{i}"])
+        np.testing.assert_allclose(C, fx[f"centers_{i}"], rtol=1e-10, atol=1e-12)
+        assert abs(cost - float(fx[f"cost_{i}"])) <= 1e-10 * cost
