@@ -125,7 +125,7 @@ def test_committed_oracle_fixtures(m):
     (9000, 96, 70),       # three K chunks: the last chunk pair is half empty
     (3000, 160, 50),      # five K chunks
     (30000, 32, 13000),   # k beyond the shared-memory histogram limit of the bucketing kernels
-    (4000, 512, 5000),    # C4 shape: d = 512 (first-generation kernel), many centroid tiles
+    (10000, 512, 3000),   # C4 shape: d = 512 (first-generation kernel), many centroid tiles
 ])
 def test_fit_parity_blobs(m, n, d, k):
     X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + d + k)
