@@ -72,7 +72,8 @@ __global__ void rownorm_kernel(const float *__restrict__ X, float *__restrict__ 
 // chunk [bf16(x_lo) x 32 | bf16(x) x 32] and sums x_lo.w_hi + x.w_lo.
 __global__ void split_centers_kernel(const double *__restrict__ cent, float *__restrict__ bhi,
                                      float *__restrict__ blo, __nv_bfloat16 *__restrict__ bcorr,
-                                     float *__restrict__ cnorm, float *cstats, int k, int ld) {
+                                     float *__restrict__ cnorm, double *__restrict__ cnorm64, float *cstats, int k,
+                                     int ld) {
     const int j = blockIdx.x;
     __shared__ double red[32];
     double acc = 0.0;
@@ -102,6 +103,7 @@ __global__ void split_centers_kernel(const double *__restrict__ cent, float *__r
     if (threadIdx.x == 0) {
         double s = 0.0;
         for (int w = 0; w < (blockDim.x + 31) / 32; ++w) s += red[w];
+        cnorm64[j] = j < k ? s : INFINITY;   // FP64 norms for the full re-check
         if (j < k) {
             cnorm[j] = (float)s;
             // round the norm up a little so the bound stays an upper bound
@@ -227,16 +229,20 @@ __global__ void recheck_kernel(const float *__restrict__ X, const double *__rest
 
 // Full re-score of the rows listed at the BACK of flag_list (entries cap-1, cap-2, ...): a CTA of 8
 // warps takes 8 rows, one per warp, and all warps walk the k centres in the same order, so a centre
-// row fetched from L2 by one warp is an L1 hit for the other seven (k*ld*8 bytes per row would
-// otherwise come from L2 for every single row).  FP64, first minimum wins.
+// row fetched from L2 by one warp is an L1 hit for the other seven.  FP64 scores ||c||^2 - 2 x.c with
+// the norms precomputed (cn64, padded to a multiple of 4 with +inf); four centres per step: the four
+// per-lane partial dots are reduced together by a folding butterfly (6 shuffles instead of 20).
+// First minimum wins.
 __global__ void __launch_bounds__(256)
-recheck_full_kernel(const float *__restrict__ X, const double *__restrict__ cent, const int2 *__restrict__ list,
-                    const int32_t *__restrict__ full_count, int32_t list_cap, int k, int ld,
-                    int32_t *__restrict__ labels) {
+recheck_full_kernel(const float *__restrict__ X, const double *__restrict__ cent, const double *__restrict__ cn64,
+                    const int2 *__restrict__ list, const int32_t *__restrict__ full_count, int32_t list_cap, int k,
+                    int ld, int32_t *__restrict__ labels) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     int count = *full_count;
     if (count > list_cap) count = list_cap;
     const int per_lane = ld >> 5;
+    const bool b16 = lane & 16, b8 = lane & 8;
+    const int mine = (b16 ? 2 : 0) + (b8 ? 1 : 0);   // which of the four centres this lane ends up holding
     for (int e0 = blockIdx.x * 8; e0 < count; e0 += gridDim.x * 8) {
         const int e = e0 + w;
         if (e >= count) continue;
@@ -244,25 +250,39 @@ recheck_full_kernel(const float *__restrict__ X, const double *__restrict__ cent
         const float *xrow = X + (size_t)row * ld;
         double best = INFINITY;
         int bidx = 0;
-        if (per_lane <= 8) {
-            double xr[8];
+        if (per_lane <= 16) {
+            double xr[16];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) xr[i] = i < per_lane ? (double)__ldg(xrow + i * 32 + lane) : 0.0;
-            for (int j = 0; j < k; ++j) {
-                const double *cj = cent + (size_t)j * ld;
-                double dot = 0.0, cn = 0.0;
+            for (int i = 0; i < 16; ++i) xr[i] = i < per_lane ? (double)__ldg(xrow + i * 32 + lane) : 0.0;
+            for (int j = 0; j < k; j += 4) {
+                double v[4];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    if (i < per_lane) {
-                        const double c = cj[i * 32 + lane];   // plain load: keep it in L1 for the sibling warps
-                        dot = fma(xr[i], c, dot);
-                        cn = fma(c, c, cn);
-                    }
+                for (int q = 0; q < 4; ++q) {
+                    const int jj = min(j + q, k - 1);   // clamp the address; the padded norm (+inf) removes it
+                    const double *cj = cent + (size_t)jj * ld;
+                    double dot = 0.0;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (i < per_lane) dot = fma(xr[i], cj[i * 32 + lane], dot);   // plain loads: keep them in L1
+                    v[q] = dot;
                 }
-                dot = warp_sum(dot);
-                cn = warp_sum(cn);
-                const double sc = cn - 2.0 * dot;
-                if (sc < best) { best = sc; bidx = j; }
+                // fold: lanes with bit 4 clear keep centres 0,1, the others 2,3; then bit 3 picks one of the two
+                double k0 = (b16 ? v[2] : v[0]) + __shfl_xor_sync(0xffffffffu, b16 ? v[0] : v[2], 16);
+                double k1 = (b16 ? v[3] : v[1]) + __shfl_xor_sync(0xffffffffu, b16 ? v[1] : v[3], 16);
+                double t = (b8 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, b8 ? k0 : k1, 8);
+                t += __shfl_xor_sync(0xffffffffu, t, 4);
+                t += __shfl_xor_sync(0xffffffffu, t, 2);
+                t += __shfl_xor_sync(0xffffffffu, t, 1);
+                double sc = cn64[j + mine] - 2.0 * t;   // cn64 is padded with +inf beyond k
+                int si = j + mine;
+                // minimum of the four (lower index wins ties): partners at lane distance 8 and 16
+                double o = __shfl_xor_sync(0xffffffffu, sc, 8);
+                int oi = si ^ 1;
+                if (o < sc || (o == sc && oi < si)) { sc = o; si = oi; }
+                o = __shfl_xor_sync(0xffffffffu, sc, 16);
+                oi = __shfl_xor_sync(0xffffffffu, si, 16);
+                if (o < sc || (o == sc && oi < si)) { sc = o; si = oi; }
+                if (sc < best) { best = sc; bidx = si; }
             }
         } else {
             for (int j = 0; j < k; ++j) {

@@ -130,6 +130,7 @@ struct Workspace {
     double *cent = nullptr;       // [kpad x ld] FP64 master copy of the centres (padding zero)
     double *cent2 = nullptr;      // [kpad x ld] output of finalize; swapped with cent every iteration
     float *bhi = nullptr, *blo = nullptr, *cnorm = nullptr, *cstats = nullptr;
+    double *cnorm64 = nullptr;        // [kpad + 4] FP64 ||c||^2, +inf beyond k (full re-check)
     __nv_bfloat16 *bcorr = nullptr;   // [kpad x 2*ld] BF16 correction operand (see split_centers_kernel)
     int32_t *labels = nullptr, *order = nullptr, *flag_count = nullptr;
     int2 *flag_list = nullptr;    // near-tie rows: (row, runner-up centre or -1)
@@ -166,7 +167,7 @@ struct kmb200_table {
 };
 
 static void ws_free(Workspace &w) {
-    void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
+    void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.cnorm64, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
                     w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -469,6 +470,11 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(dmalloc(&w.blo, (size_t)w.kpad * ld));
     KM_TRY(dmalloc(&w.bcorr, (size_t)w.kpad * ld * 2));
     KM_TRY(dmalloc(&w.cnorm, (size_t)w.kpad));
+    KM_TRY(dmalloc(&w.cnorm64, (size_t)w.kpad + 4));
+    {
+        std::vector<double> inf((size_t)w.kpad + 4, INFINITY);   // the 4 slots past kpad are never rewritten
+        CU_TRY(cudaMemcpy(w.cnorm64, inf.data(), inf.size() * sizeof(double), cudaMemcpyHostToDevice));
+    }
     KM_TRY(dmalloc(&w.cstats, 4));
     KM_TRY(dmalloc(&w.labels, n));
     KM_TRY(dmalloc(&w.order, n));
@@ -743,7 +749,8 @@ static int launch_fused(kmb200_table *t) {
 static int launch_split(kmb200_table *t) {
     Workspace &w = t->ws;
     CU_TRY(cudaMemsetAsync(w.cstats, 0, 4 * sizeof(float), t->stream));
-    split_centers_kernel<<<w.kpad, 128, 0, t->stream>>>(w.cent, w.bhi, w.blo, w.bcorr, w.cnorm, w.cstats, w.k, t->ld);
+    split_centers_kernel<<<w.kpad, 128, 0, t->stream>>>(w.cent, w.bhi, w.blo, w.bcorr, w.cnorm, w.cnorm64, w.cstats,
+                                                        w.k, t->ld);
     CU_TRY(cudaGetLastError());
     g_prof.kernel_launches++;
     return 0;
@@ -783,7 +790,7 @@ static int launch_recheck(kmb200_table *t) {
     recheck_kernel<<<t->num_sms * 4, 256, 0, t->stream>>>(t->X, w.cent, w.flag_list, w.flag_count, (int32_t)t->rows,
                                                          t->rows, w.k, t->ld, w.labels);
     CU_TRY(cudaGetLastError());
-    recheck_full_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, w.cent, w.flag_list, w.flag_count + 1,
+    recheck_full_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, w.cent, w.cnorm64, w.flag_list, w.flag_count + 1,
                                                               (int32_t)t->rows, w.k, t->ld, w.labels);
     CU_TRY(cudaGetLastError());
     g_prof.kernel_launches += 2;
