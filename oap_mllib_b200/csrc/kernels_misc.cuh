@@ -233,28 +233,43 @@ __global__ void recheck_kernel(const float *__restrict__ X, const double *__rest
 // the norms precomputed (cn64, padded to a multiple of 4 with +inf); four centres per step: the four
 // per-lane partial dots are reduced together by a folding butterfly (6 shuffles instead of 20).
 // First minimum wins.
+// When only a few rows are listed (large k*d, e.g. k = 10000, d = 512) the k centres of a row group are split
+// over several CTAs (nsplit, derived from the list length on the device); the partial winners go to a small
+// scratch and recheck_merge_kernel picks the final one.  With many rows nsplit = 1 and labels are written directly.
+constexpr int kRecheckMaxSplit = 64;
+__device__ __forceinline__ int recheck_nsplit(int count, int grid) {
+    const int ngroups = (count + 7) / 8;
+    if (ngroups <= 0) return 1;
+    return max(1, min(kRecheckMaxSplit, grid / ngroups));
+}
+
 __global__ void __launch_bounds__(256)
 recheck_full_kernel(const float *__restrict__ X, const double *__restrict__ cent, const double *__restrict__ cn64,
                     const int2 *__restrict__ list, const int32_t *__restrict__ full_count, int32_t list_cap, int k,
-                    int ld, int32_t *__restrict__ labels) {
+                    int ld, int32_t *__restrict__ labels, double *__restrict__ part_score,
+                    int32_t *__restrict__ part_idx) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     int count = *full_count;
     if (count > list_cap) count = list_cap;
     const int per_lane = ld >> 5;
     const bool b16 = lane & 16, b8 = lane & 8;
     const int mine = (b16 ? 2 : 0) + (b8 ? 1 : 0);   // which of the four centres this lane ends up holding
-    for (int e0 = blockIdx.x * 8; e0 < count; e0 += gridDim.x * 8) {
-        const int e = e0 + w;
+    const int ngroups = (count + 7) / 8;
+    const int nsplit = recheck_nsplit(count, gridDim.x);
+    const int kk = (((k + nsplit - 1) / nsplit) + 3) & ~3;   // centres per split, multiple of 4
+    for (int u = blockIdx.x; u < ngroups * nsplit; u += gridDim.x) {
+        const int e = (u / nsplit) * 8 + w, c = u % nsplit;
         if (e >= count) continue;
         const int row = list[list_cap - 1 - e].x;
         const float *xrow = X + (size_t)row * ld;
+        const int j0 = c * kk, j1 = min(k, j0 + kk);
         double best = INFINITY;
-        int bidx = 0;
+        int bidx = 0x7fffffff;
         if (per_lane <= 16) {
             double xr[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) xr[i] = i < per_lane ? (double)__ldg(xrow + i * 32 + lane) : 0.0;
-            for (int j = 0; j < k; j += 4) {
+            for (int j = j0; j < j1; j += 4) {
                 double v[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -285,12 +300,38 @@ recheck_full_kernel(const float *__restrict__ X, const double *__restrict__ cent
                 if (sc < best) { best = sc; bidx = si; }
             }
         } else {
-            for (int j = 0; j < k; ++j) {
+            for (int j = j0; j < j1; ++j) {
                 const double sc = exact_score(xrow, cent + (size_t)j * ld, ld, lane);
                 if (sc < best) { best = sc; bidx = j; }
             }
         }
-        if (lane == 0) labels[row] = bidx;
+        if (lane == 0) {
+            if (nsplit == 1) {
+                labels[row] = bidx;
+            } else {
+                part_score[(size_t)e * kRecheckMaxSplit + c] = best;
+                part_idx[(size_t)e * kRecheckMaxSplit + c] = bidx;
+            }
+        }
+    }
+}
+
+// grid0 = the grid size recheck_full_kernel was launched with (same nsplit derivation)
+__global__ void recheck_merge_kernel(const int2 *__restrict__ list, const int32_t *__restrict__ full_count,
+                                     int32_t list_cap, int grid0, const double *__restrict__ part_score,
+                                     const int32_t *__restrict__ part_idx, int32_t *__restrict__ labels) {
+    int count = *full_count;
+    if (count > list_cap) count = list_cap;
+    const int nsplit = recheck_nsplit(count, grid0);
+    if (nsplit == 1) return;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < count; e += gridDim.x * blockDim.x) {
+        double b = INFINITY;
+        int bi = 0x7fffffff;
+        for (int c = 0; c < nsplit; ++c) {   // ascending centre ranges: strict '<' keeps the lowest index
+            const double sc = part_score[(size_t)e * kRecheckMaxSplit + c];
+            if (sc < b) { b = sc; bi = part_idx[(size_t)e * kRecheckMaxSplit + c]; }
+        }
+        labels[list[list_cap - 1 - e].x] = bi;
     }
 }
 

@@ -131,6 +131,8 @@ struct Workspace {
     double *cent2 = nullptr;      // [kpad x ld] output of finalize; swapped with cent every iteration
     float *bhi = nullptr, *blo = nullptr, *cnorm = nullptr, *cstats = nullptr;
     double *cnorm64 = nullptr;        // [kpad + 4] FP64 ||c||^2, +inf beyond k (full re-check)
+    double *rc_score = nullptr;       // partial winners of a full re-check split over several CTAs
+    int32_t *rc_idx = nullptr;
     __nv_bfloat16 *bcorr = nullptr;   // [kpad x 2*ld] BF16 correction operand (see split_centers_kernel)
     int32_t *labels = nullptr, *order = nullptr, *flag_count = nullptr;
     int2 *flag_list = nullptr;    // near-tie rows: (row, runner-up centre or -1)
@@ -167,7 +169,7 @@ struct kmb200_table {
 };
 
 static void ws_free(Workspace &w) {
-    void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.cnorm64, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
+    void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.cnorm64, w.rc_score, w.rc_idx, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
                     w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -471,6 +473,8 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(dmalloc(&w.bcorr, (size_t)w.kpad * ld * 2));
     KM_TRY(dmalloc(&w.cnorm, (size_t)w.kpad));
     KM_TRY(dmalloc(&w.cnorm64, (size_t)w.kpad + 4));
+    KM_TRY(dmalloc(&w.rc_score, (size_t)t->num_sms * 8 * 8 * kRecheckMaxSplit));   // nsplit > 1 only below 8 rows per CTA
+    KM_TRY(dmalloc(&w.rc_idx, (size_t)t->num_sms * 8 * 8 * kRecheckMaxSplit));
     {
         std::vector<double> inf((size_t)w.kpad + 4, INFINITY);   // the 4 slots past kpad are never rewritten
         CU_TRY(cudaMemcpy(w.cnorm64, inf.data(), inf.size() * sizeof(double), cudaMemcpyHostToDevice));
@@ -790,10 +794,14 @@ static int launch_recheck(kmb200_table *t) {
     recheck_kernel<<<t->num_sms * 4, 256, 0, t->stream>>>(t->X, w.cent, w.flag_list, w.flag_count, (int32_t)t->rows,
                                                          t->rows, w.k, t->ld, w.labels);
     CU_TRY(cudaGetLastError());
-    recheck_full_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, w.cent, w.cnorm64, w.flag_list, w.flag_count + 1,
-                                                              (int32_t)t->rows, w.k, t->ld, w.labels);
+    const int rgrid = t->num_sms * 8;
+    recheck_full_kernel<<<rgrid, 256, 0, t->stream>>>(t->X, w.cent, w.cnorm64, w.flag_list, w.flag_count + 1,
+                                                     (int32_t)t->rows, w.k, t->ld, w.labels, w.rc_score, w.rc_idx);
     CU_TRY(cudaGetLastError());
-    g_prof.kernel_launches += 2;
+    recheck_merge_kernel<<<8, 256, 0, t->stream>>>(w.flag_list, w.flag_count + 1, (int32_t)t->rows, rgrid, w.rc_score,
+                                                  w.rc_idx, w.labels);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches += 3;
     return 0;
 }
 
