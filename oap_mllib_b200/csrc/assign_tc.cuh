@@ -64,6 +64,7 @@ struct AssignParams {
     int32_t kpad;
     long long *role_prof;  // optional cycle counters of the MMA-issuer warp of CTA 0 (diagnostics), else nullptr
     int32_t knockout;      // debugging only: 1 = no TMA, 2 = no transform work, 4 = no epilogue work (results invalid)
+    float sqrt_ld;         // sqrt(ld) (FP16-split kernel: absolute part of the near-tie bound)
 };
 
 // Near-tie bookkeeping shared by the assign kernels: rows whose winner must be decided in FP64.

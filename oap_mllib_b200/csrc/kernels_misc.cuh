@@ -2,6 +2,7 @@
 // of near-tie rows, label bucketing, per-cluster FP64 accumulation, finalize / convergence, the
 // empty-cluster candidate search and the synthetic-blob generator.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <math.h>
@@ -38,9 +39,10 @@ __global__ void convert_rows_kernel(const T *__restrict__ src, float *__restrict
     }
 }
 
-// ||x_i||^2 for rows [row0, row0 + nrows): G = min(32, ld/4) lanes per row, float4 loads.
-__global__ void rownorm_kernel(const float *__restrict__ X, float *__restrict__ xnorm, int64_t row0, int64_t nrows,
-                               int ld) {
+// ||x_i||^2 for rows [row0, row0 + nrows): G = min(32, ld/4) lanes per row, float4 loads.  Also folds max |x_ij|
+// into *xabs (atomicMax on the bits of a non-negative float).
+__global__ void rownorm_kernel(const float *__restrict__ X, float *__restrict__ xnorm, float *xabs, int64_t row0,
+                               int64_t nrows, int ld) {
     const int vec = ld >> 2;
     const int G = vec < 32 ? vec : 32;  // ld is a multiple of 32 -> vec is a multiple of 8
     const int rows_per_warp = 32 / G;
@@ -48,6 +50,7 @@ __global__ void rownorm_kernel(const float *__restrict__ X, float *__restrict__ 
     const int sub = lane / G, gl = lane % G;
     const int64_t warp_global = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    float amax = 0.f;
     for (int64_t rb = warp_global * rows_per_warp; rb < nrows; rb += nwarps * rows_per_warp) {
         const int64_t r = rb + sub;
         float acc = 0.f;
@@ -56,11 +59,14 @@ __global__ void rownorm_kernel(const float *__restrict__ X, float *__restrict__ 
             for (int v = gl; v < vec; v += G) {
                 const float4 q = __ldg(p + v);
                 acc += q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+                amax = fmaxf(amax, fmaxf(fmaxf(fabsf(q.x), fabsf(q.y)), fmaxf(fabsf(q.z), fabsf(q.w))));
             }
         }
         for (int o = G >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (r < nrows && gl == 0) xnorm[row0 + r] = acc;
     }
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if (lane == 0 && amax > 0.f) atomicMax(reinterpret_cast<int *>(xabs), __float_as_int(amax));
 }
 
 // ------------------------------------------------------------------ centroid preparation
@@ -107,6 +113,73 @@ __global__ void split_centers_kernel(const double *__restrict__ cent, float *__r
         if (j < k) {
             cnorm[j] = (float)s;
             // round the norm up a little so the bound stays an upper bound
+            const float nrm = (float)sqrt(s) * 1.000001f;
+            atomicMax(reinterpret_cast<int *>(cstats), __float_as_int(nrm));
+        } else {
+            cnorm[j] = __int_as_float(0x7f800000);
+        }
+    }
+}
+
+// ---- FP16-split operand (assign_pair_h16.cuh)
+// cstats[1] = max |c_ij| (launch before split16_kernel; cstats zeroed by the caller)
+__global__ void cent_absmax_kernel(const double *__restrict__ cent, int64_t count, float *cstats) {
+    float m = 0.f;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+        m = fmaxf(m, __double2float_ru(fabs(cent[i])));
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(reinterpret_cast<int *>(cstats + 1), __float_as_int(m));
+}
+
+// smallest E (clamped to +-60) with m < 2^E
+__device__ __forceinline__ int pow2_above(float m) {
+    if (!(m > 0.f)) return 0;
+    int e;
+    frexpf(m, &e);   // m = f * 2^e, f in [0.5, 1)
+    return max(-60, min(60, e));
+}
+
+// One CTA per padded centroid row j: b16[j] = [g1 (ld64 values) | g2 (ld64 values)] with g1 + g2 ~= -2 c_j sw in FP16
+// (sw = 2^(14 - Ec), |c| < 2^Ec, so |g| < 2^15), zero beyond ld / k.  Also cnorm, cnorm64, cstats[0] exactly as
+// split_centers_kernel, and (block 0) the scales the assign kernel needs: cstats[2] = 1 / (sx sw), cstats[3] = sx
+// (= 2^(15 - Ex), |x| < 2^Ex), cstats[4] / cstats[5] = the absolute error of one x / -2c element that falls into the
+// FP16 subnormal range (2^-25 in scaled units).
+__global__ void split16_kernel(const double *__restrict__ cent, __half *__restrict__ b16, float *__restrict__ cnorm,
+                               double *__restrict__ cnorm64, float *cstats, const float *__restrict__ xabs, int k,
+                               int ld, int ld64) {
+    const int j = blockIdx.x;
+    __shared__ double red[32];
+    const int Ex = pow2_above(*xabs), Ec = pow2_above(cstats[1]);
+    const int ex = 15 - Ex, ew = 14 - Ec;
+    const double sw = ldexp(1.0, ew);
+    if (j == 0 && threadIdx.x == 0) {
+        cstats[2] = ldexpf(1.f, -(ex + ew));
+        cstats[3] = ldexpf(1.f, ex);
+        cstats[4] = ldexpf(1.f, -25 - ex);
+        cstats[5] = ldexpf(1.f, -25 - ew);
+    }
+    double acc = 0.0;
+    for (int c = threadIdx.x; c < ld64; c += blockDim.x) {
+        __half g1 = __float2half_rn(0.f), g2 = g1;
+        if (j < k && c < ld) {
+            const double v = cent[(size_t)j * ld + c];
+            acc += v * v;
+            const double ws = -2.0 * v * sw;
+            g1 = __double2half(ws);
+            g2 = __double2half(ws - (double)__half2float(g1));
+        }
+        b16[(size_t)j * 2 * ld64 + c] = g1;
+        b16[(size_t)j * 2 * ld64 + ld64 + c] = g2;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < (blockDim.x + 31) / 32; ++w) s += red[w];
+        cnorm64[j] = j < k ? s : INFINITY;
+        if (j < k) {
+            cnorm[j] = (float)s;
             const float nrm = (float)sqrt(s) * 1.000001f;
             atomicMax(reinterpret_cast<int *>(cstats), __float_as_int(nrm));
         } else {

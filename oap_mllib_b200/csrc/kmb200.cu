@@ -22,6 +22,7 @@
 #include "assign_tc2.cuh"
 #include "assign_pair.cuh"
 #include "assign_pair_ss.cuh"
+#include "assign_pair_h16.cuh"
 #include "fused_smallk.cuh"
 #include "kernels_misc.cuh"
 
@@ -61,6 +62,7 @@ static int g_knockout = 0;
 static int g_kernel = 2;   // 2 = X-resident / multicast kernel where it applies (ld <= 256), 1 = first-generation kernel
 static int g_fused = 1;    // 1 = one-pass CUDA-core kernel when k*ld is small (HBM-bound regime)
 static int g_ss = 1;       // pair kernel: 1 = main product reads X from shared memory (SS), corrections only in TMEM
+static int g_h16 = 1;      // 1 = FP16-split pair kernel (assign_pair_h16.cuh) where it applies, 0 = TF32 + BF16 corrections
 static int g_rb_cap = 4;   // experiments: cap on the B-ring group slots of the pair kernel
 static int g_corr = 1;     // pair kernel: 1 = BF16 correction MMAs (2 pass-equivalents), 0 = TF32 corrections (3 passes)
 static int g_cluster = 2;  // 2 = CTA pairs (tcgen05 cta_group::2, centroid tiles split across the pair), 1 = single CTAs
@@ -71,6 +73,7 @@ static void env_overrides() {
     if (const char *e = getenv("KMB200_KERNEL")) g_kernel = atoi(e) == 1 ? 1 : 2;
     if (const char *e = getenv("KMB200_CLUSTER")) g_cluster = atoi(e) == 1 ? 1 : 2;
     if (const char *e = getenv("KMB200_BF16_CORR")) g_corr = atoi(e) != 0;
+    if (const char *e = getenv("KMB200_H16")) g_h16 = atoi(e) != 0;
 }
 static long long *g_role_prof = nullptr;  // device buffer, allocated by option "role_prof"
 static float *g_dbg_scores = nullptr;  // set only inside kmb200_debug_scores
@@ -133,6 +136,7 @@ struct Workspace {
     double *cnorm64 = nullptr;        // [kpad + 4] FP64 ||c||^2, +inf beyond k (full re-check)
     double *rc_score = nullptr;       // partial winners of a full re-check split over several CTAs
     int32_t *rc_idx = nullptr;
+    __half *b16 = nullptr;            // [kpad x 2*ld64] FP16 split of -2c*sw: g1 | g2 (split16_kernel)
     __nv_bfloat16 *bcorr = nullptr;   // [kpad x 2*ld] BF16 correction operand (see split_centers_kernel)
     int32_t *labels = nullptr, *order = nullptr, *flag_count = nullptr;
     int2 *flag_list = nullptr;    // near-tie rows: (row, runner-up centre or -1)
@@ -144,6 +148,7 @@ struct Workspace {
     int fused_ctas = 0;
     int64_t max_chunks = 0;
     CUtensorMap tm_x, tm_bhi, tm_blo;
+    CUtensorMap tm_b16_half;               // FP16 [kpad x 2*ld64], box 64 values (128 bytes) x bn/2 rows
     CUtensorMap tm_bcorr_half;             // BF16 [kpad x 2*ld], box 64 values (128 bytes) x bn/2 rows
     CUtensorMap tm_bhi_half, tm_blo_half;  // boxes of bn/2 rows: each CTA of a pair loads half a centroid tile
     // pinned host mirror read once per iteration
@@ -161,6 +166,7 @@ struct kmb200_table {
     int d = 0, ld = 0;
     float *X = nullptr;
     float *xnorm = nullptr;
+    float *xabs = nullptr;   // [1] max |x_ij| over everything ever appended (scale of the FP16 split)
     void *stage = nullptr;
     size_t stage_bytes = 0;
     cudaStream_t stream = nullptr;
@@ -169,7 +175,7 @@ struct kmb200_table {
 };
 
 static void ws_free(Workspace &w) {
-    void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.cnorm64, w.rc_score, w.rc_idx, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
+    void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.b16, w.cnorm64, w.rc_score, w.rc_idx, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
                     w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -234,7 +240,7 @@ static EncodeTiledFn get_encode_fn() {
     return fn;
 }
 // 2-D BF16 row-major [rows x ld2] tensor, box = 64 values (128 bytes) x box_rows rows, 128-byte swizzle.
-static int make_map_bf16(CUtensorMap *m, const void *base, uint64_t rows, uint64_t ld2, uint32_t box_rows);
+static int make_map_bf16(CUtensorMap *m, const void *base, uint64_t rows, uint64_t ld2, uint32_t box_rows, bool fp16 = false);
 // 2-D FP32 row-major [rows x ld] tensor, box = 32 columns x box_rows rows, 128-byte swizzle.
 static int make_map(CUtensorMap *m, const float *base, uint64_t rows, uint64_t ld, uint32_t box_rows) {
     EncodeTiledFn fn = get_encode_fn();
@@ -250,14 +256,14 @@ static int make_map(CUtensorMap *m, const float *base, uint64_t rows, uint64_t l
     return 0;
 }
 
-static int make_map_bf16(CUtensorMap *m, const void *base, uint64_t rows, uint64_t ld2, uint32_t box_rows) {
+static int make_map_bf16(CUtensorMap *m, const void *base, uint64_t rows, uint64_t ld2, uint32_t box_rows, bool fp16) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) return fail(KMB200_ERR_DEVICE, "cuTensorMapEncodeTiled is not available from the driver");
     cuuint64_t dims[2] = {ld2, rows};
     cuuint64_t strides[1] = {ld2 * 2};
     cuuint32_t box[2] = {64, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+    CUresult r = fn(m, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(KMB200_ERR_DEVICE, "cuTensorMapEncodeTiled(bf16) failed with CUresult %d", (int)r);
@@ -279,6 +285,8 @@ extern "C" int kmb200_table_create(int64_t rows, int32_t cols, kmb200_table **ou
     cudaError_t e = cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc(&t->X, (size_t)rows * t->ld * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc(&t->xnorm, (size_t)rows * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&t->xabs, sizeof(float));
+    if (e == cudaSuccess) e = cudaMemsetAsync(t->xabs, 0, sizeof(float), t->stream);
     if (e == cudaSuccess && t->ld != t->d) e = cudaMemsetAsync(t->X, 0, (size_t)rows * t->ld * sizeof(float), t->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(t->xnorm, 0, (size_t)rows * sizeof(float), t->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
@@ -288,6 +296,7 @@ extern "C" int kmb200_table_create(int64_t rows, int32_t cols, kmb200_table **ou
         cudaGetLastError();
         if (t->X) cudaFree(t->X);
         if (t->xnorm) cudaFree(t->xnorm);
+        if (t->xabs) cudaFree(t->xabs);
         if (t->stream) cudaStreamDestroy(t->stream);
         delete t;
         return code;
@@ -304,6 +313,7 @@ extern "C" int kmb200_table_free(kmb200_table *t) {
     if (t->stage) cudaFree(t->stage);
     cudaFree(t->X);
     cudaFree(t->xnorm);
+    cudaFree(t->xabs);
     cudaStreamDestroy(t->stream);
     delete t;
     return 0;
@@ -316,7 +326,7 @@ static int launch_rownorm(kmb200_table *t, int64_t row0, int64_t nrows) {
     const int64_t warps = (nrows + 3) / 4;
     int blocks = (int)std::min<int64_t>((warps * 32 + 255) / 256, (int64_t)t->num_sms * 16);
     if (blocks < 1) blocks = 1;
-    rownorm_kernel<<<blocks, 256, 0, t->stream>>>(t->X, t->xnorm, row0, nrows, t->ld);
+    rownorm_kernel<<<blocks, 256, 0, t->stream>>>(t->X, t->xnorm, t->xabs, row0, nrows, t->ld);
     CU_TRY(cudaGetLastError());
     return 0;
 }
@@ -448,6 +458,7 @@ extern "C" int kmb200_comm_destroy(kmb200_comm *c) {
 }
 
 // ------------------------------------------------------------------------------------ workspace
+static size_t ld64(int ld) { return (size_t)(ld + 63) / 64 * 64; }
 static int pick_bn(int k) { return k <= 16 ? 16 : k <= 32 ? 32 : k <= 64 ? 64 : 128; }
 
 template <typename T>
@@ -471,6 +482,7 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(dmalloc(&w.bhi, (size_t)w.kpad * ld));
     KM_TRY(dmalloc(&w.blo, (size_t)w.kpad * ld));
     KM_TRY(dmalloc(&w.bcorr, (size_t)w.kpad * ld * 2));
+    KM_TRY(dmalloc(&w.b16, (size_t)w.kpad * ld64(t->ld) * 2));
     KM_TRY(dmalloc(&w.cnorm, (size_t)w.kpad));
     KM_TRY(dmalloc(&w.cnorm64, (size_t)w.kpad + 4));
     KM_TRY(dmalloc(&w.rc_score, (size_t)t->num_sms * 8 * 8 * kRecheckMaxSplit));   // nsplit > 1 only below 8 rows per CTA
@@ -479,7 +491,7 @@ static int ws_prepare(kmb200_table *t, int k) {
         std::vector<double> inf((size_t)w.kpad + 4, INFINITY);   // the 4 slots past kpad are never rewritten
         CU_TRY(cudaMemcpy(w.cnorm64, inf.data(), inf.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
-    KM_TRY(dmalloc(&w.cstats, 4));
+    KM_TRY(dmalloc(&w.cstats, 8));
     KM_TRY(dmalloc(&w.labels, n));
     KM_TRY(dmalloc(&w.order, n));
     KM_TRY(dmalloc(&w.flag_list, n));
@@ -503,6 +515,7 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(make_map(&w.tm_bhi_half, w.bhi, (uint64_t)w.kpad, ld, (uint32_t)std::max(w.bn / 2, 8)));
     KM_TRY(make_map(&w.tm_blo_half, w.blo, (uint64_t)w.kpad, ld, (uint32_t)std::max(w.bn / 2, 8)));
     KM_TRY(make_map_bf16(&w.tm_bcorr_half, w.bcorr, (uint64_t)w.kpad, 2 * ld, (uint32_t)std::max(w.bn / 2, 8)));
+    KM_TRY(make_map_bf16(&w.tm_b16_half, w.b16, (uint64_t)w.kpad, 2 * ld64(t->ld), (uint32_t)std::max(w.bn / 2, 8), true));
     return 0;
 }
 
@@ -668,6 +681,82 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     return 0;
 }
 
+// FP16-split pair kernel (assign_pair_h16.cuh).  The score error: 3*ld/16 accumulator updates (one unit each, as for 3xTF32;
+// measured maximum at ld = 256: 20 x 2^-24 against 80), split residuals 3*2^-22 and dropped h2.g2 2^-22, FP32 norm, final FMA.
+static float score_eps_h16(int ld) { return (float)(g_eps_scale * ldexp(3.0 * ld / 16.0 + 32.0, -24)); }
+
+template <int BN>
+static int h16_stages(const kmb200_table *t) {
+    return std::min(PairH16Cfg<BN>::b_stages(t->ld / kChunkK), 8);
+}
+static bool h16_applies(const kmb200_table *t) {
+    const Workspace &w = t->ws;
+    if (!g_h16 || g_force_simt || g_kernel != 2 || g_passes != 3 || g_cluster != 2 || t->ld > 256 || w.bn < 32) return false;
+    if ((t->rows + kTileM - 1) / kTileM < 2) return false;
+    const int st = w.bn == 32 ? h16_stages<32>(t) : w.bn == 64 ? h16_stages<64>(t) : h16_stages<128>(t);
+    return st >= 2;
+}
+
+template <int BN, bool DBG>
+static int launch_assign_h16_bn(kmb200_table *t) {
+    Workspace &w = t->ws;
+    using Cfg = PairH16Cfg<BN>;
+    auto kernel = assign_pair_h16_kernel<BN, DBG>;
+    static bool attr_set[64] = {false};
+    const int kc = t->ld / kChunkK;
+    const int bs = h16_stages<BN>(t);
+    const int smem = Cfg::smem_bytes(kc, bs);
+    if (!attr_set[t->device & 63]) {
+        CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set[t->device & 63] = true;
+    }
+    AssignParams p;
+    p.cnorm = w.cnorm;
+    p.xnorm = t->xnorm;
+    p.cstats = w.cstats;
+    p.labels = w.labels;
+    p.flag_count = w.flag_count;
+    p.flag_list = w.flag_list;
+    p.flag_cap = (int32_t)t->rows;
+    p.n = (int32_t)t->rows;
+    p.num_row_tiles = (int32_t)((t->rows + kTileM - 1) / kTileM);
+    p.num_col_tiles = w.kpad / BN;
+    p.num_k_chunks = kc;
+    p.stages = bs;
+    p.passes = 3;
+    p.eps = score_eps_h16(t->ld);
+    p.dbg_scores = g_dbg_scores;
+    p.kpad = w.kpad;
+    p.knockout = g_knockout;
+    p.role_prof = g_role_prof;
+    p.sqrt_ld = sqrtf((float)t->ld);
+    const int pairs = std::min((p.num_row_tiles + 1) / 2, t->num_sms / 2);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(pairs * 2));
+    cfg.blockDim = dim3(kPairH16Threads);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = t->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CU_TRY(cudaLaunchKernelEx(&cfg, kernel, w.tm_x, w.tm_b16_half, p));
+    g_prof.kernel_launches++;
+    return 0;
+}
+
+static int launch_assign_h16(kmb200_table *t) {
+    const bool dbg = g_dbg_scores != nullptr;
+    switch (t->ws.bn) {
+        case 32: return dbg ? launch_assign_h16_bn<32, true>(t) : launch_assign_h16_bn<32, false>(t);
+        case 64: return dbg ? launch_assign_h16_bn<64, true>(t) : launch_assign_h16_bn<64, false>(t);
+        default: return dbg ? launch_assign_h16_bn<128, true>(t) : launch_assign_h16_bn<128, false>(t);
+    }
+}
+
 static int launch_assign_pair(kmb200_table *t, bool *applicable) {
     switch (t->ws.bn) {
 #define KMB_PAIR(BN_) \
@@ -752,7 +841,18 @@ static int launch_fused(kmb200_table *t) {
 
 static int launch_split(kmb200_table *t) {
     Workspace &w = t->ws;
-    CU_TRY(cudaMemsetAsync(w.cstats, 0, 4 * sizeof(float), t->stream));
+    CU_TRY(cudaMemsetAsync(w.cstats, 0, 8 * sizeof(float), t->stream));
+    env_overrides();
+    if (h16_applies(t)) {
+        const int64_t count = (int64_t)w.k * t->ld;
+        cent_absmax_kernel<<<(int)std::min<int64_t>((count + 255) / 256, 1024), 256, 0, t->stream>>>(w.cent, count, w.cstats);
+        CU_TRY(cudaGetLastError());
+        split16_kernel<<<w.kpad, 128, 0, t->stream>>>(w.cent, w.b16, w.cnorm, w.cnorm64, w.cstats, t->xabs, w.k, t->ld,
+                                                     (int)ld64(t->ld));
+        CU_TRY(cudaGetLastError());
+        g_prof.kernel_launches += 2;
+        return 0;
+    }
     split_centers_kernel<<<w.kpad, 128, 0, t->stream>>>(w.cent, w.bhi, w.blo, w.bcorr, w.cnorm, w.cnorm64, w.cstats,
                                                         w.k, t->ld);
     CU_TRY(cudaGetLastError());
@@ -771,6 +871,7 @@ static int launch_assign(kmb200_table *t) {
         return 0;
     }
     env_overrides();
+    if (h16_applies(t)) return launch_assign_h16(t);
     if (g_kernel == 2 && g_passes == 3 && t->ld <= 256) {
         const int row_tiles = (int)((t->rows + kTileM - 1) / kTileM);
         if (g_cluster == 2 && row_tiles >= 2) {
@@ -1285,6 +1386,8 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         g_fused = value != 0;
     } else if (!strcmp(name, "ss")) {
         g_ss = value != 0;
+    } else if (!strcmp(name, "h16")) {
+        g_h16 = value != 0;
     } else if (!strcmp(name, "rb_cap")) {
         g_rb_cap = (int)value;
     } else if (!strcmp(name, "bf16_corr")) {

@@ -186,7 +186,20 @@ def test_tensor_core_score_error_is_inside_the_bound(m):
         ld = (d + 31) // 32 * 32
         eps = 2.0 ** -24 * (3.0 * ld / 8.0 + 16.0)   # the 3xTF32 bound; the BF16-correction kernel must also stay inside it
         assert np.all(np.isinf(sc[:, k:])), "padding columns must score +inf"
+        print(f"score error d={d} k={k}: max {err.max() / 2.0 ** -24:.1f} x 2^-24 (3xTF32 bound {eps / 2.0 ** -24:.0f})")
         assert err.max() <= 0.5 * eps, f"d={d}: max normalised error {err.max():.3e} vs bound {eps:.3e}"
+
+
+@pytest.mark.parametrize("scale,colscale", [(3.0e4, None), (1.0e-6, None), (1.0, 1.0e-7), (1.0, 1.0e5)])
+def test_fp16_split_scales_and_wide_column_ranges(m, scale, colscale):
+    """The FP16-split kernel rescales x and c by powers of two; very large / small data and columns many binades
+    below the largest one (FP16 subnormal range after scaling) must still give the FP64 oracle's fit."""
+    n, d, k = 20000, 128, 64
+    X, _, _ = ko.gaussian_blobs(n, d, k, seed=77)
+    X = X * np.float32(scale)
+    if colscale is not None:
+        X[:, ::3] *= np.float32(colscale)
+    check_fit_parity(m, X, ko.row_init_centers(X, k), tol=0.0, max_iter=4)
 
 
 def test_force_simt_path_agrees(m):
@@ -206,8 +219,9 @@ def test_force_simt_path_agrees(m):
 @pytest.mark.parametrize("options", [
     {"kernel": 1},                        # first-generation streaming kernel (the only one for d > 256)
     {"cluster": 1},                       # single-CTA resident-X kernel
-    {"bf16_corr": 0},                     # CTA pairs, plain 3xTF32
-    {"ss": 0},                            # CTA pairs, BF16 corrections, A operand entirely in TMEM
+    {"h16": 0},                           # CTA pairs, TF32 main product from shared memory + BF16 corrections
+    {"h16": 0, "bf16_corr": 0},           # CTA pairs, plain 3xTF32
+    {"h16": 0, "ss": 0},                  # CTA pairs, BF16 corrections, A operand entirely in TMEM
     {"fused": 0},                         # tensor-core path even where the one-pass small-k kernel applies
 ])
 def test_every_kernel_variant_keeps_parity(m, options):
@@ -220,7 +234,7 @@ def test_every_kernel_variant_keeps_parity(m, options):
             X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + k)
             check_fit_parity(m, X, ko.row_init_centers(X, k), tol=1e-4, max_iter=5)
     finally:
-        for name, val in {"kernel": 2, "cluster": 2, "bf16_corr": 1, "ss": 1, "fused": 1}.items():
+        for name, val in {"kernel": 2, "cluster": 2, "bf16_corr": 1, "ss": 1, "fused": 1, "h16": 1}.items():
             m._lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
 
 
