@@ -26,22 +26,35 @@ template <int BN>
 struct PairH16Cfg {
     static constexpr int kBRows = BN / 2;                // centroid rows held by one CTA
     static constexpr int kBHalfBytes = kBRows * 128;     // g1 (or g2) for one chunk of 64 K-values
-    static constexpr int kBStageBytes = 2 * kBHalfBytes; // [g1 | g2]
+    static constexpr int kBUnitBytes = 2 * kBHalfBytes;  // [g1 | g2]
     static constexpr int kA2Col0 = 128;                  // h1 at columns [0, 128), h2 at [128, 256)
     static constexpr int kAccCol0 = 256;
     static constexpr int kTmemCols = 512;
-    static constexpr int kNumBars = 8 /*bfull*/ + 8 /*bempty*/ + 8 /*xfull*/ + 8 /*xempty*/ + 8 /*a_full*/ + 4 /*a_free*/ + 2 + 2;
+    static constexpr int kNumBars = 4 /*bfull*/ + 4 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 8 /*a_full*/ + 2 /*a_free*/ + 2 /*acc_empty*/;
     static constexpr int kXchgBytes = 2 * 128 * 5 * 4;
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16 + kXchgBytes;
-    static int b_stages(int kc) {
-        int s = (227 * 1024 - 1024 - kTailBytes - kc * kXStageBytes) / kBStageBytes;
-        return s > 8 ? 8 : s;
+    static constexpr int kBudget = 227 * 1024 - 1024 - kTailBytes;
+    static int group_bytes(int kc) { return ((kc + 1) / 2) * kBUnitBytes; }   // B operand of one centroid tile
+    // X ring slots (32-value chunks): as many as fit next to two B groups, at most one row tile, at most 8
+    static int x_slots(int kc) {
+        int s = (kBudget - 2 * group_bytes(kc)) / kXStageBytes;
+        return s > kc ? kc : s;
     }
-    static int smem_bytes(int kc, int bs) { return 1024 + kc * kXStageBytes + bs * kBStageBytes + kTailBytes; }
+    static int b_groups(int kc) {
+        int g = (kBudget - x_slots(kc) * kXStageBytes) / group_bytes(kc);
+        return g > 4 ? 4 : g;
+    }
+    static int smem_bytes(int kc) { return 1024 + x_slots(kc) * kXStageBytes + b_groups(kc) * group_bytes(kc) + kTailBytes; }
 };
 
 // tm_b: FP16 [kpad x 2*ld64] (g1 in columns [0, ld64), g2 in [ld64, 2*ld64)), boxes of 64 values x BN/2 rows.
-// p.stages = B ring stages (2..8).  p.cstats: [0] max ||c||, [2] 1/(sx sw), [3] sx, [4]/[5] absolute error units.
+// p.stages = X ring slots | B groups << 8.  p.cstats: [0] max ||c||, [2] 1/(sx sw), [3] sx, [4]/[5] absolute error
+// units.
+//
+// Synchronisation is per CENTROID TILE, not per K chunk: every tcgen05.commit / mbarrier wait pair costs the
+// issuing warp several hundred cycles during which the (shallow) MMA queue drains, so the B operand of a whole
+// centroid tile is one ring entry ("group", 2..4 of them), and ONE commit per tile (tile_done) tells the
+// epilogue that the accumulator is complete and the B producer that the group may be refilled.
 template <int BN, bool DBG>
 __global__ void __launch_bounds__(kPairH16Threads, 1)
 assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_b,
@@ -51,28 +64,33 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
 
-    const int BS = p.stages;
+    const int XS = p.stages & 255, NG = p.stages >> 8;
     const int NT = p.num_col_tiles;
     const int KC = p.num_k_chunks;       // 32-value chunks of X, <= 8
-    const int C64 = (KC + 1) >> 1;       // 64-value chunks of B
+    const int C64 = (KC + 1) >> 1;       // 64-value units of B
+    const int C64a = C64 >> 1;           // units [0, C64a) of A are released early in a row tile's last centroid tile
     const int ld64 = C64 * 64;
-    uint8_t *xs = smem;                                  // [KC][128 rows x 128 B], swizzled
-    uint8_t *bs = smem + KC * kXStageBytes;              // [BS][g1 chunk | g2 chunk] (this CTA's rows)
-    uint8_t *tail = bs + BS * Cfg::kBStageBytes;
+    const int group_bytes = C64 * Cfg::kBUnitBytes;
+    uint8_t *xs = smem;                                  // [XS][128 rows x 128 B], swizzled
+    uint8_t *bs = smem + XS * kXStageBytes;              // [NG][C64][g1 chunk | g2 chunk] (this CTA's rows)
+    uint8_t *tail = bs + NG * group_bytes;
     float *cn_s = reinterpret_cast<float *>(tail);       // [2][BN]
     uint64_t *bars = reinterpret_cast<uint64_t *>(tail + 2 * BN * 4);
-    uint64_t *bfull = bars;           // [8]  (leader) B stage landed in BOTH CTAs
-    uint64_t *bempty = bars + 8;      // [8]  the MMAs that read the stage completed (multicast commit)
-    uint64_t *xfull = bars + 16;      // [8]  X chunk landed
-    uint64_t *xempty = bars + 24;     // [8]  X chunk read by its transform warpgroup
-    uint64_t *a_full = bars + 32;     // [8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
-    uint64_t *a_free = bars + 40;     // [4]  last MMAs of the row tile that read a 64-value chunk completed (multicast)
-    uint64_t *acc_full = bars + 44;   // [2]
-    uint64_t *acc_empty = bars + 46;  // [2]
+    uint64_t *bfull = bars;           // [4]  (leader) B group landed in BOTH CTAs
+    uint64_t *tile_done = bars + 4;   // [4]  all MMAs of a centroid tile completed (multicast commit), ring over tiles
+    uint64_t *xfull = bars + 8;       // [8]  X chunk landed
+    uint64_t *xempty = bars + 16;     // [8]  X chunk read by its transform warpgroup
+    uint64_t *a_full = bars + 24;     // [8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
+    uint64_t *a_free = bars + 32;     // [2]  units [0, C64a) / [C64a, C64) were read for the last time in this row tile (multicast)
+    uint64_t *acc_empty = bars + 34;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
     uint32_t *xchg = tmem_slot + 4;   // [2][5][128]
 
-    const int warp = threadIdx.x >> 5;
+    // Roles by PHYSICAL warp: the scheduler prefers the highest warp id, so the warps whose latency matters (MMA
+    // issuer, producers: 16-19; transform: 8-15) sit above the ALU-bound epilogue warps (0-7).  `warp` below is the
+    // logical index the role tests use; warp & 3 (the TMEM lane quarter) is the same for both.
+    const int pw = threadIdx.x >> 5;
+    const int warp = pw >= 16 ? pw - 16 : pw >= 12 ? pw : pw >= 8 ? pw - 4 : pw >= 4 ? pw + 12 : pw + 8;
     const int lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
@@ -86,18 +104,18 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         tma_prefetch_desc(&tm_b);
     }
     if (warp == 1 && lane == 0) {
-        for (int s = 0; s < 8; ++s) {
+        for (int s = 0; s < 4; ++s) {
             mbar_init(&bfull[s], 1);
-            mbar_init(&bempty[s], 1);
+            mbar_init(&tile_done[s], 1);
+        }
+        for (int s = 0; s < 8; ++s) {
             mbar_init(&xfull[s], 1);
             mbar_init(&xempty[s], 4);
             mbar_init(&a_full[s], leader ? 8 : 4);
         }
-        for (int s = 0; s < 4; ++s) mbar_init(&a_free[s], 1);
-        for (int b = 0; b < 2; ++b) {
-            mbar_init(&acc_full[b], 1);
-            mbar_init(&acc_empty[b], leader ? 16 : 8);   // two epilogue warpgroups per CTA
-        }
+        mbar_init(&a_free[0], 1);
+        mbar_init(&a_free[1], 1);
+        for (int b = 0; b < 2; ++b) mbar_init(&acc_empty[b], leader ? 16 : 8);   // two epilogue warpgroups per CTA
         fence_mbar_init();
     }
     cluster_sync_all();
@@ -110,82 +128,92 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
 
     if (warp == 0) {
         // ================================ B producer ==================================
-        uint32_t it = 0;
+        uint32_t tile = 0;
         for (int base = base0; base < p.num_row_tiles; base += gridDim.x) {
-            for (int nt = 0; nt < NT; ++nt) {
+            for (int nt = 0; nt < NT; ++nt, ++tile) {
                 const int brow = nt * BN + (int)rank * Cfg::kBRows;
-                for (int c = 0; c < C64; ++c, ++it) {
-                    const uint32_t s = it % BS, ph = (it / BS) & 1;
-                    mbar_wait(&bempty[s], ph ^ 1);
-                    if (elect_one()) {
-                        uint8_t *st = bs + s * Cfg::kBStageBytes;
-                        // both CTAs' bytes are accounted on the leader's barrier; the peer cannot run ahead of
-                        // the ring (bempty comes from the leader's MMAs), and bytes that land before the leader
-                        // arms the phase only make its transaction count transiently negative
-                        if (leader) mbar_arrive_expect_tx(&bfull[s], 2 * Cfg::kBStageBytes);
-                        tma_load_2d_pair(&tm_b, &bfull[s], st, c * 64, brow);
-                        tma_load_2d_pair(&tm_b, &bfull[s], st + Cfg::kBHalfBytes, ld64 + c * 64, brow);
-                    }
-                    __syncwarp();
+                const uint32_t g = tile % NG, gph = (tile / NG) & 1;
+                if (tile >= (uint32_t)NG) {   // the MMAs of the tile that last used this group have completed
+                    const uint32_t q = tile - NG;
+                    mbar_wait(&tile_done[q & 3], (q >> 2) & 1);
                 }
+                if (elect_one()) {
+                    uint8_t *st = bs + g * group_bytes;
+                    // both CTAs' bytes are accounted on the leader's barrier; the peer cannot run ahead of
+                    // the ring (tile_done comes from the leader's MMAs), and bytes that land before the leader
+                    // arms the phase only make its transaction count transiently negative
+                    if (p.knockout & 1) {   // timing experiments only: no B traffic
+                        if (leader) mbar_arrive(&bfull[g]);
+                    } else {
+                        if (leader) mbar_arrive_expect_tx(&bfull[g], 2 * group_bytes);
+                        for (int c = 0; c < C64; ++c) {
+                            tma_load_2d_pair(&tm_b, &bfull[g], st + c * Cfg::kBUnitBytes, c * 64, brow);
+                            tma_load_2d_pair(&tm_b, &bfull[g], st + c * Cfg::kBUnitBytes + Cfg::kBHalfBytes, ld64 + c * 64, brow);
+                        }
+                    }
+                }
+                __syncwarp();
             }
         }
     } else if (warp == 3) {
         // ================================ X producer ==================================
-        uint32_t xph = 0;
+        uint32_t xi = 0;   // running chunk index: slot xi % XS
         for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x) {
-            for (int kc = 0; kc < KC; ++kc) {
-                mbar_wait(&xempty[kc], xph ^ 1);
+            for (int kc = 0; kc < KC; ++kc, ++xi) {
+                const uint32_t s = xi % XS, ph = (xi / XS) & 1;
+                mbar_wait(&xempty[s], ph ^ 1);
                 if (elect_one()) {
-                    mbar_arrive_expect_tx(&xfull[kc], kXStageBytes);
-                    tma_load_2d(&tm_x, &xfull[kc], xs + kc * kXStageBytes, kc * kChunkK, rt * kTileM);
+                    mbar_arrive_expect_tx(&xfull[s], kXStageBytes);
+                    tma_load_2d(&tm_x, &xfull[s], xs + s * kXStageBytes, kc * kChunkK, rt * kTileM);
                 }
                 __syncwarp();
             }
-            xph ^= 1;
         }
     } else if (warp == 1) {
         if (leader) {
             // ================================ MMA issuer ==============================
             constexpr uint32_t idesc = make_idesc_f16(2 * kTileM, BN);
-            uint32_t it = 0, tile = 0, rtn = 0;
+            uint32_t tile = 0, rtn = 0;
             long long t_wait_acc = 0, t_wait = 0, t_issue = 0, t_mark = 0;
             const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
             for (int base = base0; base < p.num_row_tiles; base += gridDim.x, ++rtn) {
                 for (int nt = 0; nt < NT; ++nt, ++tile) {
                     const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
+                    const uint32_t g = tile % NG, gph = (tile / NG) & 1;
                     if (prof) t_mark = clock64();
-                    mbar_wait(&acc_empty[ab], aph ^ 1);
+                    mbar_wait2(&acc_empty[ab], aph ^ 1, &bfull[g], gph);
                     if (prof) { const long long t = clock64(); t_wait_acc += t - t_mark; t_mark = t; }
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
-                    for (int c = 0; c < C64; ++c, ++it) {
-                        const uint32_t s = it % BS, ph = (it / BS) & 1;
-                        const int nk = (2 * c + 1 < KC) ? 4 : 2;   // 16-value steps in this chunk
+                    const uint32_t bsm0 = smem_u32(bs + g * group_bytes);
+                    for (int c = 0; c < C64; ++c) {
+                        const int nk = (2 * c + 1 < KC) ? 4 : 2;   // 16-value steps in this unit
                         if (nt == 0) {
-                            // first centroid tile of a row tile: the chunk's h1/h2 must have been written
+                            // first centroid tile of a row tile: the unit's h1/h2 must have been written
                             const uint32_t k0 = 2 * c, k1 = (2 * c + 1 < KC) ? 2 * c + 1 : 2 * c;
-                            mbar_wait3(&a_full[k0], rtn & 1, &a_full[k1], rtn & 1, &bfull[s], ph);
-                        } else {
-                            mbar_wait(&bfull[s], ph);
+                            mbar_wait2(&a_full[k0], rtn & 1, &a_full[k1], rtn & 1);
+                            tc_fence_after();
                         }
                         if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
-                        tc_fence_after();
                         if (elect_one()) {
-                            const uint32_t bsm = smem_u32(bs + s * Cfg::kBStageBytes);
+                            const uint32_t bsm = bsm0 + c * Cfg::kBUnitBytes;
                             const uint64_t d1 = make_kmajor_sw128_desc(bsm);
                             const uint64_t d2 = make_kmajor_sw128_desc(bsm + Cfg::kBHalfBytes);
                             const uint32_t a1 = tmem_base + c * 32, a2 = a1 + Cfg::kA2Col0;
-                            // small terms first
-                            for (int ks = 0; ks < nk; ++ks)
-                                mma_bf16_ts_pair(d_tmem, a2 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
-                            for (int ks = 0; ks < nk; ++ks)
-                                mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d2 + static_cast<uint64_t>(ks * 2), idesc, 1u);
-                            for (int ks = 0; ks < nk; ++ks)
-                                mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
-                            tc_commit_pair(&bempty[s]);
-                            if (nt == NT - 1) tc_commit_pair(&a_free[c]);   // the chunk's h1/h2 may be overwritten
-                            if (c == C64 - 1) tc_commit_pair(&acc_full[ab]);
+                            // small terms first (knockout 8 / 16: timing experiments only, MMAs left out)
+                            if (!(p.knockout & 8)) {
+                                for (int ks = 0; ks < nk; ++ks)
+                                    mma_bf16_ts_pair(d_tmem, a2 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
+                                for (int ks = 0; ks < nk; ++ks)
+                                    mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d2 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                            }
+                            if (!(p.knockout & 16))
+                                for (int ks = 0; ks < nk; ++ks)
+                                    mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                            // last centroid tile of the row tile: the first half of h1/h2 may be overwritten
+                            if (nt == NT - 1 && c == C64a - 1) tc_commit_pair(&a_free[0]);
+                            if (nt == NT - 1 && c == C64 - 1) tc_commit_pair(&a_free[1]);   // ... and the second half
+                            if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 3]);
                         }
                         __syncwarp();
                         if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
@@ -197,7 +225,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 p.role_prof[1] = t_wait;
                 p.role_prof[2] = 0;
                 p.role_prof[3] = t_issue;
-                p.role_prof[4] = it;
+                p.role_prof[4] = tile;
             }
         }
     } else if ((warp >= 4 && warp < 8) || (warp >= 12 && warp < 16)) {
@@ -210,8 +238,9 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         uint32_t rtn = 0;
         for (int base = base0; base < p.num_row_tiles; base += gridDim.x, ++rtn) {
             for (int kc = wg; kc < KC; kc += 2) {
-                mbar_wait(&xfull[kc], rtn & 1);
-                const uint8_t *xrow = xs + kc * kXStageBytes + r * 128;
+                const uint32_t xi = rtn * KC + kc, xslot = xi % XS;
+                mbar_wait(&xfull[xslot], (xi / XS) & 1);
+                const uint8_t *xrow = xs + xslot * kXStageBytes + r * 128;
                 float x[32];
 #pragma unroll
                 for (int q = 0; q < 8; ++q) {
@@ -222,7 +251,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     x[4 * q + 3] = v.w * sx;
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&xempty[kc]);   // the chunk is in registers: the next row tile's may land
+                if (lane == 0) mbar_arrive(&xempty[xslot]);   // the chunk is in registers: the slot may be refilled
                 uint32_t h1[16], h2[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
@@ -233,7 +262,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     h2[i] = *reinterpret_cast<const uint32_t *>(&b);
                 }
                 // the previous row tile's last MMAs on this chunk have completed
-                if (rtn > 0) mbar_wait(&a_free[kc >> 1], (rtn - 1) & 1);
+                if (rtn > 0) {
+                    // (a barrier of its own, one phase per row tile: this warp gets here a whole row tile early, and
+                    // a parity wait is only meaningful within one phase of the barrier -- tile_done would alias)
+                    mbar_wait(&a_free[(kc >> 1) < C64a ? 0 : 1], (rtn - 1) & 1);
+                }
                 tc_fence_after();
                 if (!(p.knockout & 2)) {
                     tmem_st16(tmem_base + lane_addr + kc * 16, h1);
@@ -250,7 +283,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         }
     } else if ((warp >= 8 && warp < 12) || warp >= 16) {
         // ================================ epilogue ====================================
-        // as in assign_pair_ss_kernel: two warpgroups, each drains half of the columns of every accumulator tile
+        // Two warpgroups, each drains half of the columns of every accumulator tile.  The TMEM loads are
+        // double-buffered in batches of 16 columns and the centre norms of the NEXT tile are fetched while this one
+        // is processed.  (The running top-3 update is 10 ALU + 1 FMA instructions per score; a form balanced 6 + 6
+        // over the two pipes with predicated FMA-pipe moves ran the tile faster in cycles but, the kernel being
+        // power-limited at this size, 1.5 % slower in time -- left out.)
         const int eg = warp >= 16 ? 1 : 0;
         const int r = threadIdx.x & 127;
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
@@ -259,44 +296,57 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         const bool has_cols = col0 < BN;
         const float cmax = p.cstats[0];
         const float unscale = p.cstats[2];
+        const bool stages_cn = eg == 0 && r < BN;
+        if (stages_cn) cn_s[r] = p.cnorm[r];
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // both epilogue warpgroups
         uint32_t tile = 0, rtn = 0;
         for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x, ++rtn) {
+            // Four independent running top-3 sets (columns i mod 4).  Inside a set the columns arrive in ascending
+            // order, so strict '<' keeps the lowest index; the sets are merged once per row tile with an explicit
+            // (value, index) tie rule.  Indices are carried as floats (exact below 2^24).
             constexpr int NS = 4;
             const float inf = __int_as_float(0x7f800000);
-            float best[NS], second[NS], third[NS];
-            int bidx[NS], sidx[NS];
+            float best[NS], second[NS], third[NS], bidxf[NS], sidxf[NS];
 #pragma unroll
-            for (int q = 0; q < NS; ++q) { best[q] = second[q] = third[q] = inf; bidx[q] = sidx[q] = 0; }
+            for (int q = 0; q < NS; ++q) { best[q] = second[q] = third[q] = inf; bidxf[q] = sidxf[q] = 0.f; }
             for (int nt = 0; nt < NT; ++nt, ++tile) {
-                const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
-                float *cn = cn_s + ab * BN;
-                if (eg == 0 && r < BN) cn[r] = p.cnorm[nt * BN + r];
-                asm volatile("bar.sync 1, 256;" ::: "memory");   // both epilogue warpgroups
-                mbar_wait(&acc_full[ab], aph);
+                const uint32_t ab = tile & 1;
+                const float *cn = cn_s + ab * BN;
+                float cn_next = 0.f;
+                if (stages_cn) cn_next = __ldg(p.cnorm + (nt + 1 == NT ? 0 : nt + 1) * BN + r);
+                mbar_wait(&tile_done[tile & 3], (tile >> 2) & 1);
                 tc_fence_after();
                 if (has_cols && !(p.knockout & 4)) {
-                    const uint32_t acc = tmem_base + lane_addr + Cfg::kAccCol0 + ab * BN;
-#pragma unroll 1
-                    for (int c0 = col0; c0 < col0 + HALF; c0 += 32) {
-                        uint32_t v[32];
-                        tmem_ld32(acc + c0, v);
-                        tmem_wait_ld();
+                    const uint32_t acc = tmem_base + lane_addr + Cfg::kAccCol0 + ab * BN + col0;
+                    uint32_t va[16], vb[16];
+                    auto consume = [&](const uint32_t (&v)[16], int c0) {
+                        const float basef = (float)(nt * BN + c0);
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
+                        for (int i = 0; i < 16; ++i) {
                             const int q = i & (NS - 1);
                             const float sc = fmaf(__uint_as_float(v[i]), unscale, cn[c0 + i]);
                             if constexpr (DBG) {
                                 if (rt * kTileM + r < p.n)
                                     p.dbg_scores[(size_t)(rt * kTileM + r) * p.kpad + nt * BN + c0 + i] = sc;
                             }
-                            const int j = nt * BN + c0 + i;
+                            const float jf = basef + (float)i;
                             const bool lt1 = sc < best[q], lt2 = sc < second[q];
                             third[q] = fminf(third[q], fmaxf(sc, second[q]));
-                            sidx[q] = lt1 ? bidx[q] : (lt2 ? j : sidx[q]);
+                            sidxf[q] = lt1 ? bidxf[q] : (lt2 ? jf : sidxf[q]);
                             second[q] = fminf(second[q], fmaxf(sc, best[q]));
-                            bidx[q] = lt1 ? j : bidx[q];
+                            bidxf[q] = lt1 ? jf : bidxf[q];
                             best[q] = fminf(best[q], sc);
                         }
+                    };
+                    tmem_ld16(acc, va);
+#pragma unroll 1
+                    for (int c0 = 0; c0 < HALF; c0 += 32) {
+                        tmem_wait_ld();
+                        tmem_ld16(acc + c0 + 16, vb);
+                        consume(va, col0 + c0);
+                        tmem_wait_ld();
+                        if (c0 + 32 < HALF) tmem_ld16(acc + c0 + 32, va);
+                        consume(vb, col0 + c0 + 16);
                     }
                 }
                 tc_fence_before();
@@ -305,7 +355,12 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     if (leader) mbar_arrive(&acc_empty[ab]);
                     else mbar_arrive_remote_relaxed(&acc_empty[ab], 0);
                 }
+                if (stages_cn) cn_s[(ab ^ 1) * BN + r] = cn_next;   // last read one tile ago, before the previous bar.sync
+                asm volatile("bar.sync 1, 256;" ::: "memory");
             }
+            int bidx[NS], sidx[NS];
+#pragma unroll
+            for (int q = 0; q < NS; ++q) { bidx[q] = (int)bidxf[q]; sidx[q] = (int)sidxf[q]; }
             // merge sets 1..3 into set 0: lower value first, equal values -> lower index first
             float mb = best[0], ms = second[0], mt = third[0];
             int mbi = bidx[0], msi = sidx[0];

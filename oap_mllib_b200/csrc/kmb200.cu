@@ -686,15 +686,15 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
 static float score_eps_h16(int ld) { return (float)(g_eps_scale * ldexp(3.0 * ld / 16.0 + 32.0, -24)); }
 
 template <int BN>
-static int h16_stages(const kmb200_table *t) {
-    return std::min(PairH16Cfg<BN>::b_stages(t->ld / kChunkK), 8);
+static bool h16_fits(const kmb200_table *t) {
+    const int kc = t->ld / kChunkK;
+    return PairH16Cfg<BN>::x_slots(kc) >= 1 && PairH16Cfg<BN>::b_groups(kc) >= 2;
 }
 static bool h16_applies(const kmb200_table *t) {
     const Workspace &w = t->ws;
     if (!g_h16 || g_force_simt || g_kernel != 2 || g_passes != 3 || g_cluster != 2 || t->ld > 256 || w.bn < 32) return false;
     if ((t->rows + kTileM - 1) / kTileM < 2) return false;
-    const int st = w.bn == 32 ? h16_stages<32>(t) : w.bn == 64 ? h16_stages<64>(t) : h16_stages<128>(t);
-    return st >= 2;
+    return w.bn == 32 ? h16_fits<32>(t) : w.bn == 64 ? h16_fits<64>(t) : h16_fits<128>(t);
 }
 
 template <int BN, bool DBG>
@@ -704,8 +704,7 @@ static int launch_assign_h16_bn(kmb200_table *t) {
     auto kernel = assign_pair_h16_kernel<BN, DBG>;
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
-    const int bs = h16_stages<BN>(t);
-    const int smem = Cfg::smem_bytes(kc, bs);
+    const int smem = Cfg::smem_bytes(kc);
     if (!attr_set[t->device & 63]) {
         CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set[t->device & 63] = true;
@@ -722,7 +721,7 @@ static int launch_assign_h16_bn(kmb200_table *t) {
     p.num_row_tiles = (int32_t)((t->rows + kTileM - 1) / kTileM);
     p.num_col_tiles = w.kpad / BN;
     p.num_k_chunks = kc;
-    p.stages = bs;
+    p.stages = Cfg::x_slots(kc) | (Cfg::b_groups(kc) << 8);
     p.passes = 3;
     p.eps = score_eps_h16(t->ld);
     p.dbg_scores = g_dbg_scores;
