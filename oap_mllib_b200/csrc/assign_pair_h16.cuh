@@ -55,11 +55,22 @@ struct PairH16Cfg {
 // issuing warp several hundred cycles during which the (shallow) MMA queue drains, so the B operand of a whole
 // centroid tile is one ring entry ("group", 2..4 of them), and ONE commit per tile (tile_done) tells the
 // epilogue that the accumulator is complete and the B producer that the group may be refilled.
-template <int BN, bool DBG>
+// MODE: 0 = full bookkeeping (best, runner-up with indices, third value -> p.flag_list), 1 = the same plus the score
+// dump of kmb200_debug_scores, 2 = FAST: best with index and the runner-up VALUE only; rows whose gap is inside the
+// bound are appended to p.cand_list and go through a MODE 0 launch over a gathered copy (see launch_assign_h16).
+// p.n_dev (optional): the row count is read from device memory (the gathered copy's length is only known there).
+template <int BN, int MODE>
 __global__ void __launch_bounds__(kPairH16Threads, 1)
 assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_b,
                        const AssignParams p) {
     using Cfg = PairH16Cfg<BN>;
+    constexpr bool DBG = MODE == 1, FAST = MODE == 2;
+    int n_rows = p.n;
+    if (p.n_dev != nullptr) {
+        const int c = *p.n_dev;
+        n_rows = c < p.n ? c : p.n;
+    }
+    const int num_row_tiles = (n_rows + kTileM - 1) / kTileM;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -129,7 +140,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     if (warp == 0) {
         // ================================ B producer ==================================
         uint32_t tile = 0;
-        for (int base = base0; base < p.num_row_tiles; base += gridDim.x) {
+        for (int base = base0; base < num_row_tiles; base += gridDim.x) {
             for (int nt = 0; nt < NT; ++nt, ++tile) {
                 const int brow = nt * BN + (int)rank * Cfg::kBRows;
                 const uint32_t g = tile % NG, gph = (tile / NG) & 1;
@@ -158,7 +169,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     } else if (warp == 3) {
         // ================================ X producer ==================================
         uint32_t xi = 0;   // running chunk index: slot xi % XS
-        for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x) {
+        for (int rt = tile0; rt - (int)rank < num_row_tiles; rt += gridDim.x) {
             for (int kc = 0; kc < KC; ++kc, ++xi) {
                 const uint32_t s = xi % XS, ph = (xi / XS) & 1;
                 mbar_wait(&xempty[s], ph ^ 1);
@@ -176,7 +187,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             uint32_t tile = 0, rtn = 0;
             long long t_wait_acc = 0, t_wait = 0, t_issue = 0, t_mark = 0;
             const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
-            for (int base = base0; base < p.num_row_tiles; base += gridDim.x, ++rtn) {
+            for (int base = base0; base < num_row_tiles; base += gridDim.x, ++rtn) {
                 for (int nt = 0; nt < NT; ++nt, ++tile) {
                     const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
                     const uint32_t g = tile % NG, gph = (tile / NG) & 1;
@@ -236,7 +247,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
         const float sx = p.cstats[3];
         uint32_t rtn = 0;
-        for (int base = base0; base < p.num_row_tiles; base += gridDim.x, ++rtn) {
+        for (int base = base0; base < num_row_tiles; base += gridDim.x, ++rtn) {
             for (int kc = wg; kc < KC; kc += 2) {
                 const uint32_t xi = rtn * KC + kc, xslot = xi % XS;
                 mbar_wait(&xfull[xslot], (xi / XS) & 1);
@@ -300,7 +311,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         if (stages_cn) cn_s[r] = p.cnorm[r];
         asm volatile("bar.sync 1, 256;" ::: "memory");   // both epilogue warpgroups
         uint32_t tile = 0, rtn = 0;
-        for (int rt = tile0; rt - (int)rank < p.num_row_tiles; rt += gridDim.x, ++rtn) {
+        for (int rt = tile0; rt - (int)rank < num_row_tiles; rt += gridDim.x, ++rtn) {
             // Four independent running top-3 sets (columns i mod 4).  Inside a set the columns arrive in ascending
             // order, so strict '<' keeps the lowest index; the sets are merged once per row tile with an explicit
             // (value, index) tie rule.  Indices are carried as floats (exact below 2^24).
@@ -326,16 +337,23 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                             const int q = i & (NS - 1);
                             const float sc = fmaf(__uint_as_float(v[i]), unscale, cn[c0 + i]);
                             if constexpr (DBG) {
-                                if (rt * kTileM + r < p.n)
+                                if (rt * kTileM + r < n_rows)
                                     p.dbg_scores[(size_t)(rt * kTileM + r) * p.kpad + nt * BN + c0 + i] = sc;
                             }
                             const float jf = basef + (float)i;
-                            const bool lt1 = sc < best[q], lt2 = sc < second[q];
-                            third[q] = fminf(third[q], fmaxf(sc, second[q]));
-                            sidxf[q] = lt1 ? bidxf[q] : (lt2 ? jf : sidxf[q]);
-                            second[q] = fminf(second[q], fmaxf(sc, best[q]));
-                            bidxf[q] = lt1 ? jf : bidxf[q];
-                            best[q] = fminf(best[q], sc);
+                            if constexpr (FAST) {   // 6 instructions per score instead of 11
+                                const bool lt1 = sc < best[q];
+                                second[q] = fminf(second[q], fmaxf(sc, best[q]));
+                                bidxf[q] = lt1 ? jf : bidxf[q];
+                                best[q] = fminf(best[q], sc);
+                            } else {
+                                const bool lt1 = sc < best[q], lt2 = sc < second[q];
+                                third[q] = fminf(third[q], fmaxf(sc, second[q]));
+                                sidxf[q] = lt1 ? bidxf[q] : (lt2 ? jf : sidxf[q]);
+                                second[q] = fminf(second[q], fmaxf(sc, best[q]));
+                                bidxf[q] = lt1 ? jf : bidxf[q];
+                                best[q] = fminf(best[q], sc);
+                            }
                         }
                     };
                     tmem_ld16(acc, va);
@@ -369,11 +387,22 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 else if (has_index && (v < ms || (v == ms && j < msi))) { mt = ms; ms = v; msi = j; }
                 else if (v < mt) mt = v;
             };
+            // FAST mode: (best, index, runner-up value) only
+            auto merge2 = [&](float bq, float sq, int jq) {
+                const bool win = bq < mb || (bq == mb && jq < mbi);
+                ms = win ? fminf(mb, sq) : fminf(ms, bq);
+                mbi = win ? jq : mbi;
+                mb = win ? bq : mb;
+            };
 #pragma unroll
             for (int q = 1; q < NS; ++q) {
-                insert(best[q], bidx[q], true);
-                insert(second[q], sidx[q], true);
-                insert(third[q], 0, false);
+                if constexpr (FAST) {
+                    merge2(best[q], second[q], bidx[q]);
+                } else {
+                    insert(best[q], bidx[q], true);
+                    insert(second[q], sidx[q], true);
+                    insert(third[q], 0, false);
+                }
             }
             uint32_t *xb = xchg + (rtn & 1) * 5 * 128;
             if (eg == 1) {
@@ -385,17 +414,29 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             }
             asm volatile("bar.sync 2, 256;" ::: "memory");
             if (eg == 0) {
-                insert(__uint_as_float(xb[0 * 128 + r]), (int)xb[3 * 128 + r], true);
-                insert(__uint_as_float(xb[1 * 128 + r]), (int)xb[4 * 128 + r], true);
-                insert(__uint_as_float(xb[2 * 128 + r]), 0, false);
+                if constexpr (FAST) {
+                    merge2(__uint_as_float(xb[0 * 128 + r]), __uint_as_float(xb[1 * 128 + r]), (int)xb[3 * 128 + r]);
+                } else {
+                    insert(__uint_as_float(xb[0 * 128 + r]), (int)xb[3 * 128 + r], true);
+                    insert(__uint_as_float(xb[1 * 128 + r]), (int)xb[4 * 128 + r], true);
+                    insert(__uint_as_float(xb[2 * 128 + r]), 0, false);
+                }
                 const int row = rt * kTileM + r;
-                if (row < p.n && !(p.knockout & 4)) {
+                if (row < n_rows && !(p.knockout & 4)) {
                     p.labels[row] = mbi;
                     const float xn = sqrtf(p.xnorm[row]);
                     // relative part (accumulation, split residuals) + absolute part (FP16 subnormal range)
                     const float bound = 2.0f * (p.eps * (2.0f * xn * cmax + cmax * cmax) +
                                                 p.sqrt_ld * (p.cstats[4] * 2.0f * cmax + p.cstats[5] * xn));
-                    if (ms - mb <= bound) flag_row(p, row, mbi, msi, mt - mb <= bound);
+                    if constexpr (FAST) {
+                        // (in FAST mode `ms` is exact -- the merge below only needs values for it -- msi / mt are not)
+                        if (ms - mb <= bound) {
+                            const int pos = atomicAdd(p.cand_count, 1);   // may run past cand_cap: the host checks
+                            if (pos < p.cand_cap) p.cand_list[pos] = row;
+                        }
+                    } else {
+                        if (ms - mb <= bound) flag_row(p, row, mbi, msi, mt - mb <= bound);
+                    }
                 }
             }
         }

@@ -65,6 +65,11 @@ struct AssignParams {
     long long *role_prof;  // optional cycle counters of the MMA-issuer warp of CTA 0 (diagnostics), else nullptr
     int32_t knockout;      // debugging only: 1 = no TMA, 2 = no transform work, 4 = no epilogue work (results invalid)
     float sqrt_ld;         // sqrt(ld) (FP16-split kernel: absolute part of the near-tie bound)
+    // FP16-split kernel, two-level bookkeeping (assign_pair_h16.cuh)
+    const int32_t *n_dev = nullptr;   // optional: row count in device memory (min with n)
+    int32_t *cand_list = nullptr;     // FAST mode: rows whose best / runner-up gap is inside the bound
+    int32_t *cand_count = nullptr;
+    int32_t cand_cap = 0;
 };
 
 // Near-tie bookkeeping shared by the assign kernels: rows whose winner must be decided in FP64.

@@ -408,6 +408,33 @@ __global__ void recheck_merge_kernel(const int2 *__restrict__ list, const int32_
     }
 }
 
+// ---- two-level bookkeeping of the FP16-split assign kernel
+// Dense copy of the candidate rows (one warp per row, float4 moves) and of their squared norms.
+__global__ void gather_rows_kernel(const float *__restrict__ X, const float *__restrict__ xnorm,
+                                   const int32_t *__restrict__ cand, const int32_t *__restrict__ cand_count,
+                                   int32_t cand_cap, int ld, float *__restrict__ xc, float *__restrict__ xnc) {
+    int count = *cand_count;
+    if (count > cand_cap) count = cand_cap;
+    const int lane = threadIdx.x & 31;
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    const int vec = ld >> 2;
+    for (int i = warp_global; i < count; i += nwarps) {
+        const int row = cand[i];
+        const float4 *src = reinterpret_cast<const float4 *>(X + (size_t)row * ld);
+        float4 *dst = reinterpret_cast<float4 *>(xc + (size_t)i * ld);
+        for (int v = lane; v < vec; v += 32) dst[v] = __ldg(src + v);
+        if (lane == 0) xnc[i] = xnorm[row];
+    }
+}
+
+__global__ void scatter_labels_kernel(const int32_t *__restrict__ cand, const int32_t *__restrict__ cand_count,
+                                      int32_t cand_cap, const int32_t *__restrict__ labels_c,
+                                      int32_t *__restrict__ labels) {
+    int count = *cand_count;
+    if (count > cand_cap) count = cand_cap;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) labels[cand[i]] = labels_c[i];
+}
+
 // ------------------------------------------------------------------ bucketing rows by label
 // counts[j] = number of local rows with label j.
 __global__ void label_hist_kernel(const int32_t *__restrict__ labels, int64_t n, int k, int32_t *counts) {

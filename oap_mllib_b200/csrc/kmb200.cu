@@ -63,6 +63,9 @@ static int g_kernel = 2;   // 2 = X-resident / multicast kernel where it applies
 static int g_fused = 1;    // 1 = one-pass CUDA-core kernel when k*ld is small (HBM-bound regime)
 static int g_ss = 1;       // pair kernel: 1 = main product reads X from shared memory (SS), corrections only in TMEM
 static int g_h16 = 1;      // 1 = FP16-split pair kernel (assign_pair_h16.cuh) where it applies, 0 = TF32 + BF16 corrections
+static int g_two_level = 1;  // FP16-split kernel: 1 = fast bookkeeping over all rows + full bookkeeping over the near-tie rows
+                             //   (tables of >= kTwoLevelMinRows rows), 2 = always, 0 = never
+static int64_t g_cand_cap = 0;   // candidate-buffer rows (0 = rows / 16); tests shrink it to force the overflow path
 static int g_rb_cap = 4;   // experiments: cap on the B-ring group slots of the pair kernel
 static int g_corr = 1;     // pair kernel: 1 = BF16 correction MMAs (2 pass-equivalents), 0 = TF32 corrections (3 passes)
 static int g_cluster = 2;  // 2 = CTA pairs (tcgen05 cta_group::2, centroid tiles split across the pair), 1 = single CTAs
@@ -151,11 +154,21 @@ struct Workspace {
     CUtensorMap tm_b16_half;               // FP16 [kpad x 2*ld64], box 64 values (128 bytes) x bn/2 rows
     CUtensorMap tm_bcorr_half;             // BF16 [kpad x 2*ld], box 64 values (128 bytes) x bn/2 rows
     CUtensorMap tm_bhi_half, tm_blo_half;  // boxes of bn/2 rows: each CTA of a pair loads half a centroid tile
+    // two-level bookkeeping of the FP16-split kernel: the near-tie rows of the fast pass, gathered
+    float *xc = nullptr;              // [cand_cap x ld] copies of the candidate rows
+    float *xnc = nullptr;             // [cand_cap] their ||x||^2
+    int32_t *cand_list = nullptr;     // [cand_cap] their row numbers
+    int32_t *labels_c = nullptr;      // [cand_cap] their labels (scattered back after the re-check)
+    int64_t cand_cap = 0;
+    CUtensorMap tm_xc;
+    bool two_level_active = false;    // set by launch_assign for the launch_recheck that follows
+    bool two_level_off = false;       // the candidate buffer overflowed once in this fit: full bookkeeping from then on
     // pinned host mirror read once per iteration
     struct Host {
         int32_t flags[2];
         int32_t flag_count;
         int32_t full_count;
+        int32_t cand_count;
         double cost;
     } *host = nullptr;
 };
@@ -176,7 +189,8 @@ struct kmb200_table {
 
 static void ws_free(Workspace &w) {
     void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.b16, w.cnorm64, w.rc_score, w.rc_idx, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
-                    w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage};
+                    w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage,
+                    w.xc, w.xnc, w.cand_list, w.labels_c};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (w.host) cudaFreeHost(w.host);
@@ -697,11 +711,43 @@ static bool h16_applies(const kmb200_table *t) {
     return w.bn == 32 ? h16_fits<32>(t) : w.bn == 64 ? h16_fits<64>(t) : h16_fits<128>(t);
 }
 
-template <int BN, bool DBG>
-static int launch_assign_h16_bn(kmb200_table *t) {
+constexpr int64_t kTwoLevelMinRows = 1 << 18;
+
+// (Re)allocates the candidate buffers when the two-level scheme applies to this table; false = use full bookkeeping.
+static bool two_level_prepare(kmb200_table *t) {
+    Workspace &w = t->ws;
+    if (!g_two_level || w.two_level_off || g_dbg_scores) return false;
+    if (g_two_level == 1 && t->rows < kTwoLevelMinRows) return false;
+    int64_t cap = g_cand_cap > 0 ? g_cand_cap : t->rows / 16;
+    cap = std::max<int64_t>((cap + kTileM - 1) / kTileM * kTileM, 2 * kTileM);
+    if (w.cand_cap == cap && w.xc) return true;
+    for (void *ptr : {(void *)w.xc, (void *)w.xnc, (void *)w.cand_list, (void *)w.labels_c})
+        if (ptr) cudaFree(ptr);
+    w.xc = nullptr; w.xnc = nullptr; w.cand_list = nullptr; w.labels_c = nullptr;
+    w.cand_cap = 0;
+    bool ok = cudaMalloc(reinterpret_cast<void **>(&w.xc), (size_t)cap * t->ld * sizeof(float)) == cudaSuccess &&
+              cudaMalloc(reinterpret_cast<void **>(&w.xnc), (size_t)cap * sizeof(float)) == cudaSuccess &&
+              cudaMalloc(reinterpret_cast<void **>(&w.cand_list), (size_t)cap * sizeof(int32_t)) == cudaSuccess &&
+              cudaMalloc(reinterpret_cast<void **>(&w.labels_c), (size_t)cap * sizeof(int32_t)) == cudaSuccess;
+    if (ok) ok = make_map(&w.tm_xc, w.xc, (uint64_t)cap, (uint64_t)t->ld, kTileM) == 0;
+    if (!ok) {   // not enough memory left for the copies: the single-pass scheme needs none
+        cudaGetLastError();
+        for (void *ptr : {(void *)w.xc, (void *)w.xnc, (void *)w.cand_list, (void *)w.labels_c})
+            if (ptr) cudaFree(ptr);
+        w.xc = nullptr; w.xnc = nullptr; w.cand_list = nullptr; w.labels_c = nullptr;
+        w.two_level_off = true;
+        return false;
+    }
+    w.cand_cap = cap;
+    return true;
+}
+
+// MODE 0 / 1 (score dump) over the table, MODE 2 (fast) over the table, or MODE 0 over the gathered candidates (cand).
+template <int BN, int MODE>
+static int launch_assign_h16_bn(kmb200_table *t, bool cand) {
     Workspace &w = t->ws;
     using Cfg = PairH16Cfg<BN>;
-    auto kernel = assign_pair_h16_kernel<BN, DBG>;
+    auto kernel = assign_pair_h16_kernel<BN, MODE>;
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
     const int smem = Cfg::smem_bytes(kc);
@@ -709,16 +755,17 @@ static int launch_assign_h16_bn(kmb200_table *t) {
         CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set[t->device & 63] = true;
     }
+    const int64_t rows = cand ? (int64_t)w.host->cand_count : t->rows;
     AssignParams p;
     p.cnorm = w.cnorm;
-    p.xnorm = t->xnorm;
+    p.xnorm = cand ? w.xnc : t->xnorm;
     p.cstats = w.cstats;
-    p.labels = w.labels;
+    p.labels = cand ? w.labels_c : w.labels;
     p.flag_count = w.flag_count;
     p.flag_list = w.flag_list;
     p.flag_cap = (int32_t)t->rows;
-    p.n = (int32_t)t->rows;
-    p.num_row_tiles = (int32_t)((t->rows + kTileM - 1) / kTileM);
+    p.n = (int32_t)rows;
+    p.num_row_tiles = (int32_t)((rows + kTileM - 1) / kTileM);
     p.num_col_tiles = w.kpad / BN;
     p.num_k_chunks = kc;
     p.stages = Cfg::x_slots(kc) | (Cfg::b_groups(kc) << 8);
@@ -727,8 +774,12 @@ static int launch_assign_h16_bn(kmb200_table *t) {
     p.dbg_scores = g_dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;
-    p.role_prof = g_role_prof;
+    p.role_prof = cand ? nullptr : g_role_prof;
     p.sqrt_ld = sqrtf((float)t->ld);
+    p.n_dev = nullptr;
+    p.cand_list = w.cand_list;
+    p.cand_count = w.flag_count + 2;
+    p.cand_cap = (int32_t)w.cand_cap;
     const int pairs = std::min((p.num_row_tiles + 1) / 2, t->num_sms / 2);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(pairs * 2));
@@ -742,18 +793,48 @@ static int launch_assign_h16_bn(kmb200_table *t) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    CU_TRY(cudaLaunchKernelEx(&cfg, kernel, w.tm_x, w.tm_b16_half, p));
+    CU_TRY(cudaLaunchKernelEx(&cfg, kernel, cand ? w.tm_xc : w.tm_x, w.tm_b16_half, p));
     g_prof.kernel_launches++;
     return 0;
 }
 
-static int launch_assign_h16(kmb200_table *t) {
-    const bool dbg = g_dbg_scores != nullptr;
+template <int MODE>
+static int launch_assign_h16_mode(kmb200_table *t, bool cand) {
     switch (t->ws.bn) {
-        case 32: return dbg ? launch_assign_h16_bn<32, true>(t) : launch_assign_h16_bn<32, false>(t);
-        case 64: return dbg ? launch_assign_h16_bn<64, true>(t) : launch_assign_h16_bn<64, false>(t);
-        default: return dbg ? launch_assign_h16_bn<128, true>(t) : launch_assign_h16_bn<128, false>(t);
+        case 32: return launch_assign_h16_bn<32, MODE>(t, cand);
+        case 64: return launch_assign_h16_bn<64, MODE>(t, cand);
+        default: return launch_assign_h16_bn<128, MODE>(t, cand);
     }
+}
+
+// Two-level bookkeeping: the epilogue's running (best, runner-up, third) update is 11 instructions per score and a
+// quarter of the kernel's energy at the headline shape, but only the ~1 % of rows whose two best scores are inside
+// the error bound need more than the winner.  So: a FAST pass over all rows (6 instructions per score) that lists
+// those rows, a gather of the listed rows into a dense copy, and a full-bookkeeping pass over the copy whose
+// (row, runner-up) / (row, all) lists feed the FP64 re-check as before (launch_recheck scatters the labels back).
+static int launch_assign_h16(kmb200_table *t) {
+    Workspace &w = t->ws;
+    w.two_level_active = false;
+    if (g_dbg_scores) return launch_assign_h16_mode<1>(t, false);
+    if (!two_level_prepare(t)) return launch_assign_h16_mode<0>(t, false);
+    KM_TRY(launch_assign_h16_mode<2>(t, false));
+    // The candidate count decides what runs next, so it is read back here: one short host round trip per
+    // iteration (the fit loop has one already).  Overflow of the candidate buffer (pathological data: a large
+    // share of near-ties) switches this fit to the single-pass scheme, starting with this very assignment.
+    CU_TRY(cudaMemcpyAsync(&w.host->cand_count, w.flag_count + 2, sizeof(int32_t), cudaMemcpyDeviceToHost, t->stream));
+    CU_TRY(cudaStreamSynchronize(t->stream));
+    if ((int64_t)w.host->cand_count > w.cand_cap) {
+        w.two_level_off = true;
+        CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
+        return launch_assign_h16_mode<0>(t, false);
+    }
+    w.two_level_active = true;
+    if (w.host->cand_count == 0) return 0;   // no near-ties at all: the lists stay empty
+    gather_rows_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, t->xnorm, w.cand_list, w.flag_count + 2,
+                                                              (int32_t)w.cand_cap, t->ld, w.xc, w.xnc);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches++;
+    return launch_assign_h16_mode<0>(t, true);
 }
 
 static int launch_assign_pair(kmb200_table *t, bool *applicable) {
@@ -891,17 +972,27 @@ static int launch_assign(kmb200_table *t) {
 static int launch_recheck(kmb200_table *t) {
     Workspace &w = t->ws;
     if (g_force_simt) return 0;
-    recheck_kernel<<<t->num_sms * 4, 256, 0, t->stream>>>(t->X, w.cent, w.flag_list, w.flag_count, (int32_t)t->rows,
-                                                         t->rows, w.k, t->ld, w.labels);
+    // two-level scheme: the lists index the gathered copy of the candidate rows
+    const bool tl = w.two_level_active;
+    const float *X = tl ? w.xc : t->X;
+    int32_t *labels = tl ? w.labels_c : w.labels;
+    recheck_kernel<<<t->num_sms * 4, 256, 0, t->stream>>>(X, w.cent, w.flag_list, w.flag_count, (int32_t)t->rows,
+                                                         t->rows, w.k, t->ld, labels);
     CU_TRY(cudaGetLastError());
     const int rgrid = t->num_sms * 8;
-    recheck_full_kernel<<<rgrid, 256, 0, t->stream>>>(t->X, w.cent, w.cnorm64, w.flag_list, w.flag_count + 1,
-                                                     (int32_t)t->rows, w.k, t->ld, w.labels, w.rc_score, w.rc_idx);
+    recheck_full_kernel<<<rgrid, 256, 0, t->stream>>>(X, w.cent, w.cnorm64, w.flag_list, w.flag_count + 1,
+                                                     (int32_t)t->rows, w.k, t->ld, labels, w.rc_score, w.rc_idx);
     CU_TRY(cudaGetLastError());
     recheck_merge_kernel<<<8, 256, 0, t->stream>>>(w.flag_list, w.flag_count + 1, (int32_t)t->rows, rgrid, w.rc_score,
-                                                  w.rc_idx, w.labels);
+                                                  w.rc_idx, labels);
     CU_TRY(cudaGetLastError());
     g_prof.kernel_launches += 3;
+    if (tl) {
+        scatter_labels_kernel<<<t->num_sms * 2, 256, 0, t->stream>>>(w.cand_list, w.flag_count + 2, (int32_t)w.cand_cap,
+                                                                    w.labels_c, w.labels);
+        CU_TRY(cudaGetLastError());
+        g_prof.kernel_launches++;
+    }
     return 0;
 }
 
@@ -1127,6 +1218,7 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
     KM_TRY(upload_centers(t, init_centers, k, d));
     KM_TRY(launch_split(t));
     KM_TRY(g_events.ensure(max_iter));
+    w.two_level_off = false;
 
     double cost = 0.0;
     int it = 0;
@@ -1218,6 +1310,7 @@ extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *c
     KM_TRY(g_events.ensure(1));
     cudaEvent_t *ev = &g_events.ev[0];
     KM_TRY(upload_centers(t, centers, k, d));
+    w.two_level_off = false;
     KM_TRY(launch_split(t));
     const bool fused = fused_applies(t);
     CU_TRY(cudaEventRecord(ev[0], st));
@@ -1385,6 +1478,10 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         g_fused = value != 0;
     } else if (!strcmp(name, "ss")) {
         g_ss = value != 0;
+    } else if (!strcmp(name, "two_level")) {
+        g_two_level = (int)value;
+    } else if (!strcmp(name, "cand_cap")) {
+        g_cand_cap = (int64_t)value;
     } else if (!strcmp(name, "h16")) {
         g_h16 = value != 0;
     } else if (!strcmp(name, "rb_cap")) {

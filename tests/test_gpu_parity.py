@@ -162,6 +162,30 @@ def test_near_ties_and_duplicates_take_lowest_index(m):
     assert np.array_equal(labels, want)
 
 
+@pytest.mark.parametrize("two_level,copies", [(0, 2), (2, 2), (0, 3), (2, 3)])
+def test_h16_duplicated_centres_take_lowest_index(m, two_level, copies):
+    """Every row has `copies` exactly tied best centres on the FP16-split path: all rows are near-ties (pair re-check
+    for two copies, full re-check for three) and the lowest index must win, single-pass and two-level alike."""
+    n, d, base = 6000, 128, 32
+    X, _, _ = ko.gaussian_blobs(n, d, base, seed=9)
+    C0 = ko.row_init_centers(X, base)
+    Cn = np.concatenate([C0] * copies)
+    try:
+        m._lib.check(m.lib().kmb200_set_option(b"two_level", float(two_level)))
+        m._lib.check(m.lib().kmb200_set_option(b"cand_cap", float(n)))
+        t = m.OneDAL.vectorsToMergedNumericTables(X)
+        try:
+            labels, sizes, _ = gpu_assign(m, t, Cn)
+        finally:
+            t.release()
+    finally:
+        m._lib.check(m.lib().kmb200_set_option(b"two_level", 1.0))
+        m._lib.check(m.lib().kmb200_set_option(b"cand_cap", 0.0))
+    want, _, _ = ko.assign(X.astype(np.float64), Cn)
+    assert np.array_equal(labels, want)
+    assert labels.max() < base and sizes[base:].sum() == 0
+
+
 def test_tensor_core_score_error_is_inside_the_bound(m):
     """3xTF32 scores vs FP64: the measured error, normalised by (2|x||c|max + |c|max^2), must sit
     well inside the bound the kernel uses to decide which rows need the FP64 re-check."""
@@ -223,6 +247,9 @@ def test_force_simt_path_agrees(m):
     {"h16": 0, "bf16_corr": 0},           # CTA pairs, plain 3xTF32
     {"h16": 0, "ss": 0},                  # CTA pairs, BF16 corrections, A operand entirely in TMEM
     {"fused": 0},                         # tensor-core path even where the one-pass small-k kernel applies
+    {"two_level": 2},                     # fast pass + full bookkeeping over the near-tie rows, forced on small tables
+    {"two_level": 2, "cand_cap": 256},    # ... with a candidate buffer that overflows: falls back to the single pass
+    {"two_level": 0},                     # single pass with full bookkeeping
 ])
 def test_every_kernel_variant_keeps_parity(m, options):
     """The dispatcher picks one kernel per shape; the others stay selectable and must give the same fit."""
@@ -234,7 +261,8 @@ def test_every_kernel_variant_keeps_parity(m, options):
             X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + k)
             check_fit_parity(m, X, ko.row_init_centers(X, k), tol=1e-4, max_iter=5)
     finally:
-        for name, val in {"kernel": 2, "cluster": 2, "bf16_corr": 1, "ss": 1, "fused": 1, "h16": 1}.items():
+        for name, val in {"kernel": 2, "cluster": 2, "bf16_corr": 1, "ss": 1, "fused": 1, "h16": 1, "two_level": 1,
+                          "cand_cap": 0}.items():
             m._lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
 
 
