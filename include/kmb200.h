@@ -116,18 +116,26 @@ typedef struct {
     int32_t empty_cluster_events;
     int64_t full_rechecks;     /* of those, rows that needed all k centres re-scored (third centre inside the bound) */
     float total_ms;            /* first kernel of the first iteration -> end of the last         */
-    float assign_ms;           /* tcgen05 distance GEMM + argmin epilogue                        */
+    float assign_ms;           /* tcgen05 distance GEMM + argmin epilogue (all launches of the phase) */
     float recheck_ms;          /* FP64 re-evaluation of near-tie rows                            */
     float bucket_ms;           /* label histogram + scan + row bucketing                         */
     float accumulate_ms;       /* per-cluster FP64 sums / cost                                   */
     float allreduce_ms;        /* NCCL all-reduce (0 for a single GPU)                           */
     float finalize_ms;         /* centres, convergence flag, TF32 split of the new centres      */
+    float assign_main_ms;      /* of assign_ms: the main assign kernel alone (without the candidate gather and the
+                                  second pass over the near-tie rows of the two-level scheme)    */
 } kmb200_profile;
 int kmb200_get_profile(kmb200_profile *out);
 
 /* Tunables (process-wide; for experiments and tests).  name: "eps_scale" (multiplier on the
- * near-tie error bound, default 1.0), "passes" (3 = 3xTF32 [default], 1 = single TF32 pass + wider
- * re-check), "force_simt" (1 = use the CUDA-core FP32 assign kernel instead of tcgen05; debugging). */
+ * near-tie error bound, default 1.0), "passes" (3 = full-accuracy tensor-core schemes [default],
+ * 1 = single TF32 pass + wider re-check), "force_simt" (1 = use the CUDA-core FP64 assign kernel
+ * instead of tcgen05; debugging).  Kernel selection (all default to the production choice; every
+ * variant gives the same fit, tests/test_gpu_parity.py): "h16" (1 = FP16-split CTA-pair kernel for
+ * d <= 256), "two_level" (1 = fast pass + full bookkeeping over the near-tie rows for tables of
+ * >= 2^18 rows, 2 = always, 0 = never), "cand_cap" (rows of the near-tie copy, 0 = rows/16),
+ * "ss", "bf16_corr", "cluster", "kernel", "fused", "rb_cap" (older kernels), and the diagnostics
+ * "knockout" / "role_prof" (timing experiments; results are invalid with knockout != 0). */
 int kmb200_set_option(const char *name, double value);
 
 /* ---- cluster sizes without any device allocation ------------------------------------------------

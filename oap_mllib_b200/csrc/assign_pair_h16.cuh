@@ -82,6 +82,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     const int C64a = C64 >> 1;           // units [0, C64a) of A are released early in a row tile's last centroid tile
     const int ld64 = C64 * 64;
     const int group_bytes = C64 * Cfg::kBUnitBytes;
+    const int RES = NG < NT ? NG : NT;   // centroid tiles still resident in the B groups at a row-tile switch
     uint8_t *xs = smem;                                  // [XS][128 rows x 128 B], swizzled
     uint8_t *bs = smem + XS * kXStageBytes;              // [NG][C64][g1 chunk | g2 chunk] (this CTA's rows)
     uint8_t *tail = bs + NG * group_bytes;
@@ -139,16 +140,20 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
 
     if (warp == 0) {
         // ================================ B producer ==================================
-        uint32_t tile = 0;
-        for (int base = base0; base < num_row_tiles; base += gridDim.x) {
-            for (int nt = 0; nt < NT; ++nt, ++tile) {
+        uint32_t tile = 0, rtn = 0;
+        for (int base = base0; base < num_row_tiles; base += gridDim.x, ++rtn) {
+            for (int i = 0; i < NT; ++i, ++tile) {
+                const int nt = (rtn & 1) ? NT - 1 - i : i;   // serpentine order, see the MMA issuer
                 const int brow = nt * BN + (int)rank * Cfg::kBRows;
-                const uint32_t g = tile % NG, gph = (tile / NG) & 1;
-                if (tile >= (uint32_t)NG) {   // the MMAs of the tile that last used this group have completed
+                const uint32_t g = nt % NG;
+                // the MMAs of the tile that last used this group have completed (waited for at EVERY tile, also
+                // the resident ones: a parity wait must not skip a phase of its barrier)
+                if (tile >= (uint32_t)NG) {
                     const uint32_t q = tile - NG;
                     mbar_wait(&tile_done[q & 3], (q >> 2) & 1);
                 }
-                if (elect_one()) {
+                const bool resident = rtn > 0 && i < RES;
+                if (!resident && elect_one()) {
                     uint8_t *st = bs + g * group_bytes;
                     // both CTAs' bytes are accounted on the leader's barrier; the peer cannot run ahead of
                     // the ring (tile_done comes from the leader's MMAs), and bytes that land before the leader
@@ -184,22 +189,34 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         if (leader) {
             // ================================ MMA issuer ==============================
             constexpr uint32_t idesc = make_idesc_f16(2 * kTileM, BN);
-            uint32_t tile = 0, rtn = 0;
+            uint32_t tile = 0, rtn = 0, bpar = 0;   // bpar: parity of the next load into each B group
             long long t_wait_acc = 0, t_wait = 0, t_issue = 0, t_mark = 0;
             const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
             for (int base = base0; base < num_row_tiles; base += gridDim.x, ++rtn) {
-                for (int nt = 0; nt < NT; ++nt, ++tile) {
+                for (int i = 0; i < NT; ++i, ++tile) {
+                    // Serpentine order over the centroid tiles: odd row tiles walk them backwards, and centroid
+                    // tile nt always lives in B group nt % NG -- so the last RES = min(NG, NT) tiles of one row tile
+                    // are exactly the first RES of the next and are still in shared memory (no reload; with
+                    // NT <= NG the whole B operand stays resident).  Which of two exactly tied columns is met
+                    // first now depends on the direction; tied rows are re-checked in FP64 with the index rule.
+                    const int nt = (rtn & 1) ? NT - 1 - i : i;
                     const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
-                    const uint32_t g = tile % NG, gph = (tile / NG) & 1;
+                    const uint32_t g = nt % NG;
+                    const bool resident = rtn > 0 && i < RES;
                     if (prof) t_mark = clock64();
-                    mbar_wait2(&acc_empty[ab], aph ^ 1, &bfull[g], gph);
+                    if (resident) {
+                        mbar_wait(&acc_empty[ab], aph ^ 1);
+                    } else {
+                        mbar_wait2(&acc_empty[ab], aph ^ 1, &bfull[g], (bpar >> g) & 1);
+                        bpar ^= 1u << g;
+                    }
                     if (prof) { const long long t = clock64(); t_wait_acc += t - t_mark; t_mark = t; }
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
                     const uint32_t bsm0 = smem_u32(bs + g * group_bytes);
                     for (int c = 0; c < C64; ++c) {
                         const int nk = (2 * c + 1 < KC) ? 4 : 2;   // 16-value steps in this unit
-                        if (nt == 0) {
+                        if (i == 0) {
                             // first centroid tile of a row tile: the unit's h1/h2 must have been written
                             const uint32_t k0 = 2 * c, k1 = (2 * c + 1 < KC) ? 2 * c + 1 : 2 * c;
                             mbar_wait2(&a_full[k0], rtn & 1, &a_full[k1], rtn & 1);
@@ -222,8 +239,8 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                                 for (int ks = 0; ks < nk; ++ks)
                                     mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
                             // last centroid tile of the row tile: the first half of h1/h2 may be overwritten
-                            if (nt == NT - 1 && c == C64a - 1) tc_commit_pair(&a_free[0]);
-                            if (nt == NT - 1 && c == C64 - 1) tc_commit_pair(&a_free[1]);   // ... and the second half
+                            if (i == NT - 1 && c == C64a - 1) tc_commit_pair(&a_free[0]);
+                            if (i == NT - 1 && c == C64 - 1) tc_commit_pair(&a_free[1]);   // ... and the second half
                             if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 3]);
                         }
                         __syncwarp();
@@ -308,7 +325,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         const float cmax = p.cstats[0];
         const float unscale = p.cstats[2];
         const bool stages_cn = eg == 0 && r < BN;
-        if (stages_cn) cn_s[r] = p.cnorm[r];
+        if (stages_cn) cn_s[r] = p.cnorm[r];   // row tile 0 starts with centroid tile 0
         asm volatile("bar.sync 1, 256;" ::: "memory");   // both epilogue warpgroups
         uint32_t tile = 0, rtn = 0;
         for (int rt = tile0; rt - (int)rank < num_row_tiles; rt += gridDim.x, ++rtn) {
@@ -320,11 +337,16 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             float best[NS], second[NS], third[NS], bidxf[NS], sidxf[NS];
 #pragma unroll
             for (int q = 0; q < NS; ++q) { best[q] = second[q] = third[q] = inf; bidxf[q] = sidxf[q] = 0.f; }
-            for (int nt = 0; nt < NT; ++nt, ++tile) {
+            for (int i = 0; i < NT; ++i, ++tile) {
+                const int nt = (rtn & 1) ? NT - 1 - i : i;   // serpentine order, see the MMA issuer
                 const uint32_t ab = tile & 1;
                 const float *cn = cn_s + ab * BN;
                 float cn_next = 0.f;
-                if (stages_cn) cn_next = __ldg(p.cnorm + (nt + 1 == NT ? 0 : nt + 1) * BN + r);
+                if (stages_cn) {
+                    // the next tile in the walk (the next row tile starts where this one ends)
+                    const int nn = i + 1 == NT ? nt : ((rtn & 1) ? nt - 1 : nt + 1);
+                    cn_next = __ldg(p.cnorm + nn * BN + r);
+                }
                 mbar_wait(&tile_done[tile & 3], (tile >> 2) & 1);
                 tc_fence_after();
                 if (has_cols && !(p.knockout & 4)) {

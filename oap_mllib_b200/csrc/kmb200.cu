@@ -80,6 +80,7 @@ static void env_overrides() {
 }
 static long long *g_role_prof = nullptr;  // device buffer, allocated by option "role_prof"
 static float *g_dbg_scores = nullptr;  // set only inside kmb200_debug_scores
+static cudaEvent_t *g_main_ev = nullptr;   // [2] events bracketing the main assign kernel of the current iteration (or null)
 
 // ------------------------------------------------------------------------------------ NCCL (dlopen)
 struct NcclApi {
@@ -817,7 +818,12 @@ static int launch_assign_h16(kmb200_table *t) {
     w.two_level_active = false;
     if (g_dbg_scores) return launch_assign_h16_mode<1>(t, false);
     if (!two_level_prepare(t)) return launch_assign_h16_mode<0>(t, false);
+    if (g_main_ev) CU_TRY(cudaEventRecord(g_main_ev[0], t->stream));
     KM_TRY(launch_assign_h16_mode<2>(t, false));
+    if (g_main_ev) {
+        CU_TRY(cudaEventRecord(g_main_ev[1], t->stream));
+        g_main_ev = nullptr;   // recorded: launch_assign() must not bracket the whole phase
+    }
     // The candidate count decides what runs next, so it is read back here: one short host round trip per
     // iteration (the fit loop has one already).  Overflow of the candidate buffer (pathological data: a large
     // share of near-ties) switches this fit to the single-pass scheme, starting with this very assignment.
@@ -1168,7 +1174,7 @@ static int handle_empty_clusters(kmb200_table *t, kmb200_comm *comm, int m, doub
 // ------------------------------------------------------------------------------------ profile
 struct EventPool {
     std::vector<cudaEvent_t> ev;
-    int per_iter = 7;
+    int per_iter = 9;   // 7 phase boundaries + 2 around the main assign kernel
     int cap_iters = 0;
     ~EventPool() {
         for (auto e : ev) cudaEventDestroy(e);
@@ -1225,6 +1231,7 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
     bool converged = false;
     const bool fused = fused_applies(t);
     const int P = g_events.per_iter;
+    std::vector<char> main_timed((size_t)std::max(g_events.cap_iters, 1), 0);
     for (it = 0; it < max_iter && !converged; ++it) {
         const bool timed = it < g_events.cap_iters;
         cudaEvent_t *ev = timed ? &g_events.ev[(size_t)it * P] : nullptr;
@@ -1237,8 +1244,13 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
                 CU_TRY(cudaEventRecord(ev[3], st));
             }
         } else {
+            g_main_ev = timed ? ev + 7 : nullptr;
             KM_TRY(launch_assign(t));
             if (timed) CU_TRY(cudaEventRecord(ev[1], st));
+            // the two-level launcher brackets its main kernel itself (and clears g_main_ev); otherwise the phase IS the kernel
+            const bool main_separate = timed && g_main_ev == nullptr;
+            g_main_ev = nullptr;
+            if (timed) main_timed[it] = main_separate;
             KM_TRY(launch_recheck(t));
             if (timed) CU_TRY(cudaEventRecord(ev[2], st));
             KM_TRY(launch_bucket(t));
@@ -1288,6 +1300,9 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
         g_prof.accumulate_ms += ms[3];
         g_prof.allreduce_ms += ms[4];
         g_prof.finalize_ms += ms[5];
+        float main_ms = ms[0];
+        if (!fused && main_timed[i]) cudaEventElapsedTime(&main_ms, ev[7], ev[8]);
+        g_prof.assign_main_ms += main_ms;
     }
     if (timed_iters > 0) {
         float tot = 0.f;
