@@ -146,7 +146,7 @@ def run_reference(args, rank, world):
             "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "oneDAL/oneCCL/JVM are absent from this image: the reference's own build cannot run; this is "
                     "the CPU restatement of its algorithm on the box's host cores"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------- GPU arm
@@ -341,10 +341,29 @@ def run_ours(args, rank, local_rank, world):
             "full_rechecks_per_step": prof["full_rechecks"] / args.steps,
             "final_cost": cost, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cpu}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line of the contract, on the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
+    # Libraries loaded below print to stdout on their own (NCCL writes its version banner there): keep the real
+    # stdout for the JSON line and send everything else to stderr.
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

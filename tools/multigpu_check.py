@@ -22,8 +22,12 @@ def main():
     m._lib.check(m.lib().kmb200_set_device(local))
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     failures = []
-    cases = [("blobs", 60000, 64, 100, 8), ("blobs", 30011, 256, 300, 6), ("blobs", 200000, 32, 16, 6), ("empty", 0, 0, 0, 5)]
+    cases = [("blobs", 60000, 64, 100, 8), ("blobs", 30011, 256, 300, 6), ("blobs", 200000, 32, 16, 6), ("empty", 0, 0, 0, 5),
+             ("blobs2", 30011, 256, 300, 6)]   # blobs2: two-level bookkeeping forced on (fast pass + near-tie pass)
     for kind, n, d, k, iters in cases:
+        m._lib.check(m.lib().kmb200_set_option(b"two_level", 2.0 if kind == "blobs2" else 1.0))
+        if kind == "blobs2":
+            kind = "blobs"
         if kind == "blobs":
             X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + k)
             init = ko.row_init_centers(X, k)
