@@ -30,7 +30,7 @@ struct PairH16Cfg {
     static constexpr int kA2Col0 = 128;                  // h1 at columns [0, 128), h2 at [128, 256)
     static constexpr int kAccCol0 = 256;
     static constexpr int kTmemCols = 512;
-    static constexpr int kNumBars = 4 /*bfull*/ + 4 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 8 /*a_full*/ + 2 /*a_free*/ + 2 /*acc_empty*/;
+    static constexpr int kNumBars = 4 /*bfull*/ + 4 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 8 /*a_full*/ + 4 /*a_free*/ + 2 /*acc_empty*/;
     static constexpr int kXchgBytes = 2 * 128 * 5 * 4;
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16 + kXchgBytes;
     static constexpr int kBudget = 227 * 1024 - 1024 - kTailBytes;
@@ -79,10 +79,13 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     const int NT = p.num_col_tiles;
     const int KC = p.num_k_chunks;       // 32-value chunks of X, <= 8
     const int C64 = (KC + 1) >> 1;       // 64-value units of B
-    const int C64a = C64 >> 1;           // units [0, C64a) of A are released early in a row tile's last centroid tile
     const int ld64 = C64 * 64;
     const int group_bytes = C64 * Cfg::kBUnitBytes;
     const int RES = NG < NT ? NG : NT;   // centroid tiles still resident in the B groups at a row-tile switch
+    // ld <= 128: h1 / h2 of a row tile take at most 64 columns each, so there are TWO A buffers (row tile parity)
+    // and the transform of the next row tile overlaps this one's MMAs completely -- with few centroid tiles per
+    // row tile (k <= 128: one) the a_free -> transform -> a_full handshake would otherwise be the critical path.
+    const bool ADB = KC <= 4;
     uint8_t *xs = smem;                                  // [XS][128 rows x 128 B], swizzled
     uint8_t *bs = smem + XS * kXStageBytes;              // [NG][C64][g1 chunk | g2 chunk] (this CTA's rows)
     uint8_t *tail = bs + NG * group_bytes;
@@ -93,8 +96,9 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     uint64_t *xfull = bars + 8;       // [8]  X chunk landed
     uint64_t *xempty = bars + 16;     // [8]  X chunk read by its transform warpgroup
     uint64_t *a_full = bars + 24;     // [8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
-    uint64_t *a_free = bars + 32;     // [2]  units [0, C64a) / [C64a, C64) were read for the last time in this row tile (multicast)
-    uint64_t *acc_empty = bars + 34;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
+    uint64_t *a_free = bars + 32;     // [4]  unit c of A was read for the last time in this row tile (multicast);
+                                      //      with two A buffers: [2 * buffer + 1], once per row tile
+    uint64_t *acc_empty = bars + 36;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
     uint32_t *xchg = tmem_slot + 4;   // [2][5][128]
 
@@ -125,8 +129,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             mbar_init(&xempty[s], 4);
             mbar_init(&a_full[s], leader ? 8 : 4);
         }
-        mbar_init(&a_free[0], 1);
-        mbar_init(&a_free[1], 1);
+        for (int s = 0; s < 4; ++s) mbar_init(&a_free[s], 1);
         for (int b = 0; b < 2; ++b) mbar_init(&acc_empty[b], leader ? 16 : 8);   // two epilogue warpgroups per CTA
         fence_mbar_init();
     }
@@ -214,20 +217,28 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
                     const uint32_t bsm0 = smem_u32(bs + g * group_bytes);
+                    const uint32_t abuf = ADB ? (rtn & 1) : 0, apar = ADB ? (rtn >> 1) & 1 : rtn & 1;
                     for (int c = 0; c < C64; ++c) {
                         const int nk = (2 * c + 1 < KC) ? 4 : 2;   // 16-value steps in this unit
                         if (i == 0) {
                             // first centroid tile of a row tile: the unit's h1/h2 must have been written
                             const uint32_t k0 = 2 * c, k1 = (2 * c + 1 < KC) ? 2 * c + 1 : 2 * c;
-                            mbar_wait2(&a_full[k0], rtn & 1, &a_full[k1], rtn & 1);
+                            mbar_wait2(&a_full[abuf * 4 + k0], apar, &a_full[abuf * 4 + k1], apar);
                             tc_fence_after();
                         }
-                        if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
+                        if (prof) {
+                            const long long t = clock64();
+                            t_wait += t - t_mark;
+                            // (the issuer runs ahead of the tensor pipe by the depth of the MMA queue: time spent here
+                            // is not necessarily time the pipe idles)
+                            if (i == 0 && lane == 0 && c >= 1 && c <= 3) p.role_prof[12 + c] += t - t_mark;   // a_full wait per unit
+                            t_mark = t;
+                        }
                         if (elect_one()) {
                             const uint32_t bsm = bsm0 + c * Cfg::kBUnitBytes;
                             const uint64_t d1 = make_kmajor_sw128_desc(bsm);
                             const uint64_t d2 = make_kmajor_sw128_desc(bsm + Cfg::kBHalfBytes);
-                            const uint32_t a1 = tmem_base + c * 32, a2 = a1 + Cfg::kA2Col0;
+                            const uint32_t a1 = tmem_base + abuf * 64 + c * 32, a2 = a1 + Cfg::kA2Col0;
                             // small terms first (knockout 8 / 16: timing experiments only, MMAs left out)
                             if (!(p.knockout & 8)) {
                                 for (int ks = 0; ks < nk; ++ks)
@@ -239,8 +250,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                                 for (int ks = 0; ks < nk; ++ks)
                                     mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
                             // last centroid tile of the row tile: the first half of h1/h2 may be overwritten
-                            if (i == NT - 1 && c == C64a - 1) tc_commit_pair(&a_free[0]);
-                            if (i == NT - 1 && c == C64 - 1) tc_commit_pair(&a_free[1]);   // ... and the second half
+                            // last centroid tile of the row tile: this unit's h1/h2 columns may be overwritten -- released
+                            // unit by unit, so that every chunk of the next row tile has the same lead (the commit ->
+                            // transform -> a_full chain is ~2000 cycles).  Two A buffers: one release per row tile is
+                            // enough, the buffer has a whole row tile of slack.
+                            if (i == NT - 1 && (ADB ? c == C64 - 1 : true)) tc_commit_pair(&a_free[ADB ? abuf * 2 + 1 : c]);
                             if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 3]);
                         }
                         __syncwarp();
@@ -264,9 +278,12 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
         const float sx = p.cstats[3];
         uint32_t rtn = 0;
+        long long t_x = 0, t_free = 0, t_store = 0, t_mark = 0, n_chunks = 0;
+        const bool prof = p.role_prof != nullptr && blockIdx.x < 2 && warp == 4;
         for (int base = base0; base < num_row_tiles; base += gridDim.x, ++rtn) {
             for (int kc = wg; kc < KC; kc += 2) {
                 const uint32_t xi = rtn * KC + kc, xslot = xi % XS;
+                if (prof) t_mark = clock64();
                 mbar_wait(&xfull[xslot], (xi / XS) & 1);
                 const uint8_t *xrow = xs + xslot * kXStageBytes + r * 128;
                 float x[32];
@@ -289,25 +306,42 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     h1[i] = *reinterpret_cast<const uint32_t *>(&a);
                     h2[i] = *reinterpret_cast<const uint32_t *>(&b);
                 }
-                // the previous row tile's last MMAs on this chunk have completed
-                if (rtn > 0) {
-                    // (a barrier of its own, one phase per row tile: this warp gets here a whole row tile early, and
-                    // a parity wait is only meaningful within one phase of the barrier -- tile_done would alias)
-                    mbar_wait(&a_free[(kc >> 1) < C64a ? 0 : 1], (rtn - 1) & 1);
+                // the last MMAs that read this chunk's TMEM columns have completed
+                // (barriers of their own, one phase per use of the buffer: this warp gets here a whole row tile early,
+                // and a parity wait is only meaningful within one phase of its barrier -- tile_done would alias)
+                const uint32_t abuf = ADB ? (rtn & 1) : 0;
+                if (prof) { const long long t = clock64(); t_x += t - t_mark; t_mark = t; }
+                if (ADB) {
+                    if (rtn >= 2) mbar_wait(&a_free[abuf * 2 + 1], ((rtn >> 1) - 1) & 1);
+                } else if (rtn > 0) {
+                    mbar_wait(&a_free[kc >> 1], (rtn - 1) & 1);
                 }
                 tc_fence_after();
+                if (prof) {
+                    const long long t = clock64();
+                    t_free += t - t_mark;
+                    t_mark = t;
+                }
                 if (!(p.knockout & 2)) {
-                    tmem_st16(tmem_base + lane_addr + kc * 16, h1);
-                    tmem_st16(tmem_base + lane_addr + Cfg::kA2Col0 + kc * 16, h2);
+                    tmem_st16(tmem_base + lane_addr + abuf * 64 + kc * 16, h1);
+                    tmem_st16(tmem_base + lane_addr + Cfg::kA2Col0 + abuf * 64 + kc * 16, h2);
                 }
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    if (leader) mbar_arrive(&a_full[kc]);
-                    else mbar_arrive_remote_relaxed(&a_full[kc], 0);
+                    if (leader) mbar_arrive(&a_full[abuf * 4 + kc]);
+                    else mbar_arrive_remote_relaxed(&a_full[abuf * 4 + kc], 0);
                 }
+                if (prof) { const long long t = clock64(); t_store += t - t_mark; ++n_chunks; }
             }
+        }
+        if (prof && lane == 0) {
+            long long *o = p.role_prof + 5 + 4 * blockIdx.x;
+            o[0] = t_x;       // X chunk landed + read + converted
+            o[1] = t_free;    // waiting for the TMEM columns
+            o[2] = t_store;   // tcgen05.st + wait + arrive
+            o[3] = n_chunks;
         }
     } else if ((warp >= 8 && warp < 12) || warp >= 16) {
         // ================================ epilogue ====================================
@@ -337,6 +371,9 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             float best[NS], second[NS], third[NS], bidxf[NS], sidxf[NS];
 #pragma unroll
             for (int q = 0; q < NS; ++q) { best[q] = second[q] = third[q] = inf; bidxf[q] = sidxf[q] = 0.f; }
+            // ||x||^2 of this thread's row (near-tie bound at the end of the row tile): fetched now, off the critical path
+            float xnsq = 0.f;
+            if (eg == 0 && rt * kTileM + r < n_rows) xnsq = __ldg(p.xnorm + rt * kTileM + r);
             for (int i = 0; i < NT; ++i, ++tile) {
                 const int nt = (rtn & 1) ? NT - 1 - i : i;   // serpentine order, see the MMA issuer
                 const uint32_t ab = tile & 1;
@@ -446,7 +483,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 const int row = rt * kTileM + r;
                 if (row < n_rows && !(p.knockout & 4)) {
                     p.labels[row] = mbi;
-                    const float xn = sqrtf(p.xnorm[row]);
+                    const float xn = sqrtf(xnsq);
                     // relative part (accumulation, split residuals) + absolute part (FP16 subnormal range)
                     const float bound = 2.0f * (p.eps * (2.0f * xn * cmax + cmax * cmax) +
                                                 p.sqrt_ld * (p.cstats[4] * 2.0f * cmax + p.cstats[5] * xn));

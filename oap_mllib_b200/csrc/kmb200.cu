@@ -1477,6 +1477,9 @@ extern "C" int kmb200_set_option(const char *name, double value) {
             CU_TRY(cudaMemcpy(h, g_role_prof, sizeof(h), cudaMemcpyDeviceToHost));
             fprintf(stderr, "[kmb200 role_prof] last assign launch, CTA 0 MMA warp: units=%lld cycles/unit: wait_acc=%.1f wait_full=%.1f wait_a=%.1f issue=%.1f\n",
                     h[4], (double)h[0] / h[4], (double)h[1] / h[4], (double)h[2] / h[4], (double)h[3] / h[4]);
+            if (h[13] + h[14] + h[15] > 0)
+                fprintf(stderr, "[kmb200 role_prof] a_full wait at the first centroid tile of a row tile, total cycles for units 1, 2, 3: %lld %lld %lld (tiles %lld)\n",
+                        h[13], h[14], h[15], h[4]);
             for (int c = 0; c < 2; ++c)
                 if (h[5 + 4 * c + 3] > 0)
                     fprintf(stderr, "[kmb200 role_prof] CTA %d transform warp: chunks=%lld cycles/chunk: load+split=%.1f wait_a_empty=%.1f store+arrive=%.1f\n",
