@@ -13,6 +13,7 @@
 #ifndef KMB200_H_
 #define KMB200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -55,6 +56,32 @@ int kmb200_table_create(int64_t rows, int32_t cols, kmb200_table **out);
  * input at abs 1e-6: IntelKMeansSuite.scala:204-218). */
 int kmb200_table_append_f64(kmb200_table *t, int64_t row0, const double *rows, int64_t nrows, int32_t ncols);
 int kmb200_table_append_f32(kmb200_table *t, int64_t row0, const float *rows, int64_t nrows, int32_t ncols);
+/* ---- other input layouts (what feeds the path) ------------------------
+ * The reference accepts whatever `ml.linalg.Vector` rows the DataFrame holds and turns each one into a dense
+ * double[] on the JVM (`row.toArray`, scala/.../ml/util/OneDAL.scala:135-139) before its per-row JNI copy.
+ * Here the conversion happens on the device:
+ *   append_columns_*  columns[c] points to nrows contiguous values of column c (an Arrow primitive array's data
+ *                     buffer, a Spark ColumnVector, a NumPy column): staged column by column, transposed and
+ *                     rounded to FP32 by a tiled kernel;
+ *   append_csr_f64    sparse rows (ml.linalg.SparseVector): indptr has nrows + 1 entries, indices / values are
+ *                     addressed by indptr's values; absent entries are 0; an index outside [0, cols) is an error.
+ * Same row-range rules and FP32 rounding as append_f64. */
+int kmb200_table_append_columns_f64(kmb200_table *t, int64_t row0, const double *const *columns, int64_t nrows,
+                                    int32_t ncols);
+int kmb200_table_append_columns_f32(kmb200_table *t, int64_t row0, const float *const *columns, int64_t nrows,
+                                    int32_t ncols);
+int kmb200_table_append_csr_f64(kmb200_table *t, int64_t row0, int64_t nrows, const int64_t *indptr,
+                                const int32_t *indices, const double *values);
+/* Replaces the reference's counting pass (Utils.getPartitionDims, scala/.../ml/util/Utils.scala:28-49: a whole
+ * Spark job that only counts rows per partition so that tables can be sized): create the table with an upper
+ * bound, append, then cut it to the rows actually appended (1 <= rows <= the rows given at creation).  Drops the
+ * per-(table, k) workspace. */
+int kmb200_table_truncate(kmb200_table *t, int64_t rows);
+/* Page-locked host memory for the caller's staging buffers (the JVM side wraps it in a direct ByteBuffer and
+ * fills it instead of a double[]; replaces the GetPrimitiveArrayCritical + memcpy of native/OneDAL.cpp:50-60):
+ * appends from it run at the PCIe link rate. */
+int kmb200_pinned_alloc(size_t bytes, void **out);
+int kmb200_pinned_free(void *p);
 /* Reads rows back as FP32 (diagnostics / tests; the reference has numericTableToVectors,
  * OneDAL.scala:37-52, for the same purpose). */
 int kmb200_table_read_rows(const kmb200_table *t, int64_t row0, int64_t nrows, float *out);

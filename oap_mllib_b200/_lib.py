@@ -37,6 +37,12 @@ SIGNATURES = {
     "kmb200_table_create": (C.c_int, [C.c_int64, C.c_int32, C.POINTER(_P)]),
     "kmb200_table_append_f64": (C.c_int, [_P, C.c_int64, _P, C.c_int64, C.c_int32]),
     "kmb200_table_append_f32": (C.c_int, [_P, C.c_int64, _P, C.c_int64, C.c_int32]),
+    "kmb200_table_append_columns_f64": (C.c_int, [_P, C.c_int64, _P, C.c_int64, C.c_int32]),
+    "kmb200_table_append_columns_f32": (C.c_int, [_P, C.c_int64, _P, C.c_int64, C.c_int32]),
+    "kmb200_table_append_csr_f64": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P]),
+    "kmb200_table_truncate": (C.c_int, [_P, C.c_int64]),
+    "kmb200_pinned_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
+    "kmb200_pinned_free": (C.c_int, [_P]),
     "kmb200_table_read_rows": (C.c_int, [_P, C.c_int64, C.c_int64, _P]),
     "kmb200_table_rows": (C.c_int64, [_P]),
     "kmb200_table_cols": (C.c_int32, [_P]),

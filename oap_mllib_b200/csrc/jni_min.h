@@ -18,6 +18,9 @@ typedef jobject jarray;
 typedef jarray jdoubleArray;
 typedef jarray jbyteArray;
 typedef jarray jfloatArray;
+typedef jarray jlongArray;
+typedef jarray jintArray;
+typedef jarray jobjectArray;
 typedef void *jfieldID;
 
 #define JNI_ABORT 2
@@ -39,6 +42,7 @@ enum JniSlot {
     kJniGetStringUTFChars = 169,
     kJniReleaseStringUTFChars = 170,
     kJniGetArrayLength = 171,
+    kJniGetObjectArrayElement = 173,
     kJniNewByteArray = 176,
     kJniNewDoubleArray = 182,
     kJniGetByteArrayRegion = 200,

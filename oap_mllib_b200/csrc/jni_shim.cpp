@@ -78,6 +78,48 @@ JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cSetDoubleBatc
     if (rc != 0) throw_runtime(env, kmb200_last_error());
 }
 
+// ---- other input layouts (no counterpart in the reference, which densifies every row on the JVM with
+// Vector.toArray, OneDAL.scala:135-139): see include/kmb200.h, "other input layouts"
+// columns: double[numCols][numRows]
+JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cSetColumnsBatch(JNIEnvPtr env, jobject,
+                                                                                   jlong numTableAddr, jint curRows,
+                                                                                   jobjectArray columns, jint numRows,
+                                                                                   jint numCols) {
+    auto elem = slot<jobject (*)(JNIEnvPtr, jobjectArray, jsize)>(env, kJniGetObjectArrayElement);
+    auto get = slot<void *(*)(JNIEnvPtr, jarray, jboolean *)>(env, kJniGetPrimitiveArrayCritical);
+    auto rel = slot<void (*)(JNIEnvPtr, jarray, void *, jint)>(env, kJniReleasePrimitiveArrayCritical);
+    std::vector<jarray> arrays((size_t)numCols);
+    std::vector<const double *> ptrs((size_t)numCols);
+    for (int c = 0; c < numCols; ++c) arrays[c] = elem(env, columns, c);
+    for (int c = 0; c < numCols; ++c) ptrs[c] = static_cast<const double *>(get(env, arrays[c], nullptr));
+    const int rc = kmb200_table_append_columns_f64(reinterpret_cast<kmb200_table *>(numTableAddr), curRows, ptrs.data(),
+                                                   numRows, numCols);
+    for (int c = numCols - 1; c >= 0; --c) rel(env, arrays[c], const_cast<double *>(ptrs[c]), JNI_ABORT);
+    if (rc != 0) throw_runtime(env, kmb200_last_error());
+}
+
+// sparse rows: indptr long[numRows + 1], indices int[nnz], values double[nnz]
+JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cSetSparseBatch(JNIEnvPtr env, jobject,
+                                                                                  jlong numTableAddr, jint curRows,
+                                                                                  jlongArray indptr, jintArray indices,
+                                                                                  jdoubleArray values, jint numRows) {
+    auto get = slot<void *(*)(JNIEnvPtr, jarray, jboolean *)>(env, kJniGetPrimitiveArrayCritical);
+    auto rel = slot<void (*)(JNIEnvPtr, jarray, void *, jint)>(env, kJniReleasePrimitiveArrayCritical);
+    int64_t *ip = static_cast<int64_t *>(get(env, indptr, nullptr));
+    int32_t *ix = static_cast<int32_t *>(get(env, indices, nullptr));
+    double *va = static_cast<double *>(get(env, values, nullptr));
+    const int rc = kmb200_table_append_csr_f64(reinterpret_cast<kmb200_table *>(numTableAddr), curRows, numRows, ip, ix, va);
+    rel(env, values, va, JNI_ABORT);
+    rel(env, indices, ix, JNI_ABORT);
+    rel(env, indptr, ip, JNI_ABORT);
+    if (rc != 0) throw_runtime(env, kmb200_last_error());
+}
+
+JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cTruncateTable(JNIEnvPtr env, jobject, jlong addr,
+                                                                                 jlong rows) {
+    if (kmb200_table_truncate(reinterpret_cast<kmb200_table *>(addr), rows) != 0) throw_runtime(env, kmb200_last_error());
+}
+
 JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cFreeDataMemory(JNIEnvPtr, jobject, jlong addr) {
     kmb200_table_free(reinterpret_cast<kmb200_table *>(addr));
 }

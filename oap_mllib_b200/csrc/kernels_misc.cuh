@@ -39,6 +39,55 @@ __global__ void convert_rows_kernel(const T *__restrict__ src, float *__restrict
     }
 }
 
+// ---- columnar and sparse ingest
+// src: ncols columns of h values each, column c at src + c * col_stride (Arrow-style contiguous columns staged in
+// device memory); dst: rows [0, h) of the row-major FP32 table.  32 x 32 tiles through shared memory so that both
+// the column reads and the row writes are coalesced.
+template <typename T>
+__global__ void transpose_columns_kernel(const T *__restrict__ src, int64_t col_stride, float *__restrict__ dst,
+                                         int64_t h, int d, int ld) {
+    __shared__ float tile[32][33];
+    const int64_t tiles_r = (h + 31) / 32;
+    const int tiles_c = (d + 31) / 32;
+    for (int64_t tix = blockIdx.x; tix < tiles_r * tiles_c; tix += gridDim.x) {
+        const int64_t r0 = (tix / tiles_c) * 32;
+        const int c0 = (int)(tix % tiles_c) * 32;
+        // threadIdx.x walks ROWS here (contiguous inside a column), threadIdx.y the columns
+        for (int cy = threadIdx.y; cy < 32; cy += blockDim.y) {
+            const int64_t r = r0 + threadIdx.x;
+            const int c = c0 + cy;
+            tile[cy][threadIdx.x] = (r < h && c < d) ? (float)src[(size_t)c * col_stride + r] : 0.f;
+        }
+        __syncthreads();
+        // threadIdx.x walks COLUMNS here (contiguous inside a row)
+        for (int ry = threadIdx.y; ry < 32; ry += blockDim.y) {
+            const int64_t r = r0 + ry;
+            const int c = c0 + threadIdx.x;
+            if (r < h && c < d) dst[r * ld + c] = tile[threadIdx.x][ry];
+        }
+        __syncthreads();
+    }
+}
+
+// CSR rows -> dense FP32 rows (the reference densifies sparse vectors with Vector.toArray on the JVM,
+// scala/.../ml/util/OneDAL.scala:135-139).  dst rows must have been zeroed.  One warp per row; indptr is relative
+// to `base` (the first nonzero of the staged chunk).  An index outside [0, d) sets *bad and is skipped.
+__global__ void csr_scatter_kernel(const int64_t *__restrict__ indptr, int64_t base, const int32_t *__restrict__ indices,
+                                   const double *__restrict__ values, float *__restrict__ dst, int64_t h, int d, int ld,
+                                   int32_t *bad) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp_global = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = warp_global; r < h; r += nwarps) {
+        const int64_t b = indptr[r] - base, e = indptr[r + 1] - base;
+        for (int64_t q = b + lane; q < e; q += 32) {
+            const int32_t c = indices[q];
+            if (c < 0 || c >= d) { *bad = 1; continue; }
+            dst[r * ld + c] = (float)values[q];
+        }
+    }
+}
+
 // ||x_i||^2 for rows [row0, row0 + nrows): G = min(32, ld/4) lanes per row, float4 loads.  Also folds max |x_ij|
 // into *xabs (atomicMax on the bits of a non-negative float).
 __global__ void rownorm_kernel(const float *__restrict__ X, float *__restrict__ xnorm, float *xabs, int64_t row0,

@@ -66,6 +66,7 @@ static int g_h16 = 1;      // 1 = FP16-split pair kernel (assign_pair_h16.cuh) w
 static int g_two_level = 1;  // FP16-split kernel: 1 = fast bookkeeping over all rows + full bookkeeping over the near-tie rows
                              //   (tables of >= kTwoLevelMinRows rows), 2 = always, 0 = never
 static int64_t g_cand_cap = 0;   // candidate-buffer rows (0 = rows / 16); tests shrink it to force the overflow path
+static size_t g_stage_bytes = (size_t)256 << 20;   // device staging buffer of the columnar / sparse / FP64 uploads ("stage_mb")
 static int g_rb_cap = 4;   // experiments: cap on the B-ring group slots of the pair kernel
 static int g_corr = 1;     // pair kernel: 1 = BF16 correction MMAs (2 pass-equivalents), 0 = TF32 corrections (3 passes)
 static int g_cluster = 2;  // 2 = CTA pairs (tcgen05 cta_group::2, centroid tiles split across the pair), 1 = single CTAs
@@ -176,7 +177,8 @@ struct Workspace {
 
 struct kmb200_table {
     int device = 0;
-    int64_t rows = 0;
+    int64_t rows = 0;       // logical rows (kmb200_table_truncate may lower it)
+    int64_t capacity = 0;   // rows allocated at creation
     int d = 0, ld = 0;
     float *X = nullptr;
     float *xnorm = nullptr;
@@ -294,6 +296,7 @@ extern "C" int kmb200_table_create(int64_t rows, int32_t cols, kmb200_table **ou
     kmb200_table *t = new kmb200_table();
     cudaGetDevice(&t->device);
     t->rows = rows;
+    t->capacity = rows;
     t->d = cols;
     t->ld = (cols + 31) / 32 * 32;
     cudaDeviceGetAttribute(&t->num_sms, cudaDevAttrMultiProcessorCount, t->device);
@@ -401,6 +404,137 @@ extern "C" int kmb200_table_append_f64(kmb200_table *t, int64_t row0, const doub
 extern "C" int kmb200_table_append_f32(kmb200_table *t, int64_t row0, const float *rows, int64_t nrows,
                                        int32_t ncols) {
     return append_rows<float>(t, row0, rows, nrows, ncols);
+}
+
+static int ensure_stage(kmb200_table *t, size_t want) {
+    if (t->stage_bytes >= want) return 0;
+    if (t->stage) cudaFree(t->stage);
+    t->stage = nullptr;
+    t->stage_bytes = 0;
+    CU_TRY(cudaMalloc(&t->stage, want));
+    t->stage_bytes = want;
+    return 0;
+}
+
+static int check_append_range(const kmb200_table *t, const void *p, int64_t row0, int64_t nrows, int32_t ncols,
+                              const char *what) {
+    if (!t || !p) return fail(KMB200_ERR_ARG, "%s: null argument", what);
+    if (ncols != t->d) return fail(KMB200_ERR_ARG, "%s: ncols %d != table cols %d", what, ncols, t->d);
+    if (row0 < 0 || nrows < 0 || row0 + nrows > t->rows)
+        return fail(KMB200_ERR_ARG, "%s: rows [%lld, %lld) outside the table of %lld rows", what, (long long)row0,
+                    (long long)(row0 + nrows), (long long)t->rows);
+    return 0;
+}
+
+// Columnar ingest: one contiguous host buffer per column (an Arrow primitive array's data buffer, a Spark
+// ColumnVector, a NumPy column).  Columns are staged in device memory in chunks of rows and transposed there.
+template <typename T>
+static int append_columns(kmb200_table *t, int64_t row0, const T *const *columns, int64_t nrows, int32_t ncols) {
+    KM_TRY(check_append_range(t, columns, row0, nrows, ncols, "table_append_columns"));
+    for (int c = 0; c < ncols; ++c)
+        if (!columns[c]) return fail(KMB200_ERR_ARG, "table_append_columns: column %d is null", c);
+    if (nrows == 0) return 0;
+    CU_TRY(cudaSetDevice(t->device));
+    const size_t row_bytes = (size_t)t->d * sizeof(T);
+    const int64_t chunk = std::max<int64_t>(32, std::min<int64_t>(nrows, (int64_t)(g_stage_bytes / row_bytes)) / 32 * 32);
+    KM_TRY(ensure_stage(t, (size_t)chunk * row_bytes));
+    T *stage = reinterpret_cast<T *>(t->stage);
+    for (int64_t r = 0; r < nrows; r += chunk) {
+        const int64_t h = std::min(chunk, nrows - r);
+        for (int c = 0; c < ncols; ++c)
+            CU_TRY(cudaMemcpyAsync(stage + (size_t)c * chunk, columns[c] + r, (size_t)h * sizeof(T), cudaMemcpyHostToDevice,
+                                   t->stream));
+        const int64_t tiles = ((h + 31) / 32) * ((t->d + 31) / 32);
+        const int blocks = (int)std::min<int64_t>(tiles, (int64_t)t->num_sms * 16);
+        transpose_columns_kernel<T><<<blocks, dim3(32, 8), 0, t->stream>>>(stage, chunk, t->X + (row0 + r) * t->ld, h, t->d,
+                                                                           t->ld);
+        CU_TRY(cudaGetLastError());
+    }
+    KM_TRY(launch_rownorm(t, row0, nrows));
+    CU_TRY(cudaStreamSynchronize(t->stream));
+    return 0;
+}
+extern "C" int kmb200_table_append_columns_f64(kmb200_table *t, int64_t row0, const double *const *columns, int64_t nrows,
+                                               int32_t ncols) {
+    return append_columns<double>(t, row0, columns, nrows, ncols);
+}
+extern "C" int kmb200_table_append_columns_f32(kmb200_table *t, int64_t row0, const float *const *columns, int64_t nrows,
+                                               int32_t ncols) {
+    return append_columns<float>(t, row0, columns, nrows, ncols);
+}
+
+// Sparse rows in CSR form.  indptr has nrows + 1 entries (indptr[0] need not be 0), indices / values are addressed
+// by indptr's values.
+extern "C" int kmb200_table_append_csr_f64(kmb200_table *t, int64_t row0, int64_t nrows, const int64_t *indptr,
+                                           const int32_t *indices, const double *values) {
+    if (!t || !indptr) return fail(KMB200_ERR_ARG, "table_append_csr: null argument");
+    KM_TRY(check_append_range(t, indptr, row0, nrows, t->d, "table_append_csr"));
+    if (nrows == 0) return 0;
+    for (int64_t r = 0; r < nrows; ++r)
+        if (indptr[r + 1] < indptr[r]) return fail(KMB200_ERR_ARG, "table_append_csr: indptr decreases at row %lld", (long long)r);
+    if (indptr[nrows] > indptr[0] && (!indices || !values)) return fail(KMB200_ERR_ARG, "table_append_csr: null indices / values");
+    CU_TRY(cudaSetDevice(t->device));
+    // chunks of rows whose nonzeros fit the staging buffer: [indptr (h+1) int64 | values nnz f64 | indices nnz i32]
+    const int64_t max_nnz = std::max<int64_t>(1024, (int64_t)(g_stage_bytes / 32)), max_rows = std::max<int64_t>(32, (int64_t)(g_stage_bytes / 256));
+    KM_TRY(ensure_stage(t, (size_t)(max_rows + 1) * 8 + (size_t)max_nnz * 12 + 64));
+    uint8_t *sb = reinterpret_cast<uint8_t *>(t->stage);
+    int64_t *d_indptr = reinterpret_cast<int64_t *>(sb);
+    double *d_values = reinterpret_cast<double *>(sb + (size_t)(max_rows + 1) * 8);
+    int32_t *d_indices = reinterpret_cast<int32_t *>(sb + (size_t)(max_rows + 1) * 8 + (size_t)max_nnz * 8);
+    int32_t *d_bad = reinterpret_cast<int32_t *>(sb + (size_t)(max_rows + 1) * 8 + (size_t)max_nnz * 12);
+    CU_TRY(cudaMemsetAsync(d_bad, 0, sizeof(int32_t), t->stream));
+    int64_t r = 0;
+    while (r < nrows) {
+        int64_t h = 0;
+        while (r + h < nrows && h < max_rows && indptr[r + h + 1] - indptr[r] <= max_nnz) ++h;
+        if (h == 0) return fail(KMB200_ERR_LIMIT, "table_append_csr: row %lld has more than %lld nonzeros", (long long)(row0 + r), (long long)max_nnz);
+        const int64_t base = indptr[r], nnz = indptr[r + h] - base;
+        CU_TRY(cudaMemcpyAsync(d_indptr, indptr + r, (size_t)(h + 1) * 8, cudaMemcpyHostToDevice, t->stream));
+        if (nnz > 0) {
+            CU_TRY(cudaMemcpyAsync(d_values, values + base, (size_t)nnz * 8, cudaMemcpyHostToDevice, t->stream));
+            CU_TRY(cudaMemcpyAsync(d_indices, indices + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, t->stream));
+        }
+        CU_TRY(cudaMemsetAsync(t->X + (row0 + r) * t->ld, 0, (size_t)h * t->ld * sizeof(float), t->stream));
+        const int blocks = (int)std::min<int64_t>((h * 32 + 255) / 256, (int64_t)t->num_sms * 16);
+        csr_scatter_kernel<<<blocks, 256, 0, t->stream>>>(d_indptr, base, d_indices, d_values, t->X + (row0 + r) * t->ld, h,
+                                                          t->d, t->ld, d_bad);
+        CU_TRY(cudaGetLastError());
+        CU_TRY(cudaStreamSynchronize(t->stream));   // the staging buffer is reused by the next chunk
+        r += h;
+    }
+    int32_t bad = 0;
+    CU_TRY(cudaMemcpy(&bad, d_bad, sizeof(bad), cudaMemcpyDeviceToHost));
+    KM_TRY(launch_rownorm(t, row0, nrows));
+    CU_TRY(cudaStreamSynchronize(t->stream));
+    if (bad) return fail(KMB200_ERR_ARG, "table_append_csr: a column index is outside [0, %d)", t->d);
+    return 0;
+}
+
+// Callers that do not know the row count in advance (the reference runs a whole Spark job just to count rows per
+// partition, Utils.scala:28-49) create the table with an upper bound and cut it to the rows actually appended.
+extern "C" int kmb200_table_truncate(kmb200_table *t, int64_t rows) {
+    if (!t) return fail(KMB200_ERR_ARG, "table_truncate: null table");
+    if (rows <= 0 || rows > t->capacity)
+        return fail(KMB200_ERR_ARG, "table_truncate: rows must be in [1, %lld] (got %lld)", (long long)t->capacity, (long long)rows);
+    if (rows == t->rows) return 0;
+    CU_TRY(cudaSetDevice(t->device));
+    ws_free(t->ws);   // tensor maps and per-row buffers depend on the row count
+    t->rows = rows;
+    return 0;
+}
+
+// Page-locked host memory for the caller's staging buffers (a JVM wraps it in a direct ByteBuffer): uploads from
+// it run at the link rate and do not pass through the driver's bounce buffers.
+extern "C" int kmb200_pinned_alloc(size_t bytes, void **out) {
+    if (!out || bytes == 0) return fail(KMB200_ERR_ARG, "pinned_alloc: bad argument");
+    KM_TRY(require_device());
+    CU_TRY(cudaHostAlloc(out, bytes, cudaHostAllocPortable));
+    return 0;
+}
+extern "C" int kmb200_pinned_free(void *p) {
+    if (!p) return 0;
+    CU_TRY(cudaFreeHost(p));
+    return 0;
 }
 
 extern "C" int kmb200_table_read_rows(const kmb200_table *t, int64_t row0, int64_t nrows, float *out) {
@@ -1496,6 +1630,9 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         g_fused = value != 0;
     } else if (!strcmp(name, "ss")) {
         g_ss = value != 0;
+    } else if (!strcmp(name, "stage_mb")) {
+        if (value < 1.0 / 1024 || value > 4096) return fail(KMB200_ERR_ARG, "stage_mb must be in [1/1024, 4096]");
+        g_stage_bytes = (size_t)(value * 1048576.0);
     } else if (!strcmp(name, "two_level")) {
         g_two_level = (int)value;
     } else if (!strcmp(name, "cand_cap")) {

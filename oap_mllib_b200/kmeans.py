@@ -58,6 +58,30 @@ class Table:
             rows = np.ascontiguousarray(rows, dtype=np.float64)
             check(lib().kmb200_table_append_f64(self.handle, int(row0), _ptr(rows), rows.shape[0], rows.shape[1]))
 
+    def append_columns(self, row0: int, columns) -> None:
+        """Columnar upload: one contiguous 1-D array per column (Arrow / ColumnVector layout)."""
+        cols = [np.asarray(c) for c in columns]
+        if not cols or any(c.ndim != 1 or c.shape[0] != cols[0].shape[0] for c in cols):
+            raise ValueError("columns must be 1-D arrays of equal length")
+        f32 = all(c.dtype == np.float32 for c in cols)
+        cols = [np.ascontiguousarray(c, dtype=np.float32 if f32 else np.float64) for c in cols]
+        ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
+        fn = lib().kmb200_table_append_columns_f32 if f32 else lib().kmb200_table_append_columns_f64
+        check(fn(self.handle, int(row0), C.cast(ptrs, C.c_void_p), cols[0].shape[0], len(cols)))
+
+    def append_csr(self, row0: int, indptr, indices, values) -> None:
+        """Sparse rows (CSR), densified on the device (the reference calls Vector.toArray per row on the JVM)."""
+        indptr = np.ascontiguousarray(indptr, dtype=np.int64)
+        indices = np.ascontiguousarray(indices, dtype=np.int32)
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        check(lib().kmb200_table_append_csr_f64(self.handle, int(row0), indptr.shape[0] - 1, _ptr(indptr), _ptr(indices),
+                                                _ptr(values)))
+
+    def truncate(self, rows: int) -> None:
+        """Cut a table created with an upper bound to the rows actually appended (no counting pass)."""
+        check(lib().kmb200_table_truncate(self.handle, int(rows)))
+        self.rows = int(rows)
+
     def read_rows(self, row0: int, nrows: int) -> np.ndarray:
         out = np.empty((int(nrows), self.cols), dtype=np.float32)
         check(lib().kmb200_table_read_rows(self.handle, int(row0), int(nrows), _ptr(out)))
@@ -85,20 +109,37 @@ class OneDAL:
 
     @staticmethod
     def vectorsToMergedNumericTables(data, executorNum: int = 1, batch_rows: int = 1 << 20) -> Table:
-        """rows (2-D array, or an iterable of 2-D partitions) -> ONE device table for this executor
+        """rows (2-D array, a CSR matrix, a tuple of 1-D columns, or an iterable of such partitions) -> ONE device
+        table for this executor
         (OneDAL.scala:92-166: per-partition tables merged per executor).  Empty partitions are
         skipped like the reference's filter at :108-113."""
-        parts = [np.asarray(data)] if isinstance(data, np.ndarray) else [np.asarray(p) for p in data]
-        parts = [p for p in parts if p.size > 0]
+        def is_csr(p):
+            return hasattr(p, "indptr") and hasattr(p, "indices") and hasattr(p, "data") and hasattr(p, "shape")
+
+        def is_columns(p):   # a tuple of 1-D columns (Arrow-style); lists stay "partitions of rows"
+            return isinstance(p, tuple) and len(p) > 0 and all(np.ndim(c) == 1 for c in p)
+
+        parts = [data] if isinstance(data, np.ndarray) or is_csr(data) or is_columns(data) else list(data)
+        parts = [p if is_csr(p) or is_columns(p) else np.asarray(p) for p in parts]
+
+        def nrows(p):
+            return len(p[0]) if is_columns(p) else p.shape[0]
+
+        parts = [p for p in parts if nrows(p) > 0]
         if not parts:
             raise ValueError("no rows")
-        cols = parts[0].shape[1]
-        table = Table(sum(p.shape[0] for p in parts), cols)
+        cols = len(parts[0]) if is_columns(parts[0]) else parts[0].shape[1]
+        table = Table(sum(nrows(p) for p in parts), cols)
         r0 = 0
         for p in parts:
-            for b in range(0, p.shape[0], batch_rows):
-                table.append(r0 + b, p[b:b + batch_rows])
-            r0 += p.shape[0]
+            if is_csr(p):        # scipy.sparse.csr_matrix-like: ml.linalg.SparseVector rows
+                table.append_csr(r0, p.indptr, p.indices, p.data)
+            elif is_columns(p):  # columnar batch
+                table.append_columns(r0, p)
+            else:
+                for b in range(0, p.shape[0], batch_rows):
+                    table.append(r0 + b, p[b:b + batch_rows])
+            r0 += nrows(p)
         return table
 
     @staticmethod

@@ -200,3 +200,21 @@ def row_init_centers(X: np.ndarray, k: int) -> np.ndarray:
     n = X.shape[0]
     idx = (np.arange(k, dtype=np.int64) * n) // k
     return np.asarray(X[idx], dtype=np.float64)
+
+
+def dense_rows(data) -> np.ndarray:
+    """What OneDAL.vectorsToMergedNumericTables feeds the native side, restated: every input row becomes a dense
+    double[] (``row.toArray``, scala/.../ml/util/OneDAL.scala:135-139, memcpy'd by cSetDoubleBatch,
+    native/OneDAL.cpp:50-60) in a row-major FP64 table.  Accepts a 2-D array, a tuple of 1-D columns or a CSR
+    matrix (indptr / indices / data / shape)."""
+    if hasattr(data, "indptr"):
+        n, d = data.shape
+        out = np.zeros((n, d), dtype=np.float64)
+        indptr, indices, values = np.asarray(data.indptr), np.asarray(data.indices), np.asarray(data.data)
+        for r in range(n):
+            lo, hi = indptr[r], indptr[r + 1]
+            out[r, indices[lo:hi]] = values[lo:hi]
+        return out
+    if isinstance(data, tuple):
+        return np.stack([np.asarray(c, dtype=np.float64) for c in data], axis=1)
+    return np.ascontiguousarray(data, dtype=np.float64)
