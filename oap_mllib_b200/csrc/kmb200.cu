@@ -608,7 +608,9 @@ extern "C" int kmb200_comm_destroy(kmb200_comm *c) {
 
 // ------------------------------------------------------------------------------------ workspace
 static size_t ld64(int ld) { return (size_t)(ld + 63) / 64 * 64; }
-static int pick_bn(int k) { return k <= 16 ? 16 : k <= 32 ? 32 : k <= 64 ? 64 : 128; }
+// (the CTA-pair kernels need N >= 32: with the FP16-split kernel enabled, k <= 16 is padded to 32 columns rather than
+// sent to the single-CTA kernel)
+static int pick_bn(int k) { return k <= 16 ? (g_h16 ? 32 : 16) : k <= 32 ? 32 : k <= 64 ? 64 : 128; }
 
 template <typename T>
 static int dmalloc(T **p, size_t count) {
@@ -618,7 +620,7 @@ static int dmalloc(T **p, size_t count) {
 
 static int ws_prepare(kmb200_table *t, int k) {
     Workspace &w = t->ws;
-    if (w.k == k && w.cent) return 0;
+    if (w.k == k && w.cent && w.bn == pick_bn(k)) return 0;
     ws_free(w);
     w.k = k;
     w.bn = pick_bn(k);
