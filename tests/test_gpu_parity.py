@@ -357,3 +357,57 @@ def test_full_size_c2_properties(m):
         np.testing.assert_allclose(total, colsum, rtol=1e-9)
     finally:
         t.release()
+
+
+def test_full_size_c3_properties(m):
+    """BASELINE config 3 (the headline, 100M x 256, k = 1000) at full size, through size-independent properties: the
+    cost never increases; cluster sizes sum to N; sum_j count_j * centre_j equals N times the grand mean (obtained
+    independently as the k = 1 fit); and the two bookkeeping schemes of the production kernel (fast pass + near-tie
+    pass vs. single pass) give the SAME cluster sizes and cost -- both are FP64-faithful, so they must."""
+    n, d, k = 100_000_000, 256, 1000
+    free, _ = __import__("torch").cuda.mem_get_info()
+    if free < 125e9:
+        pytest.skip("needs ~115 GB of free device memory")
+    centres = np.random.default_rng(2).uniform(-10, 10, (k, d)).astype(np.float32)
+    t = m.Table(n, d)
+    try:
+        t.fill_blobs(centres, seed=42)
+        idx = (np.arange(k, dtype=np.int64) * n) // k
+        init = np.vstack([t.read_rows(int(i), 1) for i in idx]).astype(np.float64)
+
+        def one_iteration(c, kk):
+            out = np.empty((kk, d))
+            cost, it = C.c_double(), C.c_int32()
+            m._lib.check(m.lib().kmb200_fit(t.handle, None, np.ascontiguousarray(c).ctypes.data_as(C.c_void_p), kk, d,
+                                            -1.0, 1, out.ctypes.data_as(C.c_void_p), C.byref(cost), C.byref(it)))
+            return out, cost.value
+
+        costs, c = [], init
+        for _ in range(3):
+            c_prev = c
+            c, cost = one_iteration(c, k)
+            costs.append(cost)
+        assert all(b <= a * (1 + 1e-12) for a, b in zip(costs, costs[1:])), costs
+
+        def sizes_and_cost(cc):
+            sizes = np.empty(k, np.int64)
+            cost = C.c_double()
+            cc = np.ascontiguousarray(cc, np.float64)
+            m._lib.check(m.lib().kmb200_assign(t.handle, None, cc.ctypes.data_as(C.c_void_p), k, d, None,
+                                               sizes.ctypes.data_as(C.c_void_p), C.byref(cost)))
+            return sizes, cost.value
+
+        sizes, cost = sizes_and_cost(c_prev)
+        assert sizes.sum() == n
+        assert abs(cost - costs[-1]) <= 1e-12 * cost          # the last fit step assigned against c_prev too
+        try:
+            m._lib.check(m.lib().kmb200_set_option(b"two_level", 0.0))
+            sizes1, cost1 = sizes_and_cost(c_prev)
+        finally:
+            m._lib.check(m.lib().kmb200_set_option(b"two_level", 1.0))
+        assert np.array_equal(sizes, sizes1)
+        assert abs(cost - cost1) <= 1e-12 * cost
+        mean, _ = one_iteration(init[:1], 1)                    # k = 1: the centre after one step is the grand mean
+        np.testing.assert_allclose((sizes[:, None] * c).sum(0), n * mean[0], rtol=1e-9, atol=1e-3)
+    finally:
+        t.release()
