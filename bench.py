@@ -269,6 +269,7 @@ def run_ours(args, rank, local_rank, world):
                 "algorithmic_flops_per_launch": flops_per_launch,
                 "tensor_time_in_tf32_passes": 1.5 if h16 else 3.0,   # three FP16 products = 1.5 TF32 passes of tensor time; 3xTF32 on the fallback kernel
                 "main_kernel_ms_per_launch": main_ms,
+                **tf32_measured(achieved),
                 "assign_phase_ms": assign_ms,
                 "hbm_frac_of_step": (n_local * d * 4.0 / (ms_per_step * 1e-3) / 1e9) / peaks["hbm_gbs"]}
     phases = {kk: max_over_ranks(prof[kk]) / args.steps for kk in
@@ -345,6 +346,18 @@ def run_ours(args, rank, local_rank, world):
 
 
 _JSON_FD = None
+
+
+def tf32_measured(achieved):
+    """cuBLAS TF32 on this pool's B200, measured by tools/measure_tf32_peak.py with MEASURED_PEAKS.json's protocol
+    (the driver's file holds bf16 only, so `peak` above stays the 0.5 x bf16 proxy; this is the direct figure)."""
+    path = os.path.join(ROOT, "profiles", "tf32_peak.json")
+    if not os.path.exists(path):
+        return {}
+    with open(path) as f:
+        t = json.load(f)
+    return {"tf32_cublas_sustained_measured": t["tf32_tflops_sustained"],
+            "frac_of_measured_tf32_sustained": achieved / t["tf32_tflops_sustained"]}
 
 
 def emit(line):
