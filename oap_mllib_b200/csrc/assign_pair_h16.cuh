@@ -79,6 +79,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     const int NT = p.num_col_tiles;
     const int KC = p.num_k_chunks;       // 32-value chunks of X, <= 8
     const int C64 = (KC + 1) >> 1;       // 64-value units of B
+    const int C64a = C64 >> 1;           // units [0, C64a) of A are released first in a row tile's last centroid tile
     const int ld64 = C64 * 64;
     const int group_bytes = C64 * Cfg::kBUnitBytes;
     const int RES = NG < NT ? NG : NT;   // centroid tiles still resident in the B groups at a row-tile switch
@@ -96,8 +97,8 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     uint64_t *xfull = bars + 8;       // [8]  X chunk landed
     uint64_t *xempty = bars + 16;     // [8]  X chunk read by its transform warpgroup
     uint64_t *a_full = bars + 24;     // [8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
-    uint64_t *a_free = bars + 32;     // [4]  unit c of A was read for the last time in this row tile (multicast);
-                                      //      with two A buffers: [2 * buffer + 1], once per row tile
+    uint64_t *a_free = bars + 32;     // [4]  units [0, C64a) / [C64a, C64) of A were read for the last time in this row
+                                      //      tile (multicast); with two A buffers: [2 * buffer + 1], once per row tile
     uint64_t *acc_empty = bars + 36;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
     uint32_t *xchg = tmem_slot + 4;   // [2][5][128]
@@ -250,11 +251,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                                 for (int ks = 0; ks < nk; ++ks)
                                     mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
                             // last centroid tile of the row tile: the first half of h1/h2 may be overwritten
-                            // last centroid tile of the row tile: this unit's h1/h2 columns may be overwritten -- released
-                            // unit by unit, so that every chunk of the next row tile has the same lead (the commit ->
-                            // transform -> a_full chain is ~2000 cycles).  Two A buffers: one release per row tile is
-                            // enough, the buffer has a whole row tile of slack.
-                            if (i == NT - 1 && (ADB ? c == C64 - 1 : true)) tc_commit_pair(&a_free[ADB ? abuf * 2 + 1 : c]);
+                            // last centroid tile of the row tile: the h1/h2 columns may be overwritten -- released in two
+                            // halves (a release per unit measured 5 % slower: every commit stalls the issuer for a few
+                            // hundred cycles).  Two A buffers: one release per row tile, the buffer has a row tile of slack.
+                            if (i == NT - 1 && c == C64a - 1 && !ADB) tc_commit_pair(&a_free[0]);
+                            if (i == NT - 1 && c == C64 - 1) tc_commit_pair(&a_free[abuf * 2 + 1]);
                             if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 3]);
                         }
                         __syncwarp();
@@ -314,7 +315,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 if (ADB) {
                     if (rtn >= 2) mbar_wait(&a_free[abuf * 2 + 1], ((rtn >> 1) - 1) & 1);
                 } else if (rtn > 0) {
-                    mbar_wait(&a_free[kc >> 1], (rtn - 1) & 1);
+                    mbar_wait(&a_free[(kc >> 1) < C64a ? 0 : 1], (rtn - 1) & 1);
                 }
                 tc_fence_after();
                 if (prof) {
