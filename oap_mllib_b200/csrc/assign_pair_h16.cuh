@@ -4,12 +4,16 @@
 //   -2 x.c  ~=  (h2.g1 + h1.g2 + h1.g1) / (sx sw)        three kind::f16 products, FP32 accumulation in TMEM
 //
 // FP16 products are exact in FP32, the dropped h2.g2 term is 2^-22 of the main one, so the score error is
-// the same size as the TF32 + BF16-correction scheme's (assign_pair_ss.cuh) at 3/4 of its tensor-pipe time:
-// 3 x (ld/16) MMA instructions per score tile instead of 2 x (ld/8).  Two further differences:
+// smaller than the TF32 + BF16-correction scheme's (assign_pair_ss.cuh) at 3/4 of its tensor-pipe time:
+// 3 x (ld/16) MMA instructions per score tile instead of 2 x (ld/8).  Further differences:
 //  * both A operands (h1, h2) of a whole 128 x ld row tile live in TMEM (2 x ld/2 columns) for ALL the
 //    centroid tiles, so the transform warps touch each X element once per row tile, not once per centroid
-//    tile; the X tile only passes through shared memory;
-//  * the B ring is a plain full/empty ring of [g1 | g2] chunks of 64 K-values (128-byte rows).
+//    tile; the X tile only passes through a small shared-memory ring (ld <= 128: two A buffers);
+//  * the B operand [g1 | g2] of a whole centroid tile is ONE ring entry (2..4 "groups"), synchronised once per
+//    tile; centroid tile nt always lives in group nt % NG and odd row tiles walk the tiles backwards
+//    (serpentine), so the tiles around a row-tile switch are not reloaded;
+//  * two bookkeeping modes (MODE below): the full running (best, runner-up, third) update, or a fast one that
+//    only lists the rows whose two best scores are inside the error bound for a second, full pass.
 // The power-of-two scales keep |h|, |g| < 2^15; values below the FP16 normal range (2^-29 of the largest
 // element) lose relative precision, which the near-tie bound accounts for with an absolute term
 // (cstats[4], cstats[5]); such rows are re-scored in FP64 like every other flagged row.
@@ -58,7 +62,7 @@ struct PairH16Cfg {
 // MODE: 0 = full bookkeeping (best, runner-up with indices, third value -> p.flag_list), 1 = the same plus the score
 // dump of kmb200_debug_scores, 2 = FAST: best with index and the runner-up VALUE only; rows whose gap is inside the
 // bound are appended to p.cand_list and go through a MODE 0 launch over a gathered copy (see launch_assign_h16).
-// p.n_dev (optional): the row count is read from device memory (the gathered copy's length is only known there).
+// p.n_dev (optional): the row count is read from device memory (min with p.n).
 template <int BN, int MODE>
 __global__ void __launch_bounds__(kPairH16Threads, 1)
 assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_b,
