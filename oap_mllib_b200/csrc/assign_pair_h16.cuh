@@ -34,7 +34,7 @@ struct PairH16Cfg {
     static constexpr int kA2Col0 = 128;                  // h1 at columns [0, 128), h2 at [128, 256)
     static constexpr int kAccCol0 = 256;
     static constexpr int kTmemCols = 512;
-    static constexpr int kNumBars = 4 /*bfull*/ + 4 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 8 /*a_full*/ + 4 /*a_free*/ + 2 /*acc_empty*/;
+    static constexpr int kNumBars = 4 /*bfull*/ + 4 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 16 /*a_full*/ + 4 /*a_free*/ + 2 /*acc_empty*/;
     static constexpr int kXchgBytes = 2 * 128 * 5 * 4;
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16 + kXchgBytes;
     static constexpr int kBudget = 227 * 1024 - 1024 - kTailBytes;
@@ -63,12 +63,15 @@ struct PairH16Cfg {
 // dump of kmb200_debug_scores, 2 = FAST: best with index and the runner-up VALUE only; rows whose gap is inside the
 // bound are appended to p.cand_list and go through a MODE 0 launch over a gathered copy (see launch_assign_h16).
 // p.n_dev (optional): the row count is read from device memory (min with p.n).
-template <int BN, int MODE>
+// NP: 3 = the three products above; 1 = h1.g1 ONLY (a third of the tensor work, score error ~2^-10 instead of
+// ~2^-20): the coarse first pass of the cascade in launch_assign_h16, always with MODE 2.  It needs neither h2 nor
+// g2, so h1 is double-buffered in TMEM for every ld <= 256 and only the g1 halves of the B units are loaded.
+template <int BN, int MODE, int NP = 3>
 __global__ void __launch_bounds__(kPairH16Threads, 1)
 assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_b,
                        const AssignParams p) {
     using Cfg = PairH16Cfg<BN>;
-    constexpr bool DBG = MODE == 1, FAST = MODE == 2;
+    constexpr bool DBG = MODE == 1, FAST = MODE == 2, ONE = NP == 1;
     int n_rows = p.n;
     if (p.n_dev != nullptr) {
         const int c = *p.n_dev;
@@ -90,7 +93,8 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     // ld <= 128: h1 / h2 of a row tile take at most 64 columns each, so there are TWO A buffers (row tile parity)
     // and the transform of the next row tile overlaps this one's MMAs completely -- with few centroid tiles per
     // row tile (k <= 128: one) the a_free -> transform -> a_full handshake would otherwise be the critical path.
-    const bool ADB = KC <= 4;
+    const bool ADB = ONE || KC <= 4;
+    const uint32_t abuf_cols = ONE ? 128 : 64;   // columns between the two A buffers
     uint8_t *xs = smem;                                  // [XS][128 rows x 128 B], swizzled
     uint8_t *bs = smem + XS * kXStageBytes;              // [NG][C64][g1 chunk | g2 chunk] (this CTA's rows)
     uint8_t *tail = bs + NG * group_bytes;
@@ -100,10 +104,10 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     uint64_t *tile_done = bars + 4;   // [4]  all MMAs of a centroid tile completed (multicast commit), ring over tiles
     uint64_t *xfull = bars + 8;       // [8]  X chunk landed
     uint64_t *xempty = bars + 16;     // [8]  X chunk read by its transform warpgroup
-    uint64_t *a_full = bars + 24;     // [8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
-    uint64_t *a_free = bars + 32;     // [4]  units [0, C64a) / [C64a, C64) of A were read for the last time in this row
+    uint64_t *a_full = bars + 24;     // [2][8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
+    uint64_t *a_free = bars + 40;     // [4]  units [0, C64a) / [C64a, C64) of A were read for the last time in this row
                                       //      tile (multicast); with two A buffers: [2 * buffer + 1], once per row tile
-    uint64_t *acc_empty = bars + 36;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
+    uint64_t *acc_empty = bars + 44;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
     uint32_t *xchg = tmem_slot + 4;   // [2][5][128]
 
@@ -133,6 +137,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             mbar_init(&xfull[s], 1);
             mbar_init(&xempty[s], 4);
             mbar_init(&a_full[s], leader ? 8 : 4);
+            mbar_init(&a_full[8 + s], leader ? 8 : 4);
         }
         for (int s = 0; s < 4; ++s) mbar_init(&a_free[s], 1);
         for (int b = 0; b < 2; ++b) mbar_init(&acc_empty[b], leader ? 16 : 8);   // two epilogue warpgroups per CTA
@@ -169,10 +174,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     if (p.knockout & 1) {   // timing experiments only: no B traffic
                         if (leader) mbar_arrive(&bfull[g]);
                     } else {
-                        if (leader) mbar_arrive_expect_tx(&bfull[g], 2 * group_bytes);
+                        if (leader) mbar_arrive_expect_tx(&bfull[g], ONE ? group_bytes : 2 * group_bytes);
                         for (int c = 0; c < C64; ++c) {
                             tma_load_2d_pair(&tm_b, &bfull[g], st + c * Cfg::kBUnitBytes, c * 64, brow);
-                            tma_load_2d_pair(&tm_b, &bfull[g], st + c * Cfg::kBUnitBytes + Cfg::kBHalfBytes, ld64 + c * 64, brow);
+                            if constexpr (!ONE)
+                                tma_load_2d_pair(&tm_b, &bfull[g], st + c * Cfg::kBUnitBytes + Cfg::kBHalfBytes, ld64 + c * 64, brow);
                         }
                     }
                 }
@@ -228,7 +234,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                         if (i == 0) {
                             // first centroid tile of a row tile: the unit's h1/h2 must have been written
                             const uint32_t k0 = 2 * c, k1 = (2 * c + 1 < KC) ? 2 * c + 1 : 2 * c;
-                            mbar_wait2(&a_full[abuf * 4 + k0], apar, &a_full[abuf * 4 + k1], apar);
+                            mbar_wait2(&a_full[abuf * 8 + k0], apar, &a_full[abuf * 8 + k1], apar);
                             tc_fence_after();
                         }
                         if (prof) {
@@ -243,7 +249,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                             const uint32_t bsm = bsm0 + c * Cfg::kBUnitBytes;
                             const uint64_t d1 = make_kmajor_sw128_desc(bsm);
                             const uint64_t d2 = make_kmajor_sw128_desc(bsm + Cfg::kBHalfBytes);
-                            const uint32_t a1 = tmem_base + abuf * 64 + c * 32, a2 = a1 + Cfg::kA2Col0;
+                            const uint32_t a1 = tmem_base + abuf * abuf_cols + c * 32, a2 = a1 + Cfg::kA2Col0;
+                            if constexpr (ONE) {
+                                for (int ks = 0; ks < nk; ++ks)
+                                    mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
+                            } else {
                             // small terms first (knockout 8 / 16: timing experiments only, MMAs left out)
                             if (!(p.knockout & 8)) {
                                 for (int ks = 0; ks < nk; ++ks)
@@ -254,6 +264,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                             if (!(p.knockout & 16))
                                 for (int ks = 0; ks < nk; ++ks)
                                     mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                            }
                             // last centroid tile of the row tile: the first half of h1/h2 may be overwritten
                             // last centroid tile of the row tile: the h1/h2 columns may be overwritten -- released in two
                             // halves (a release per unit measured 5 % slower: every commit stalls the issuer for a few
@@ -328,15 +339,15 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     t_mark = t;
                 }
                 if (!(p.knockout & 2)) {
-                    tmem_st16(tmem_base + lane_addr + abuf * 64 + kc * 16, h1);
-                    tmem_st16(tmem_base + lane_addr + Cfg::kA2Col0 + abuf * 64 + kc * 16, h2);
+                    tmem_st16(tmem_base + lane_addr + abuf * abuf_cols + kc * 16, h1);
+                    if constexpr (!ONE) tmem_st16(tmem_base + lane_addr + Cfg::kA2Col0 + abuf * 64 + kc * 16, h2);
                 }
                 tmem_wait_st();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
-                    if (leader) mbar_arrive(&a_full[abuf * 4 + kc]);
-                    else mbar_arrive_remote_relaxed(&a_full[abuf * 4 + kc], 0);
+                    if (leader) mbar_arrive(&a_full[abuf * 8 + kc]);
+                    else mbar_arrive_remote_relaxed(&a_full[abuf * 8 + kc], 0);
                 }
                 if (prof) { const long long t = clock64(); t_store += t - t_mark; ++n_chunks; }
             }

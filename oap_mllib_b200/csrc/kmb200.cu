@@ -67,6 +67,9 @@ static int g_two_level = 1;  // FP16-split kernel: 1 = fast bookkeeping over all
                              //   (tables of >= kTwoLevelMinRows rows), 2 = always, 0 = never
 static int64_t g_cand_cap = 0;   // candidate-buffer rows (0 = rows / 16); tests shrink it to force the overflow path
 static size_t g_stage_bytes = (size_t)256 << 20;   // device staging buffer of the columnar / sparse / FP64 uploads ("stage_mb")
+static int g_dbg_products = 3;   // kmb200_debug_scores: 1 = dump the coarse one-product scores ("dbg_products")
+static int g_cascade = 1;    // FP16-split kernel: 1 = coarse one-product pass first (needs the two-level scheme), 0 = off
+static double g_cand1_frac = 0.3;   // rows of the coarse pass's copy, as a fraction of the table ("cand1_frac")
 static int g_rb_cap = 4;   // experiments: cap on the B-ring group slots of the pair kernel
 static int g_corr = 1;     // pair kernel: 1 = BF16 correction MMAs (2 pass-equivalents), 0 = TF32 corrections (3 passes)
 static int g_cluster = 2;  // 2 = CTA pairs (tcgen05 cta_group::2, centroid tiles split across the pair), 1 = single CTAs
@@ -163,6 +166,16 @@ struct Workspace {
     int32_t *labels_c = nullptr;      // [cand_cap] their labels (scattered back after the re-check)
     int64_t cand_cap = 0;
     CUtensorMap tm_xc;
+    // cascade: the rows the coarse one-product pass could not decide (a larger copy, one level above xc)
+    float *xc1 = nullptr;             // [cand1_cap x ld]
+    float *xnc1 = nullptr;
+    int32_t *cand1_list = nullptr;
+    int32_t *labels_c1 = nullptr;
+    int64_t cand1_cap = 0;
+    CUtensorMap tm_xc1;
+    bool cascade_off = false;         // the coarse pass left too many rows undecided once in this fit: not used again
+    int recheck_level = 0;            // set by launch_assign: the lists index 0 = the table, 1 = xc1, 2 = xc
+    bool scatter1 = false, scatter2 = false;   // labels_c -> (labels_c1 | labels) via cand_list; labels_c1 -> labels via cand1_list
     bool two_level_active = false;    // set by launch_assign for the launch_recheck that follows
     bool two_level_off = false;       // the candidate buffer overflowed once in this fit: full bookkeeping from then on
     // pinned host mirror read once per iteration
@@ -171,6 +184,7 @@ struct Workspace {
         int32_t flag_count;
         int32_t full_count;
         int32_t cand_count;
+        int32_t cand1_count;
         double cost;
     } *host = nullptr;
 };
@@ -193,7 +207,7 @@ struct kmb200_table {
 static void ws_free(Workspace &w) {
     void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.b16, w.cnorm64, w.rc_score, w.rc_idx, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
                     w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage,
-                    w.xc, w.xnc, w.cand_list, w.labels_c};
+                    w.xc, w.xnc, w.cand_list, w.labels_c, w.xc1, w.xnc1, w.cand1_list, w.labels_c1};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (w.host) cudaFreeHost(w.host);
@@ -879,12 +893,55 @@ static bool two_level_prepare(kmb200_table *t) {
     return true;
 }
 
-// MODE 0 / 1 (score dump) over the table, MODE 2 (fast) over the table, or MODE 0 over the gathered candidates (cand).
-template <int BN, int MODE>
-static int launch_assign_h16_bn(kmb200_table *t, bool cand) {
+// (Re)allocates the copy that holds the rows the coarse pass leaves undecided; false = no cascade.
+static bool cascade_prepare(kmb200_table *t) {
+    Workspace &w = t->ws;
+    if (!g_cascade || w.cascade_off) return false;
+    int64_t cap = (int64_t)(g_cand1_frac * (double)t->rows);
+    cap = std::max<int64_t>((cap + kTileM - 1) / kTileM * kTileM, 2 * kTileM);
+    if (w.cand1_cap == cap && w.xc1) return true;
+    for (void *ptr : {(void *)w.xc1, (void *)w.xnc1, (void *)w.cand1_list, (void *)w.labels_c1})
+        if (ptr) cudaFree(ptr);
+    w.xc1 = nullptr; w.xnc1 = nullptr; w.cand1_list = nullptr; w.labels_c1 = nullptr;
+    w.cand1_cap = 0;
+    bool ok = cudaMalloc(reinterpret_cast<void **>(&w.xc1), (size_t)cap * t->ld * sizeof(float)) == cudaSuccess &&
+              cudaMalloc(reinterpret_cast<void **>(&w.xnc1), (size_t)cap * sizeof(float)) == cudaSuccess &&
+              cudaMalloc(reinterpret_cast<void **>(&w.cand1_list), (size_t)cap * sizeof(int32_t)) == cudaSuccess &&
+              cudaMalloc(reinterpret_cast<void **>(&w.labels_c1), (size_t)cap * sizeof(int32_t)) == cudaSuccess;
+    if (ok) ok = make_map(&w.tm_xc1, w.xc1, (uint64_t)cap, (uint64_t)t->ld, kTileM) == 0;
+    if (!ok) {   // not enough memory left: the two-level scheme alone needs a fifth of it
+        cudaGetLastError();
+        for (void *ptr : {(void *)w.xc1, (void *)w.xnc1, (void *)w.cand1_list, (void *)w.labels_c1})
+            if (ptr) cudaFree(ptr);
+        w.xc1 = nullptr; w.xnc1 = nullptr; w.cand1_list = nullptr; w.labels_c1 = nullptr;
+        w.cascade_off = true;
+        return false;
+    }
+    w.cand1_cap = cap;
+    return true;
+}
+
+// What one launch of the FP16-split kernel reads and writes: the table itself or one of the gathered copies.
+struct H16Src {
+    const CUtensorMap *tm;    // rows to score
+    const float *xnorm;
+    int32_t *labels;
+    int64_t rows;
+    int32_t *cand_list;       // MODE 2: where the undecided rows are listed
+    int32_t *cand_count;
+    int64_t cand_cap;
+    bool prof;                // role counters (diagnostics) for this launch
+};
+
+// Score error of the one-product pass: both operands rounded to 11 bits (2^-11 each, relative to |x||w| element
+// by element, so 2^-10 of 2|x||c| by Cauchy-Schwarz), ld/16 accumulator updates, FP32 norm and final FMA.
+static float score_eps_h16_one(int ld) { return (float)(g_eps_scale * (ldexp(1.0, -10) + ldexp(ld / 16.0 + 32.0, -24))); }
+
+template <int BN, int MODE, int NP>
+static int launch_assign_h16_bn(kmb200_table *t, const H16Src &src) {
     Workspace &w = t->ws;
     using Cfg = PairH16Cfg<BN>;
-    auto kernel = assign_pair_h16_kernel<BN, MODE>;
+    auto kernel = assign_pair_h16_kernel<BN, MODE, NP>;
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
     const int smem = Cfg::smem_bytes(kc);
@@ -892,31 +949,30 @@ static int launch_assign_h16_bn(kmb200_table *t, bool cand) {
         CU_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set[t->device & 63] = true;
     }
-    const int64_t rows = cand ? (int64_t)w.host->cand_count : t->rows;
     AssignParams p;
     p.cnorm = w.cnorm;
-    p.xnorm = cand ? w.xnc : t->xnorm;
+    p.xnorm = src.xnorm;
     p.cstats = w.cstats;
-    p.labels = cand ? w.labels_c : w.labels;
+    p.labels = src.labels;
     p.flag_count = w.flag_count;
     p.flag_list = w.flag_list;
     p.flag_cap = (int32_t)t->rows;
-    p.n = (int32_t)rows;
-    p.num_row_tiles = (int32_t)((rows + kTileM - 1) / kTileM);
+    p.n = (int32_t)src.rows;
+    p.num_row_tiles = (int32_t)((src.rows + kTileM - 1) / kTileM);
     p.num_col_tiles = w.kpad / BN;
     p.num_k_chunks = kc;
     p.stages = Cfg::x_slots(kc) | (Cfg::b_groups(kc) << 8);
     p.passes = 3;
-    p.eps = score_eps_h16(t->ld);
+    p.eps = NP == 1 ? score_eps_h16_one(t->ld) : score_eps_h16(t->ld);
     p.dbg_scores = g_dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;
-    p.role_prof = cand ? nullptr : g_role_prof;
+    p.role_prof = src.prof ? g_role_prof : nullptr;
     p.sqrt_ld = sqrtf((float)t->ld);
     p.n_dev = nullptr;
-    p.cand_list = w.cand_list;
-    p.cand_count = w.flag_count + 2;
-    p.cand_cap = (int32_t)w.cand_cap;
+    p.cand_list = src.cand_list;
+    p.cand_count = src.cand_count;
+    p.cand_cap = (int32_t)src.cand_cap;
     const int pairs = std::min((p.num_row_tiles + 1) / 2, t->num_sms / 2);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(pairs * 2));
@@ -930,53 +986,110 @@ static int launch_assign_h16_bn(kmb200_table *t, bool cand) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    CU_TRY(cudaLaunchKernelEx(&cfg, kernel, cand ? w.tm_xc : w.tm_x, w.tm_b16_half, p));
+    CU_TRY(cudaLaunchKernelEx(&cfg, kernel, *src.tm, w.tm_b16_half, p));
     g_prof.kernel_launches++;
     return 0;
 }
 
-template <int MODE>
-static int launch_assign_h16_mode(kmb200_table *t, bool cand) {
+template <int MODE, int NP>
+static int launch_assign_h16_mode(kmb200_table *t, const H16Src &src) {
     switch (t->ws.bn) {
-        case 32: return launch_assign_h16_bn<32, MODE>(t, cand);
-        case 64: return launch_assign_h16_bn<64, MODE>(t, cand);
-        default: return launch_assign_h16_bn<128, MODE>(t, cand);
+        case 32: return launch_assign_h16_bn<32, MODE, NP>(t, src);
+        case 64: return launch_assign_h16_bn<64, MODE, NP>(t, src);
+        default: return launch_assign_h16_bn<128, MODE, NP>(t, src);
     }
 }
 
-// Two-level bookkeeping: the epilogue's running (best, runner-up, third) update is 11 instructions per score and a
-// quarter of the kernel's energy at the headline shape, but only the ~1 % of rows whose two best scores are inside
-// the error bound need more than the winner.  So: a FAST pass over all rows (6 instructions per score) that lists
-// those rows, a gather of the listed rows into a dense copy, and a full-bookkeeping pass over the copy whose
-// (row, runner-up) / (row, all) lists feed the FP64 re-check as before (launch_recheck scatters the labels back).
+static int read_count(kmb200_table *t, int32_t *host_dst, const int32_t *dev_src) {
+    CU_TRY(cudaMemcpyAsync(host_dst, dev_src, sizeof(int32_t), cudaMemcpyDeviceToHost, t->stream));
+    CU_TRY(cudaStreamSynchronize(t->stream));
+    return 0;
+}
+
+static int launch_gather(kmb200_table *t, const float *X, const float *xnorm, const int32_t *list, const int32_t *count,
+                         int64_t cap, float *xc, float *xnc) {
+    gather_rows_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(X, xnorm, list, count, (int32_t)cap, t->ld, xc, xnc);
+    CU_TRY(cudaGetLastError());
+    g_prof.kernel_launches++;
+    return 0;
+}
+
+// Near-tie bookkeeping over `src` (the table or the coarse pass's copy, level 0 / 1): either one full-bookkeeping
+// pass, or -- two-level scheme -- a FAST pass (winner + runner-up value, 6 instead of 11 instructions per score) that
+// lists the ~1 % of rows whose two best scores are inside the error bound, a gather of those rows into a dense copy
+// (xc) and the full-bookkeeping pass over the copy only.  Leaves the (row, runner-up) / (row, all) lists for
+// launch_recheck and records which copy they index.
+static int launch_h16_fine(kmb200_table *t, const H16Src &src, const float *srcX, int level, bool two_level, bool bracket) {
+    Workspace &w = t->ws;
+    if (!two_level) {
+        w.recheck_level = level;
+        return launch_assign_h16_mode<0, 3>(t, src);
+    }
+    H16Src fast = src;
+    fast.cand_list = w.cand_list;
+    fast.cand_count = w.flag_count + 2;
+    fast.cand_cap = w.cand_cap;
+    if (bracket && g_main_ev) CU_TRY(cudaEventRecord(g_main_ev[0], t->stream));
+    KM_TRY((launch_assign_h16_mode<2, 3>(t, fast)));
+    if (bracket && g_main_ev) {
+        CU_TRY(cudaEventRecord(g_main_ev[1], t->stream));
+        g_main_ev = nullptr;   // recorded: the caller must not bracket the whole phase
+    }
+    // The candidate count decides what runs next, so it is read back here: one short host round trip.  Overflow of
+    // the candidate buffer (a large share of near-ties) switches this fit to the single-pass scheme on the spot.
+    KM_TRY(read_count(t, &w.host->cand_count, w.flag_count + 2));
+    if ((int64_t)w.host->cand_count > w.cand_cap) {
+        w.two_level_off = true;
+        CU_TRY(cudaMemsetAsync(w.flag_count, 0, 3 * sizeof(int32_t), t->stream));   // [3] (the coarse count) stays
+        w.recheck_level = level;
+        return launch_assign_h16_mode<0, 3>(t, src);
+    }
+    w.recheck_level = 2;
+    w.scatter2 = true;
+    if (w.host->cand_count == 0) return 0;   // no near-ties at all: the lists stay empty
+    KM_TRY(launch_gather(t, srcX, src.xnorm, w.cand_list, w.flag_count + 2, w.cand_cap, w.xc, w.xnc));
+    H16Src fine = {&w.tm_xc, w.xnc, w.labels_c, (int64_t)w.host->cand_count, nullptr, w.flag_count + 2, 0, false};
+    return launch_assign_h16_mode<0, 3>(t, fine);
+}
+
+// The assign phase on the FP16-split kernel.  Cascade (tables of >= 2^18 rows): a COARSE pass over all rows with
+// the h1.g1 product only (a third of the tensor work; error bound 2^-10) decides every row whose two best scores
+// are further apart than that bound -- 80 % of them on the benchmark's blob data -- and lists the rest; those rows
+// are gathered into a dense copy and go through the three-product kernel (two-level bookkeeping as above), and
+// what that cannot decide goes to the FP64 re-check.  Every row is still scored against every centre on the
+// tensor cores, and the labels are the FP64 arg-min whatever path a row takes.  If the coarse pass leaves more
+// than cand1_frac (30 %) of the rows undecided the fit drops it and continues with the two-level scheme.
 static int launch_assign_h16(kmb200_table *t) {
     Workspace &w = t->ws;
     w.two_level_active = false;
-    if (g_dbg_scores) return launch_assign_h16_mode<1>(t, false);
-    if (!two_level_prepare(t)) return launch_assign_h16_mode<0>(t, false);
-    if (g_main_ev) CU_TRY(cudaEventRecord(g_main_ev[0], t->stream));
-    KM_TRY(launch_assign_h16_mode<2>(t, false));
-    if (g_main_ev) {
-        CU_TRY(cudaEventRecord(g_main_ev[1], t->stream));
-        g_main_ev = nullptr;   // recorded: launch_assign() must not bracket the whole phase
-    }
-    // The candidate count decides what runs next, so it is read back here: one short host round trip per
-    // iteration (the fit loop has one already).  Overflow of the candidate buffer (pathological data: a large
-    // share of near-ties) switches this fit to the single-pass scheme, starting with this very assignment.
-    CU_TRY(cudaMemcpyAsync(&w.host->cand_count, w.flag_count + 2, sizeof(int32_t), cudaMemcpyDeviceToHost, t->stream));
-    CU_TRY(cudaStreamSynchronize(t->stream));
-    if ((int64_t)w.host->cand_count > w.cand_cap) {
-        w.two_level_off = true;
+    w.recheck_level = 0;
+    w.scatter1 = w.scatter2 = false;
+    H16Src table = {&w.tm_x, t->xnorm, w.labels, t->rows, nullptr, w.flag_count + 2, 0, true};
+    if (g_dbg_scores) return g_dbg_products == 1 ? launch_assign_h16_mode<1, 1>(t, table) : launch_assign_h16_mode<1, 3>(t, table);
+    const bool two_level = two_level_prepare(t);
+    if (two_level && cascade_prepare(t)) {
+        H16Src coarse = table;
+        coarse.cand_list = w.cand1_list;
+        coarse.cand_count = w.flag_count + 3;
+        coarse.cand_cap = w.cand1_cap;
+        cudaEvent_t *ev = g_main_ev;
+        if (ev) CU_TRY(cudaEventRecord(ev[0], t->stream));
+        KM_TRY((launch_assign_h16_mode<2, 1>(t, coarse)));
+        if (ev) CU_TRY(cudaEventRecord(ev[1], t->stream));
+        KM_TRY(read_count(t, &w.host->cand1_count, w.flag_count + 3));
+        if ((int64_t)w.host->cand1_count <= w.cand1_cap) {
+            g_main_ev = nullptr;   // bracketed above
+            w.scatter1 = true;
+            w.recheck_level = 1;
+            if (w.host->cand1_count == 0) return 0;
+            KM_TRY(launch_gather(t, t->X, t->xnorm, w.cand1_list, w.flag_count + 3, w.cand1_cap, w.xc1, w.xnc1));
+            H16Src mid = {&w.tm_xc1, w.xnc1, w.labels_c1, (int64_t)w.host->cand1_count, nullptr, w.flag_count + 2, 0, false};
+            return launch_h16_fine(t, mid, w.xc1, 1, !w.two_level_off, false);
+        }
+        w.cascade_off = true;   // too many undecided rows: the coarse pass is not worth its time on this data
         CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
-        return launch_assign_h16_mode<0>(t, false);
     }
-    w.two_level_active = true;
-    if (w.host->cand_count == 0) return 0;   // no near-ties at all: the lists stay empty
-    gather_rows_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, t->xnorm, w.cand_list, w.flag_count + 2,
-                                                              (int32_t)w.cand_cap, t->ld, w.xc, w.xnc);
-    CU_TRY(cudaGetLastError());
-    g_prof.kernel_launches++;
-    return launch_assign_h16_mode<0>(t, true);
+    return launch_h16_fine(t, table, t->X, 0, two_level && !w.two_level_off, true);
 }
 
 static int launch_assign_pair(kmb200_table *t, bool *applicable) {
@@ -1114,10 +1227,9 @@ static int launch_assign(kmb200_table *t) {
 static int launch_recheck(kmb200_table *t) {
     Workspace &w = t->ws;
     if (g_force_simt) return 0;
-    // two-level scheme: the lists index the gathered copy of the candidate rows
-    const bool tl = w.two_level_active;
-    const float *X = tl ? w.xc : t->X;
-    int32_t *labels = tl ? w.labels_c : w.labels;
+    // the lists index the table or one of the gathered copies (launch_assign_h16)
+    const float *X = w.recheck_level == 2 ? w.xc : w.recheck_level == 1 ? w.xc1 : t->X;
+    int32_t *labels = w.recheck_level == 2 ? w.labels_c : w.recheck_level == 1 ? w.labels_c1 : w.labels;
     recheck_kernel<<<t->num_sms * 4, 256, 0, t->stream>>>(X, w.cent, w.flag_list, w.flag_count, (int32_t)t->rows,
                                                          t->rows, w.k, t->ld, labels);
     CU_TRY(cudaGetLastError());
@@ -1129,9 +1241,15 @@ static int launch_recheck(kmb200_table *t) {
                                                   w.rc_idx, labels);
     CU_TRY(cudaGetLastError());
     g_prof.kernel_launches += 3;
-    if (tl) {
+    if (w.scatter2 && w.recheck_level == 2) {   // decided labels of the near-tie copy -> the level they were gathered from
         scatter_labels_kernel<<<t->num_sms * 2, 256, 0, t->stream>>>(w.cand_list, w.flag_count + 2, (int32_t)w.cand_cap,
-                                                                    w.labels_c, w.labels);
+                                                                    w.labels_c, w.scatter1 ? w.labels_c1 : w.labels);
+        CU_TRY(cudaGetLastError());
+        g_prof.kernel_launches++;
+    }
+    if (w.scatter1) {   // labels of the coarse pass's undecided rows -> the table's labels
+        scatter_labels_kernel<<<t->num_sms * 2, 256, 0, t->stream>>>(w.cand1_list, w.flag_count + 3, (int32_t)w.cand1_cap,
+                                                                    w.labels_c1, w.labels);
         CU_TRY(cudaGetLastError());
         g_prof.kernel_launches++;
     }
@@ -1361,6 +1479,7 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
     KM_TRY(launch_split(t));
     KM_TRY(g_events.ensure(max_iter));
     w.two_level_off = false;
+    w.cascade_off = false;
 
     double cost = 0.0;
     int it = 0;
@@ -1462,6 +1581,7 @@ extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *c
     cudaEvent_t *ev = &g_events.ev[0];
     KM_TRY(upload_centers(t, centers, k, d));
     w.two_level_off = false;
+    w.cascade_off = false;
     KM_TRY(launch_split(t));
     const bool fused = fused_applies(t);
     CU_TRY(cudaEventRecord(ev[0], st));
@@ -1635,6 +1755,13 @@ extern "C" int kmb200_set_option(const char *name, double value) {
     } else if (!strcmp(name, "stage_mb")) {
         if (value < 1.0 / 1024 || value > 4096) return fail(KMB200_ERR_ARG, "stage_mb must be in [1/1024, 4096]");
         g_stage_bytes = (size_t)(value * 1048576.0);
+    } else if (!strcmp(name, "dbg_products")) {
+        g_dbg_products = value == 1 ? 1 : 3;
+    } else if (!strcmp(name, "cascade")) {
+        g_cascade = value != 0;
+    } else if (!strcmp(name, "cand1_frac")) {
+        if (!(value > 0.0 && value <= 1.0)) return fail(KMB200_ERR_ARG, "cand1_frac must be in (0, 1]");
+        g_cand1_frac = value;
     } else if (!strcmp(name, "two_level")) {
         g_two_level = (int)value;
     } else if (!strcmp(name, "cand_cap")) {

@@ -226,6 +226,35 @@ def test_fp16_split_scales_and_wide_column_ranges(m, scale, colscale):
     check_fit_parity(m, X, ko.row_init_centers(X, k), tol=0.0, max_iter=4)
 
 
+def test_coarse_pass_score_error_is_inside_its_bound(m):
+    """The one-product pass of the cascade (h1.g1 only): its scores against FP64, normalised like the kernel's
+    near-tie bound, must sit inside 2^-10 + 2^-24 (ld/16 + 32)."""
+    for n, d, k in [(2048, 256, 1000), (2048, 64, 100)]:
+        X, _, _ = ko.gaussian_blobs(n, d, k, seed=d)
+        Cn = ko.row_init_centers(X, k)
+        X64 = X.astype(np.float64)
+        t = m.OneDAL.vectorsToMergedNumericTables(X)
+        try:
+            m._lib.check(m.lib().kmb200_set_option(b"dbg_products", 1.0))
+            kpad = C.c_int32()
+            Cc = np.ascontiguousarray(Cn)
+            m._lib.check(m.lib().kmb200_debug_scores(t.handle, Cc.ctypes.data_as(C.c_void_p), k, d, None, C.byref(kpad)))
+            sc = np.empty((n, kpad.value), np.float32)
+            m._lib.check(m.lib().kmb200_debug_scores(t.handle, Cc.ctypes.data_as(C.c_void_p), k, d,
+                                                     sc.ctypes.data_as(C.c_void_p), C.byref(kpad)))
+        finally:
+            m._lib.check(m.lib().kmb200_set_option(b"dbg_products", 3.0))
+            t.release()
+        exact = (Cn ** 2).sum(1)[None, :] - 2.0 * X64 @ Cn.T
+        cmax = np.sqrt((Cn ** 2).sum(1).max())
+        scale = 2.0 * np.sqrt((X64 ** 2).sum(1))[:, None] * cmax + cmax ** 2
+        err = np.abs(sc[:, :k].astype(np.float64) - exact) / scale
+        ld = (d + 31) // 32 * 32
+        eps = 2.0 ** -10 + 2.0 ** -24 * (ld / 16.0 + 32.0)
+        print(f"coarse score error d={d} k={k}: max {err.max():.3e} (bound {eps:.3e})")
+        assert 1e-7 < err.max() <= 0.5 * eps    # well inside the bound, and really the coarse product (not the fine one)
+
+
 def test_force_simt_path_agrees(m):
     X, _, _ = ko.gaussian_blobs(20000, 48, 37, seed=5)
     init = ko.row_init_centers(X, 37)
@@ -247,7 +276,9 @@ def test_force_simt_path_agrees(m):
     {"h16": 0, "bf16_corr": 0},           # CTA pairs, plain 3xTF32
     {"h16": 0, "ss": 0},                  # CTA pairs, BF16 corrections, A operand entirely in TMEM
     {"fused": 0},                         # tensor-core path even where the one-pass small-k kernel applies
-    {"two_level": 2},                     # fast pass + full bookkeeping over the near-tie rows, forced on small tables
+    {"two_level": 2},                     # coarse one-product pass + fast pass + full bookkeeping over the near-tie rows, forced on small tables
+    {"two_level": 2, "cascade": 0},       # ... without the coarse pass
+    {"two_level": 2, "cand1_frac": 0.002},  # ... with a coarse-pass copy that overflows: the fit drops the coarse pass
     {"two_level": 2, "cand_cap": 256},    # ... with a candidate buffer that overflows: falls back to the single pass
     {"two_level": 0},                     # single pass with full bookkeeping
 ])
@@ -262,7 +293,7 @@ def test_every_kernel_variant_keeps_parity(m, options):
             check_fit_parity(m, X, ko.row_init_centers(X, k), tol=1e-4, max_iter=5)
     finally:
         for name, val in {"kernel": 2, "cluster": 2, "bf16_corr": 1, "ss": 1, "fused": 1, "h16": 1, "two_level": 1,
-                          "cand_cap": 0}.items():
+                          "cand_cap": 0, "cascade": 1, "cand1_frac": 0.3}.items():
             m._lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
 
 
@@ -366,8 +397,8 @@ def test_full_size_c3_properties(m):
     pass vs. single pass) give the SAME cluster sizes and cost -- both are FP64-faithful, so they must."""
     n, d, k = 100_000_000, 256, 1000
     free, _ = __import__("torch").cuda.mem_get_info()
-    if free < 125e9:
-        pytest.skip("needs ~115 GB of free device memory")
+    if free < 150e9:
+        pytest.skip("needs ~145 GB of free device memory")
     centres = np.random.default_rng(2).uniform(-10, 10, (k, d)).astype(np.float32)
     t = m.Table(n, d)
     try:
