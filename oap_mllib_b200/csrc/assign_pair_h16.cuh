@@ -139,7 +139,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             mbar_init(&a_full[s], leader ? 8 : 4);
             mbar_init(&a_full[8 + s], leader ? 8 : 4);
         }
-        for (int s = 0; s < 4; ++s) mbar_init(&a_free[s], 1);
+        for (int s = 0; s < 4; ++s) mbar_init(&a_free[s], 2);   // both MMA issuers commit
         for (int b = 0; b < 2; ++b) mbar_init(&acc_empty[b], leader ? 16 : 8);   // two epilogue warpgroups per CTA
         fence_mbar_init();
     }
@@ -199,14 +199,23 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 __syncwarp();
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp == 2) {
         if (leader) {
-            // ================================ MMA issuer ==============================
+            // ================================ MMA issuers =============================
+            // TWO issuing warps (logical warps 1 and 2), one per accumulator buffer: issuer q takes the centroid
+            // tiles with tile % 2 == q.  Between two tiles an issuer spends > 1000 cycles in the tile's commit and
+            // the next tile's waits while the (shallow) MMA queue drains; with two of them one is issuing while the
+            // other waits.  tcgen05.commit only tracks the MMAs of the thread that executes it, hence: tile_done is
+            // committed by the tile's owner, and everything that releases the A operand (a_free) is committed by
+            // BOTH issuers (barrier count 2), each after its own last tile of the row tile.
+            const uint32_t issuer = warp - 1;
             constexpr uint32_t idesc = make_idesc_f16(2 * kTileM, BN);
             uint32_t tile = 0, rtn = 0, bpar = 0;   // bpar: parity of the next load into each B group
             long long t_wait_acc = 0, t_wait = 0, t_issue = 0, t_mark = 0;
-            const bool prof = p.role_prof != nullptr && blockIdx.x == 0;
+            const bool prof = p.role_prof != nullptr && blockIdx.x == 0 && issuer == 0;
             for (int base = base0; base < num_row_tiles; base += gridDim.x, ++rtn) {
+                const uint32_t abuf = ADB ? (rtn & 1) : 0, apar = ADB ? (rtn >> 1) & 1 : rtn & 1;
+                bool a_checked = false;   // this issuer has waited for the row tile's A operand
                 for (int i = 0; i < NT; ++i, ++tile) {
                     // Serpentine order over the centroid tiles: odd row tiles walk them backwards, and centroid
                     // tile nt always lives in B group nt % NG -- so the last RES = min(NG, NT) tiles of one row tile
@@ -217,22 +226,30 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
                     const uint32_t g = nt % NG;
                     const bool resident = rtn > 0 && i < RES;
-                    if (prof) t_mark = clock64();
-                    if (resident) {
-                        mbar_wait(&acc_empty[ab], aph ^ 1);
-                    } else {
-                        mbar_wait2(&acc_empty[ab], aph ^ 1, &bfull[g], (bpar >> g) & 1);
-                        bpar ^= 1u << g;
+                    const uint32_t bfull_par = resident ? ((bpar >> g) & 1) ^ 1 : (bpar >> g) & 1;   // resident: the load that filled it
+                    if (!resident) bpar ^= 1u << g;
+                    if (ab != issuer) {
+                        // not this issuer's tile; a row tile of ONE tile leaves this issuer without any MMA on its
+                        // A operand, but the release barriers still expect its arrival
+                        if (NT == 1 && elect_one()) {
+                            if (!ADB && C64a > 0) tc_commit_pair(&a_free[0]);
+                            tc_commit_pair(&a_free[abuf * 2 + 1]);
+                        }
+                        __syncwarp();
+                        continue;
                     }
+                    if (prof) t_mark = clock64();
+                    mbar_wait2(&acc_empty[ab], aph ^ 1, &bfull[g], bfull_par);
                     if (prof) { const long long t = clock64(); t_wait_acc += t - t_mark; t_mark = t; }
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
                     const uint32_t bsm0 = smem_u32(bs + g * group_bytes);
-                    const uint32_t abuf = ADB ? (rtn & 1) : 0, apar = ADB ? (rtn >> 1) & 1 : rtn & 1;
+                    const bool last_tile = i == NT - 1;           // of the row tile
+                    const bool my_last = last_tile || i == NT - 2;   // this issuer's last tile of the row tile
                     for (int c = 0; c < C64; ++c) {
                         const int nk = (2 * c + 1 < KC) ? 4 : 2;   // 16-value steps in this unit
-                        if (i == 0) {
-                            // first centroid tile of a row tile: the unit's h1/h2 must have been written
+                        if (!a_checked) {
+                            // this issuer's first tile of the row tile: the unit's h1/h2 must have been written
                             const uint32_t k0 = 2 * c, k1 = (2 * c + 1 < KC) ? 2 * c + 1 : 2 * c;
                             mbar_wait2(&a_full[abuf * 8 + k0], apar, &a_full[abuf * 8 + k1], apar);
                             tc_fence_after();
@@ -254,28 +271,31 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                                 for (int ks = 0; ks < nk; ++ks)
                                     mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
                             } else {
-                            // small terms first (knockout 8 / 16: timing experiments only, MMAs left out)
-                            if (!(p.knockout & 8)) {
-                                for (int ks = 0; ks < nk; ++ks)
-                                    mma_bf16_ts_pair(d_tmem, a2 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
-                                for (int ks = 0; ks < nk; ++ks)
-                                    mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d2 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                                // small terms first (knockout 8 / 16: timing experiments only, MMAs left out)
+                                if (!(p.knockout & 8)) {
+                                    for (int ks = 0; ks < nk; ++ks)
+                                        mma_bf16_ts_pair(d_tmem, a2 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
+                                    for (int ks = 0; ks < nk; ++ks)
+                                        mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d2 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                                }
+                                if (!(p.knockout & 16))
+                                    for (int ks = 0; ks < nk; ++ks)
+                                        mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
                             }
-                            if (!(p.knockout & 16))
-                                for (int ks = 0; ks < nk; ++ks)
-                                    mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                            // Release of the A operand after this issuer's last tile of the row tile.  One A buffer: in
+                            // two halves by the owner of the row tile's last tile (a release per unit measured 5 %
+                            // slower: every commit stalls the issuer for a few hundred cycles), both halves at once by
+                            // the other issuer.  Two A buffers: one release, the buffer has a row tile of slack.
+                            if (my_last) {
+                                if (!ADB && C64a > 0 && (last_tile ? c == C64a - 1 : c == C64 - 1)) tc_commit_pair(&a_free[0]);
+                                if (c == C64 - 1) tc_commit_pair(&a_free[abuf * 2 + 1]);
                             }
-                            // last centroid tile of the row tile: the first half of h1/h2 may be overwritten
-                            // last centroid tile of the row tile: the h1/h2 columns may be overwritten -- released in two
-                            // halves (a release per unit measured 5 % slower: every commit stalls the issuer for a few
-                            // hundred cycles).  Two A buffers: one release per row tile, the buffer has a row tile of slack.
-                            if (i == NT - 1 && c == C64a - 1 && !ADB) tc_commit_pair(&a_free[0]);
-                            if (i == NT - 1 && c == C64 - 1) tc_commit_pair(&a_free[abuf * 2 + 1]);
                             if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 3]);
                         }
                         __syncwarp();
                         if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
                     }
+                    a_checked = true;
                 }
             }
             if (prof && lane == 0) {
@@ -431,15 +451,34 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                             }
                         }
                     };
-                    tmem_ld16(acc, va);
+                    if constexpr (FAST) {
+                        // The fast update is short enough that the drain is bound by the LATENCY of tcgen05.ld (one
+                        // load per 16 columns, each issued after the previous wait): up to three loads in flight.
+                        constexpr int NB = HALF / 16;   // 2 or 4 batches
+                        uint32_t vc[16];
+                        tmem_ld16(acc, va);
+                        tmem_ld16(acc + 16, vb);
+                        if constexpr (NB > 2) tmem_ld16(acc + 32, vc);
+                        tmem_wait_ld();
+                        consume(va, col0);
+                        if constexpr (NB > 3) tmem_ld16(acc + 48, va);
+                        consume(vb, col0 + 16);
+                        if constexpr (NB > 2) consume(vc, col0 + 32);
+                        if constexpr (NB > 3) {
+                            tmem_wait_ld();
+                            consume(va, col0 + 48);
+                        }
+                    } else {
+                        tmem_ld16(acc, va);
 #pragma unroll 1
-                    for (int c0 = 0; c0 < HALF; c0 += 32) {
-                        tmem_wait_ld();
-                        tmem_ld16(acc + c0 + 16, vb);
-                        consume(va, col0 + c0);
-                        tmem_wait_ld();
-                        if (c0 + 32 < HALF) tmem_ld16(acc + c0 + 32, va);
-                        consume(vb, col0 + c0 + 16);
+                        for (int c0 = 0; c0 < HALF; c0 += 32) {
+                            tmem_wait_ld();
+                            tmem_ld16(acc + c0 + 16, vb);
+                            consume(va, col0 + c0);
+                            tmem_wait_ld();
+                            if (c0 + 32 < HALF) tmem_ld16(acc + c0 + 32, va);
+                            consume(vb, col0 + c0 + 16);
+                        }
                     }
                 }
                 tc_fence_before();
