@@ -340,6 +340,7 @@ def run_ours(args, rank, local_rank, world):
             "wall_ms_per_step": wall_ms / args.steps, "phases_ms_per_step": phases,
             "rechecked_rows_per_step": prof["rechecked_rows"] / args.steps,
             "full_rechecks_per_step": prof["full_rechecks"] / args.steps,
+            "coarse_undecided_rows_per_step": prof.get("coarse_undecided_rows", 0) / args.steps,
             "final_cost": cost, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cpu}
     emit(line)

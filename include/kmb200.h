@@ -151,6 +151,8 @@ typedef struct {
     float finalize_ms;         /* centres, convergence flag, TF32 split of the new centres      */
     float assign_main_ms;      /* of assign_ms: the main assign kernel alone (without the candidate gather and the
                                   second pass over the near-tie rows of the two-level scheme)    */
+    int64_t coarse_undecided_rows; /* cascade: rows the one-product pass could not decide (summed over iterations;
+                                      0 when the cascade is off)                                  */
 } kmb200_profile;
 int kmb200_get_profile(kmb200_profile *out);
 

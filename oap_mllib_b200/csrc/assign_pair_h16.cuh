@@ -246,54 +246,63 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     const uint32_t bsm0 = smem_u32(bs + g * group_bytes);
                     const bool last_tile = i == NT - 1;           // of the row tile
                     const bool my_last = last_tile || i == NT - 2;   // this issuer's last tile of the row tile
-                    for (int c = 0; c < C64; ++c) {
+                    // one unit (64 K-values) of this tile: its MMAs and whatever is committed after them
+                    auto issue_unit = [&](int c) {
                         const int nk = (2 * c + 1 < KC) ? 4 : 2;   // 16-value steps in this unit
-                        if (!a_checked) {
+                        const uint32_t bsm = bsm0 + c * Cfg::kBUnitBytes;
+                        const uint64_t d1 = make_kmajor_sw128_desc(bsm);
+                        const uint64_t d2 = make_kmajor_sw128_desc(bsm + Cfg::kBHalfBytes);
+                        const uint32_t a1 = tmem_base + abuf * abuf_cols + c * 32, a2 = a1 + Cfg::kA2Col0;
+                        if constexpr (ONE) {
+                            for (int ks = 0; ks < nk; ++ks)
+                                mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
+                        } else {
+                            // small terms first (knockout 8 / 16: timing experiments only, MMAs left out)
+                            if (!(p.knockout & 8)) {
+                                for (int ks = 0; ks < nk; ++ks)
+                                    mma_bf16_ts_pair(d_tmem, a2 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
+                                for (int ks = 0; ks < nk; ++ks)
+                                    mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d2 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                            }
+                            if (!(p.knockout & 16))
+                                for (int ks = 0; ks < nk; ++ks)
+                                    mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                        }
+                        // Release of the A operand after this issuer's last tile of the row tile.  One A buffer: in
+                        // two halves by the owner of the row tile's last tile (a release per unit measured 5 %
+                        // slower: every commit stalls the issuer for a few hundred cycles), both halves at once by
+                        // the other issuer.  Two A buffers: one release, the buffer has a row tile of slack.
+                        if (my_last) {
+                            if (!ADB && C64a > 0 && (last_tile ? c == C64a - 1 : c == C64 - 1)) tc_commit_pair(&a_free[0]);
+                            if (c == C64 - 1) tc_commit_pair(&a_free[abuf * 2 + 1]);
+                        }
+                        if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 3]);
+                    };
+                    if (a_checked) {
+                        // the row tile's A operand is known to be complete: the whole tile in one go
+                        if (prof) { const long long t = clock64(); t_wait += t - t_mark; t_mark = t; }
+                        if (elect_one())
+                            for (int c = 0; c < C64; ++c) issue_unit(c);
+                        __syncwarp();
+                        if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
+                    } else {
+                        for (int c = 0; c < C64; ++c) {
                             // this issuer's first tile of the row tile: the unit's h1/h2 must have been written
                             const uint32_t k0 = 2 * c, k1 = (2 * c + 1 < KC) ? 2 * c + 1 : 2 * c;
                             mbar_wait2(&a_full[abuf * 8 + k0], apar, &a_full[abuf * 8 + k1], apar);
                             tc_fence_after();
-                        }
-                        if (prof) {
-                            const long long t = clock64();
-                            t_wait += t - t_mark;
-                            // (the issuer runs ahead of the tensor pipe by the depth of the MMA queue: time spent here
-                            // is not necessarily time the pipe idles)
-                            if (i == 0 && lane == 0 && c >= 1 && c <= 3) p.role_prof[12 + c] += t - t_mark;   // a_full wait per unit
-                            t_mark = t;
-                        }
-                        if (elect_one()) {
-                            const uint32_t bsm = bsm0 + c * Cfg::kBUnitBytes;
-                            const uint64_t d1 = make_kmajor_sw128_desc(bsm);
-                            const uint64_t d2 = make_kmajor_sw128_desc(bsm + Cfg::kBHalfBytes);
-                            const uint32_t a1 = tmem_base + abuf * abuf_cols + c * 32, a2 = a1 + Cfg::kA2Col0;
-                            if constexpr (ONE) {
-                                for (int ks = 0; ks < nk; ++ks)
-                                    mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
-                            } else {
-                                // small terms first (knockout 8 / 16: timing experiments only, MMAs left out)
-                                if (!(p.knockout & 8)) {
-                                    for (int ks = 0; ks < nk; ++ks)
-                                        mma_bf16_ts_pair(d_tmem, a2 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, (c | ks) == 0 ? 0u : 1u);
-                                    for (int ks = 0; ks < nk; ++ks)
-                                        mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d2 + static_cast<uint64_t>(ks * 2), idesc, 1u);
-                                }
-                                if (!(p.knockout & 16))
-                                    for (int ks = 0; ks < nk; ++ks)
-                                        mma_bf16_ts_pair(d_tmem, a1 + ks * 8, d1 + static_cast<uint64_t>(ks * 2), idesc, 1u);
+                            if (prof) {
+                                const long long t = clock64();
+                                t_wait += t - t_mark;
+                                // (the issuer runs ahead of the tensor pipe by the depth of the MMA queue: time spent
+                                // here is not necessarily time the pipe idles)
+                                if (i == 0 && lane == 0 && c >= 1 && c <= 3) p.role_prof[12 + c] += t - t_mark;   // a_full wait per unit
+                                t_mark = t;
                             }
-                            // Release of the A operand after this issuer's last tile of the row tile.  One A buffer: in
-                            // two halves by the owner of the row tile's last tile (a release per unit measured 5 %
-                            // slower: every commit stalls the issuer for a few hundred cycles), both halves at once by
-                            // the other issuer.  Two A buffers: one release, the buffer has a row tile of slack.
-                            if (my_last) {
-                                if (!ADB && C64a > 0 && (last_tile ? c == C64a - 1 : c == C64 - 1)) tc_commit_pair(&a_free[0]);
-                                if (c == C64 - 1) tc_commit_pair(&a_free[abuf * 2 + 1]);
-                            }
-                            if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 3]);
+                            if (elect_one()) issue_unit(c);
+                            __syncwarp();
+                            if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
                         }
-                        __syncwarp();
-                        if (prof) { const long long t = clock64(); t_issue += t - t_mark; t_mark = t; }
                     }
                     a_checked = true;
                 }

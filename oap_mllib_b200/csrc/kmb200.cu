@@ -1078,6 +1078,7 @@ static int launch_assign_h16(kmb200_table *t) {
         if (ev) CU_TRY(cudaEventRecord(ev[1], t->stream));
         KM_TRY(read_count(t, &w.host->cand1_count, w.flag_count + 3));
         if ((int64_t)w.host->cand1_count <= w.cand1_cap) {
+            g_prof.coarse_undecided_rows += w.host->cand1_count;
             g_main_ev = nullptr;   // bracketed above
             w.scatter1 = true;
             w.recheck_level = 1;
