@@ -125,3 +125,29 @@ def test_oracle_reproduces_committed_fixtures():
         assert it == int(fx[f"iters_{i}"])
         np.testing.assert_allclose(C, fx[f"centers_{i}"], rtol=1e-10, atol=1e-12)
         assert abs(cost - float(fx[f"cost_{i}"])) <= 1e-10 * cost
+
+
+def test_dense_rows_restates_the_reference_conversion():
+    """OneDAL.vectorsToMergedNumericTables densifies every row (row.toArray) into a row-major FP64 table: the oracle's
+    restatement must give the same table from dense rows, from columns and from CSR (with empty rows)."""
+    rng = np.random.default_rng(4)
+    X = rng.normal(size=(37, 9))
+    X[np.abs(X) < 0.7] = 0.0
+    X[5] = 0.0
+
+    class Csr:   # the three arrays of a SparseVector batch, without needing scipy
+        def __init__(self, dense):
+            self.shape = dense.shape
+            self.indptr = np.zeros(dense.shape[0] + 1, np.int64)
+            idx, val = [], []
+            for r, row in enumerate(dense):
+                nz = np.flatnonzero(row)
+                idx.extend(nz.tolist())
+                val.extend(row[nz].tolist())
+                self.indptr[r + 1] = len(idx)
+            self.indices, self.data = np.array(idx, np.int32), np.array(val, np.float64)
+
+    assert np.array_equal(ko.dense_rows(X), X)
+    assert np.array_equal(ko.dense_rows(tuple(np.ascontiguousarray(X[:, c]) for c in range(X.shape[1]))), X)
+    assert np.array_equal(ko.dense_rows(Csr(X)), X)
+    assert ko.dense_rows(X.astype(np.float32)).dtype == np.float64
