@@ -34,7 +34,7 @@ struct PairH16Cfg {
     static constexpr int kA2Col0 = 128;                  // h1 at columns [0, 128), h2 at [128, 256)
     static constexpr int kAccCol0 = 256;
     static constexpr int kTmemCols = 512;
-    static constexpr int kNumBars = 4 /*bfull*/ + 4 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 16 /*a_full*/ + 4 /*a_free*/ + 2 /*acc_empty*/;
+    static constexpr int kNumBars = 4 /*bfull*/ + 8 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 16 /*a_full*/ + 4 /*a_free*/ + 2 /*acc_empty*/;
     static constexpr int kXchgBytes = 2 * 128 * 5 * 4;
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16 + kXchgBytes;
     static constexpr int kBudget = 227 * 1024 - 1024 - kTailBytes;
@@ -101,13 +101,13 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     float *cn_s = reinterpret_cast<float *>(tail);       // [2][BN]
     uint64_t *bars = reinterpret_cast<uint64_t *>(tail + 2 * BN * 4);
     uint64_t *bfull = bars;           // [4]  (leader) B group landed in BOTH CTAs
-    uint64_t *tile_done = bars + 4;   // [4]  all MMAs of a centroid tile completed (multicast commit), ring over tiles
-    uint64_t *xfull = bars + 8;       // [8]  X chunk landed
-    uint64_t *xempty = bars + 16;     // [8]  X chunk read by its transform warpgroup
-    uint64_t *a_full = bars + 24;     // [2][8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
-    uint64_t *a_free = bars + 40;     // [4]  units [0, C64a) / [C64a, C64) of A were read for the last time in this row
+    uint64_t *tile_done = bars + 4;   // [8]  all MMAs of a centroid tile completed (multicast commit), ring over tiles
+    uint64_t *xfull = bars + 12;      // [8]  X chunk landed
+    uint64_t *xempty = bars + 20;     // [8]  X chunk read by its transform warpgroup
+    uint64_t *a_full = bars + 28;     // [2][8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
+    uint64_t *a_free = bars + 44;     // [4]  units [0, C64a) / [C64a, C64) of A were read for the last time in this row
                                       //      tile (multicast); with two A buffers: [2 * buffer + 1], once per row tile
-    uint64_t *acc_empty = bars + 44;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
+    uint64_t *acc_empty = bars + 48;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
     uint32_t *xchg = tmem_slot + 4;   // [2][5][128]
 
@@ -129,10 +129,8 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         tma_prefetch_desc(&tm_b);
     }
     if (warp == 1 && lane == 0) {
-        for (int s = 0; s < 4; ++s) {
-            mbar_init(&bfull[s], 1);
-            mbar_init(&tile_done[s], 1);
-        }
+        for (int s = 0; s < 4; ++s) mbar_init(&bfull[s], 1);
+        for (int s = 0; s < 8; ++s) mbar_init(&tile_done[s], 1);
         for (int s = 0; s < 8; ++s) {
             mbar_init(&xfull[s], 1);
             mbar_init(&xempty[s], 4);
@@ -159,13 +157,17 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 const int nt = (rtn & 1) ? NT - 1 - i : i;   // serpentine order, see the MMA issuer
                 const int brow = nt * BN + (int)rank * Cfg::kBRows;
                 const uint32_t g = nt % NG;
-                // the MMAs of the tile that last used this group have completed (waited for at EVERY tile, also
-                // the resident ones: a parity wait must not skip a phase of its barrier)
-                if (tile >= (uint32_t)NG) {
-                    const uint32_t q = tile - NG;
-                    mbar_wait(&tile_done[q & 3], (q >> 2) & 1);
-                }
+                // Before a LOAD: the MMAs of the tile that last used this group have completed.  A parity wait is only
+                // meaningful while its barrier is within one phase of the awaited one, hence the ring of 8 and no wait
+                // at resident tiles: the MMAs cannot pass a tile that needs this load, so tile q + 8 is never done
+                // (NG <= 4 < 8), and at most RES <= 4 resident tiles lie between two loads, so tile q - 8 always is.
+                // (Resident tiles do not depend on this warp at all -- with k <= NG tiles per row tile the MMAs may
+                // run arbitrarily far ahead of it.)
                 const bool resident = rtn > 0 && i < RES;
+                if (!resident && tile >= (uint32_t)NG) {
+                    const uint32_t q = tile - NG;
+                    mbar_wait(&tile_done[q & 7], (q >> 3) & 1);
+                }
                 if (!resident && elect_one()) {
                     uint8_t *st = bs + g * group_bytes;
                     // both CTAs' bytes are accounted on the leader's barrier; the peer cannot run ahead of
@@ -276,7 +278,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                             if (!ADB && C64a > 0 && (last_tile ? c == C64a - 1 : c == C64 - 1)) tc_commit_pair(&a_free[0]);
                             if (c == C64 - 1) tc_commit_pair(&a_free[abuf * 2 + 1]);
                         }
-                        if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 3]);
+                        if (c == C64 - 1) tc_commit_pair(&tile_done[tile & 7]);
                     };
                     if (a_checked) {
                         // the row tile's A operand is known to be complete: the whole tile in one go
@@ -429,7 +431,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     const int nn = i + 1 == NT ? nt : ((rtn & 1) ? nt - 1 : nt + 1);
                     cn_next = __ldg(p.cnorm + nn * BN + r);
                 }
-                mbar_wait(&tile_done[tile & 3], (tile >> 2) & 1);
+                mbar_wait(&tile_done[tile & 7], (tile >> 3) & 1);
                 tc_fence_after();
                 if (has_cols && !(p.knockout & 4)) {
                     const uint32_t acc = tmem_base + lane_addr + Cfg::kAccCol0 + ab * BN + col0;
