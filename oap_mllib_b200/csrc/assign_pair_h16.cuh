@@ -233,9 +233,14 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     if (ab != issuer) {
                         // not this issuer's tile; a row tile of ONE tile leaves this issuer without any MMA on its
                         // A operand, but the release barriers still expect its arrival
-                        if (NT == 1 && elect_one()) {
-                            if (!ADB && C64a > 0) tc_commit_pair(&a_free[0]);
-                            tc_commit_pair(&a_free[abuf * 2 + 1]);
+                        if (NT == 1) {
+                            // (it also waits for the A operand like the owner does: an issuer that skipped a phase of
+                            // the a_full barriers could pass its next parity wait on them too early)
+                            for (int kc = 0; kc < KC; ++kc) mbar_wait(&a_full[abuf * 8 + kc], apar);
+                            if (elect_one()) {
+                                if (!ADB && C64a > 0) tc_commit_pair(&a_free[0]);
+                                tc_commit_pair(&a_free[abuf * 2 + 1]);
+                            }
                         }
                         __syncwarp();
                         continue;
