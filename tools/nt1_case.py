@@ -1,3 +1,5 @@
+"""Quick check (GPU): fits on shapes whose row tiles hold a single centroid tile (k <= 128) and a few others, against the
+FP64 oracle -- the one-tile case exercises the MMA issuer that owns no tile of a row tile."""
 import sys, numpy as np
 sys.path.insert(0, ".")
 import oap_mllib_b200 as m
