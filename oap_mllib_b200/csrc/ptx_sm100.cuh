@@ -113,16 +113,6 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-// TMA load delivered to the same shared-memory offset (and signalling the same mbarrier offset) in
-// every CTA of the cluster whose bit is set in cta_mask.
-__device__ __forceinline__ void tma_load_2d_mcast(const CUtensorMap *m, uint64_t *bar, void *dst, int32_t c0,
-                                                  int32_t c1, uint16_t cta_mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, "
-        "{%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
-        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(cta_mask)
-        : "memory");
-}
 // tcgen05.commit arriving on the barrier at the same offset in every CTA of cta_mask
 __device__ __forceinline__ void tc_commit_mcast(uint64_t *bar, uint16_t cta_mask) {
     asm volatile(
