@@ -8,7 +8,10 @@
  * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative
  * kmb200_status; kmb200_last_error() gives the thread-local message.  No function falls back to a
  * CPU implementation: without a usable sm_100 GPU every compute call fails with KMB200_ERR_DEVICE.
- * Handles are not thread-safe; different handles may be used from different threads.
+ * Handles are not thread-safe; different handles may be used from different threads.  Compute
+ * calls (fit / assign) on tables of the SAME device run one at a time (a per-device lock inside the
+ * library); calls on different devices run concurrently.  kmb200_set_option is process-wide: set
+ * options before starting threads.
  */
 #ifndef KMB200_H_
 #define KMB200_H_
@@ -184,12 +187,16 @@ int kmb200_set_option(const char *name, double value);
  *   sizes_dev   DEVICE pointer, k int64 values, overwritten
  *   cuda_stream a cudaStream_t (NULL = the default stream); the work is only ENQUEUED on it, the
  *               result is valid once that stream has run it
- *   limit       k <= 65536: the k int32 counters of scratch sit in a fixed 256 KiB array inside
+ *   limits      k <= 65536: the k int32 counters of scratch sit in a fixed 256 KiB array inside
  *               the library image (each GPU that loads the library holds it until the process
- *               exits); larger k is refused with KMB200_ERR_LIMIT
+ *               exits); n <= 2^31 - 1, because those counters are 32-bit and one cluster may hold
+ *               every row.  Anything larger is refused with KMB200_ERR_LIMIT
  *
- * The first call on a device looks up that array's device address (a one-off driver query, no
- * allocation): make that first call before starting any stream capture.  All calls on one device
+ * The first call on a device looks up that array's device address (one driver query per device).
+ * With CUDA's lazy module loading that query can be what loads this library's device code, array
+ * included, onto the GPU -- the driver, not this function, takes memory for it then.  So make the
+ * first call at start-up, before the GPU's memory is handed to the pool, and before starting any
+ * stream capture.  All calls on one device
  * share the array, which keeps the previous call's counts until the next call clears the part it
  * needs; two calls whose work overlaps on the GPU (different streams, no dependency) race on it and
  * both results are then garbage -- order them with an event or use one stream. */

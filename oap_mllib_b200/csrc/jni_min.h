@@ -47,6 +47,8 @@ enum JniSlot {
     kJniNewDoubleArray = 182,
     kJniGetByteArrayRegion = 200,
     kJniSetByteArrayRegion = 208,
+    kJniSetIntArrayRegion = 211,
+    kJniSetLongArrayRegion = 212,
     kJniSetDoubleArrayRegion = 214,
     kJniGetPrimitiveArrayCritical = 222,
     kJniReleasePrimitiveArrayCritical = 223,

@@ -11,12 +11,19 @@
 //                                   javah/org_apache_spark_ml_util_OneCCL__.h
 //   changed / new (the oneDAL Java classes DALMatrix/HomogenNumericTable are gone)
 //     OneDAL$.cNewTable (JI)J, cNewCenters (II)J, cGetCenters (J)[D, cFreeCenters (J)V
-//     OneCCL$.c_getUniqueId ()[B, c_init (II[BLorg/apache/spark/ml/util/CCLParam;)I
+//     OneCCL$.c_getUniqueId ()[B, c_init (II[BLorg/apache/spark/ml/util/CCLParam;)I, c_setDevice (I)I
+//     KMeansDALImpl.cKMeansDALAssign (JJ[I[J)D   -- the summary pass (labels, cluster sizes, cost) on the GPU
 //
 // No JVM exists in this image: the layer is exercised through a hand-built JNIEnv function table
 // (tests/test_jni_shim.py).  It cannot be linked against a real JVM here -- INTEGRATION.md says so.
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <fcntl.h>
+#include <sys/file.h>
+#include <unistd.h>
+#include <mutex>
+#include <cstdio>
 #include <vector>
 
 #include "../../include/kmb200.h"
@@ -44,6 +51,80 @@ struct Centers {  // host k x d FP64 buffer handed around as a jlong (replaces N
 
 kmb200_comm *g_comm = nullptr;  // process-global like the reference's g_comms (native/OneCCL.cpp:38-40)
 int g_world = 1, g_rank = 0;
+int g_device = -1;              // set by c_setDevice; -1 = not chosen yet (c_init picks one)
+
+// Page-locked staging buffer of the calling thread.  Java arrays are copied into it inside a SHORT critical
+// region (a memcpy, nothing else: no CUDA call, no allocation, no blocking while the garbage collector is held
+// off), the region is released, and only then does the upload run -- from pinned memory, i.e. at the link rate.
+struct Staging {
+    void *p = nullptr;
+    size_t bytes = 0;
+    ~Staging() { if (p) kmb200_pinned_free(p); }
+    void *get(size_t want) {
+        if (bytes >= want) return p;
+        if (p) kmb200_pinned_free(p);
+        p = nullptr;
+        bytes = 0;
+        if (kmb200_pinned_alloc(want, &p) != 0) return nullptr;
+        bytes = want;
+        return p;
+    }
+};
+thread_local Staging g_staging;
+
+// Which GPU this executor process uses.  Order: the ordinal given to c_setDevice (the Scala side passes
+// spark.oap.mllib.b200.device or the address Spark's GPU scheduling assigned to the task); the environment variable
+// KMB200_DEVICE; else the first GPU of the node that no other executor process has claimed -- a claim is an
+// exclusive flock on /tmp/kmb200-gpu-<i>.lock held until the process exits, so that executors which all see every
+// GPU do not pile up on GPU 0.  Chosen once per process, before the first table is created.
+std::mutex g_device_mu;
+int resolve_device() {
+    std::lock_guard<std::mutex> lk(g_device_mu);
+    if (g_device >= 0) return g_device;
+    const int count = kmb200_device_count();
+    if (count <= 0) return 0;   // the compute calls will report the missing device
+    if (const char *e = getenv("KMB200_DEVICE")) {
+        g_device = atoi(e) % count;
+        if (g_device < 0) g_device = 0;
+        return g_device;
+    }
+    for (int i = 0; i < count && g_device < 0; ++i) {
+        char path[64];
+        snprintf(path, sizeof(path), "/tmp/kmb200-gpu-%d.lock", i);
+        const int fd = open(path, O_CREAT | O_RDWR, 0666);
+        if (fd < 0) continue;
+        if (flock(fd, LOCK_EX | LOCK_NB) == 0) g_device = i;   // fd stays open: the claim lasts as long as the process
+        else close(fd);
+    }
+    if (g_device < 0) g_device = (int)(getpid() % count);   // more executors than GPUs on this node
+    return g_device;
+}
+bool use_device(JNIEnvPtr env) {
+    if (kmb200_device_count() <= 0) return true;   // nothing to select; compute calls fail with their own message
+    if (kmb200_set_device(resolve_device()) != 0) {
+        throw_runtime(env, kmb200_last_error());
+        return false;
+    }
+    return true;
+}
+constexpr size_t kStagingBytes = (size_t)64 << 20;
+
+// Copies count elements of a primitive Java array, starting at element `first`, into dst.  false + a pending
+// Java exception when the JVM cannot give access to the array.
+template <typename T>
+bool copy_from_array(JNIEnvPtr env, jarray arr, size_t first, size_t count, T *dst) {
+    if (count == 0) return true;
+    auto get = slot<void *(*)(JNIEnvPtr, jarray, jboolean *)>(env, kJniGetPrimitiveArrayCritical);
+    auto rel = slot<void (*)(JNIEnvPtr, jarray, void *, jint)>(env, kJniReleasePrimitiveArrayCritical);
+    T *src = arr ? static_cast<T *>(get(env, arr, nullptr)) : nullptr;
+    if (!src) {
+        throw_runtime(env, "cannot access the Java array (null array or GetPrimitiveArrayCritical failed)");
+        return false;
+    }
+    memcpy(dst, src + first, count * sizeof(T));
+    rel(env, arr, src, JNI_ABORT);
+    return true;
+}
 
 }  // namespace
 
@@ -57,6 +138,7 @@ JNIEXPORT jboolean JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cCheckPlat
 JNIEXPORT jlong JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cNewTable(JNIEnvPtr env, jobject, jlong rows,
                                                                              jint cols) {
     kmb200_table *t = nullptr;
+    if (!use_device(env)) return 0;   // conversion tasks run on threads of their own: each selects the executor's GPU
     if (kmb200_table_create(rows, cols, &t) != 0) {
         throw_runtime(env, kmb200_last_error());
         return 0;
@@ -70,12 +152,23 @@ JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cSetDoubleBatc
                                                                                   jlong numTableAddr, jint curRows,
                                                                                   jdoubleArray batch, jint numRows,
                                                                                   jint numCols) {
-    auto get = slot<void *(*)(JNIEnvPtr, jarray, jboolean *)>(env, kJniGetPrimitiveArrayCritical);
-    auto rel = slot<void (*)(JNIEnvPtr, jarray, void *, jint)>(env, kJniReleasePrimitiveArrayCritical);
-    double *values = static_cast<double *>(get(env, batch, nullptr));
-    const int rc = kmb200_table_append_f64(reinterpret_cast<kmb200_table *>(numTableAddr), curRows, values, numRows, numCols);
-    rel(env, batch, values, JNI_ABORT);
-    if (rc != 0) throw_runtime(env, kmb200_last_error());
+    kmb200_table *t = reinterpret_cast<kmb200_table *>(numTableAddr);
+    if (numRows <= 0 || numCols <= 0) return;
+    const size_t row_bytes = (size_t)numCols * sizeof(double);
+    const size_t rows_per = std::max<size_t>(1, kStagingBytes / row_bytes);
+    double *stage = static_cast<double *>(g_staging.get(std::min((size_t)numRows, rows_per) * row_bytes));
+    if (!stage) {
+        throw_runtime(env, kmb200_last_error());
+        return;
+    }
+    for (size_t r = 0; r < (size_t)numRows; r += rows_per) {
+        const size_t h = std::min(rows_per, (size_t)numRows - r);
+        if (!copy_from_array<double>(env, batch, r * numCols, h * numCols, stage)) return;
+        if (kmb200_table_append_f64(t, (int64_t)curRows + (int64_t)r, stage, (int64_t)h, numCols) != 0) {
+            throw_runtime(env, kmb200_last_error());
+            return;
+        }
+    }
 }
 
 // ---- other input layouts (no counterpart in the reference, which densifies every row on the JVM with
@@ -86,16 +179,32 @@ JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cSetColumnsBat
                                                                                    jobjectArray columns, jint numRows,
                                                                                    jint numCols) {
     auto elem = slot<jobject (*)(JNIEnvPtr, jobjectArray, jsize)>(env, kJniGetObjectArrayElement);
-    auto get = slot<void *(*)(JNIEnvPtr, jarray, jboolean *)>(env, kJniGetPrimitiveArrayCritical);
-    auto rel = slot<void (*)(JNIEnvPtr, jarray, void *, jint)>(env, kJniReleasePrimitiveArrayCritical);
+    kmb200_table *t = reinterpret_cast<kmb200_table *>(numTableAddr);
+    if (numRows <= 0 || numCols <= 0) return;
+    // chunks of rows: every column's slice is copied (one short critical region per column) into a column-major
+    // block of the staging buffer, then the block is uploaded
+    const size_t rows_per = std::max<size_t>(1, kStagingBytes / ((size_t)numCols * sizeof(double)));
+    const size_t chunk = std::min((size_t)numRows, rows_per);
+    double *stage = static_cast<double *>(g_staging.get(chunk * numCols * sizeof(double)));
+    if (!stage) {
+        throw_runtime(env, kmb200_last_error());
+        return;
+    }
     std::vector<jarray> arrays((size_t)numCols);
     std::vector<const double *> ptrs((size_t)numCols);
-    for (int c = 0; c < numCols; ++c) arrays[c] = elem(env, columns, c);
-    for (int c = 0; c < numCols; ++c) ptrs[c] = static_cast<const double *>(get(env, arrays[c], nullptr));
-    const int rc = kmb200_table_append_columns_f64(reinterpret_cast<kmb200_table *>(numTableAddr), curRows, ptrs.data(),
-                                                   numRows, numCols);
-    for (int c = numCols - 1; c >= 0; --c) rel(env, arrays[c], const_cast<double *>(ptrs[c]), JNI_ABORT);
-    if (rc != 0) throw_runtime(env, kmb200_last_error());
+    for (int c = 0; c < numCols; ++c) {
+        arrays[c] = columns ? elem(env, columns, c) : nullptr;
+        ptrs[c] = stage + (size_t)c * chunk;
+    }
+    for (size_t r = 0; r < (size_t)numRows; r += chunk) {
+        const size_t h = std::min(chunk, (size_t)numRows - r);
+        for (int c = 0; c < numCols; ++c)
+            if (!copy_from_array<double>(env, arrays[c], r, h, stage + (size_t)c * chunk)) return;
+        if (kmb200_table_append_columns_f64(t, (int64_t)curRows + (int64_t)r, ptrs.data(), (int64_t)h, numCols) != 0) {
+            throw_runtime(env, kmb200_last_error());
+            return;
+        }
+    }
 }
 
 // sparse rows: indptr long[numRows + 1], indices int[nnz], values double[nnz]
@@ -103,16 +212,28 @@ JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cSetSparseBatc
                                                                                   jlong numTableAddr, jint curRows,
                                                                                   jlongArray indptr, jintArray indices,
                                                                                   jdoubleArray values, jint numRows) {
-    auto get = slot<void *(*)(JNIEnvPtr, jarray, jboolean *)>(env, kJniGetPrimitiveArrayCritical);
-    auto rel = slot<void (*)(JNIEnvPtr, jarray, void *, jint)>(env, kJniReleasePrimitiveArrayCritical);
-    int64_t *ip = static_cast<int64_t *>(get(env, indptr, nullptr));
-    int32_t *ix = static_cast<int32_t *>(get(env, indices, nullptr));
-    double *va = static_cast<double *>(get(env, values, nullptr));
-    const int rc = kmb200_table_append_csr_f64(reinterpret_cast<kmb200_table *>(numTableAddr), curRows, numRows, ip, ix, va);
-    rel(env, values, va, JNI_ABORT);
-    rel(env, indices, ix, JNI_ABORT);
-    rel(env, indptr, ip, JNI_ABORT);
-    if (rc != 0) throw_runtime(env, kmb200_last_error());
+    if (numRows <= 0) return;
+    // the three arrays are copied out one after the other (short critical regions), then scattered on the device
+    std::vector<int64_t> ip((size_t)numRows + 1);
+    if (!copy_from_array<int64_t>(env, indptr, 0, ip.size(), ip.data())) return;
+    const int64_t base = ip[0], nnz = ip[numRows] - base;
+    if (nnz < 0) {
+        throw_runtime(env, "cSetSparseBatch: indptr decreases");
+        return;
+    }
+    void *stage = g_staging.get(std::max<size_t>((size_t)nnz * 12, 16));
+    if (!stage) {
+        throw_runtime(env, kmb200_last_error());
+        return;
+    }
+    double *va = static_cast<double *>(stage);
+    int32_t *ix = reinterpret_cast<int32_t *>(va + nnz);
+    if (nnz > 0 && (!copy_from_array<double>(env, values, (size_t)base, (size_t)nnz, va) ||
+                    !copy_from_array<int32_t>(env, indices, (size_t)base, (size_t)nnz, ix)))
+        return;
+    for (auto &v : ip) v -= base;   // the staged copies start at the first nonzero of this batch
+    if (kmb200_table_append_csr_f64(reinterpret_cast<kmb200_table *>(numTableAddr), curRows, numRows, ip.data(), ix, va) != 0)
+        throw_runtime(env, kmb200_last_error());
 }
 
 JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cTruncateTable(JNIEnvPtr env, jobject, jlong addr,
@@ -172,7 +293,7 @@ JNIEXPORT jint JNICALL Java_org_apache_spark_ml_util_OneCCL_00024_c_1init(JNIEnv
     uint8_t buf[KMB200_UNIQUE_ID_BYTES];
     auto getr = slot<void (*)(JNIEnvPtr, jbyteArray, jsize, jsize, jbyte *)>(env, kJniGetByteArrayRegion);
     getr(env, id, 0, KMB200_UNIQUE_ID_BYTES, reinterpret_cast<jbyte *>(buf));
-    if (kmb200_set_device(0) != 0 && kmb200_device_count() > 0) { /* one executor = one visible GPU */ }
+    if (!use_device(env)) return 0;
     if (size > 1) {
         if (kmb200_comm_init(size, rank, buf, &g_comm) != 0) {
             throw_runtime(env, kmb200_last_error());
@@ -188,6 +309,20 @@ JNIEXPORT jint JNICALL Java_org_apache_spark_ml_util_OneCCL_00024_c_1init(JNIEnv
     setl(env, param, fid(env, cls, "commSize", "J"), (jlong)g_world);
     setl(env, param, fid(env, cls, "rankId", "J"), (jlong)g_rank);
     return 1;
+}
+
+// Device ordinal of this executor (no counterpart in the reference, which has no devices).  Call it before the
+// first table is created; returns the ordinal in use (an earlier choice is kept once tables may exist on it).
+JNIEXPORT jint JNICALL Java_org_apache_spark_ml_util_OneCCL_00024_c_1setDevice(JNIEnvPtr env, jobject, jint ordinal) {
+    {
+        std::lock_guard<std::mutex> lk(g_device_mu);
+        if (g_device < 0 && ordinal >= 0 && ordinal < kmb200_device_count()) g_device = ordinal;
+    }
+    if (ordinal < 0 || ordinal >= kmb200_device_count()) {
+        throw_runtime(env, "c_setDevice: no such CUDA device");
+        return -1;
+    }
+    return resolve_device();
 }
 
 JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneCCL_00024_c_1cleanup(JNIEnvPtr, jobject) {
@@ -251,6 +386,38 @@ JNIEXPORT jlong JNICALL Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMean
     seti(env, resultObj, fid(env, clazz, "iterationNum", "I"), iters);
     setd(env, resultObj, fid(env, clazz, "totalCost", "D"), cost);
     return reinterpret_cast<jlong>(out);
+}
+
+// The summary pass of KMeans.fit (spark-3.1.1/ml/clustering/KMeans.scala:359-368: model.transform + clusterSizes, one
+// more JVM pass over every row in the reference) on the GPU, over the table that is still resident after the fit.
+// predictions: int[local rows] or null; clusterSizes: long[k] (global sizes on every rank); returns the global cost
+// of the assignment.  Collective like the compute call.
+JNIEXPORT jdouble JNICALL Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansDALAssign(
+    JNIEnvPtr env, jobject, jlong pNumTabData, jlong pNumTabCenters, jintArray predictions, jlongArray clusterSizes) {
+    kmb200_table *table = reinterpret_cast<kmb200_table *>(pNumTabData);
+    Centers *cen = reinterpret_cast<Centers *>(pNumTabCenters);
+    if (!table || !cen) {
+        throw_runtime(env, "null table or centres handle");
+        return 0.0;
+    }
+    const int64_t n = kmb200_table_rows(table);
+    std::vector<int32_t> labels(predictions ? (size_t)n : 0);
+    std::vector<int64_t> sizes((size_t)cen->k);
+    double cost = 0.0;
+    if (kmb200_assign(table, g_comm, cen->v.data(), cen->k, cen->d, predictions ? labels.data() : nullptr, sizes.data(),
+                      &cost) != 0) {
+        throw_runtime(env, kmb200_last_error());
+        return 0.0;
+    }
+    if (predictions) {
+        auto seti = slot<void (*)(JNIEnvPtr, jintArray, jsize, jsize, const jint *)>(env, kJniSetIntArrayRegion);
+        seti(env, predictions, 0, (jsize)n, labels.data());
+    }
+    if (clusterSizes) {
+        auto setl = slot<void (*)(JNIEnvPtr, jlongArray, jsize, jsize, const jlong *)>(env, kJniSetLongArrayRegion);
+        setl(env, clusterSizes, 0, (jsize)cen->k, reinterpret_cast<const jlong *>(sizes.data()));
+    }
+    return cost;
 }
 
 }  // extern "C"

@@ -594,7 +594,7 @@ segment_sums_kernel(const float *__restrict__ X, const double *__restrict__ cent
     const int start = offsets[j] + (chunk - chunk_off[j]) * kSegChunk;
     const int end = min(offsets[j + 1], start + kSegChunk);
 
-    extern __shared__ double sred[];  // [RPP][ld] for the cross-row reduction
+    __shared__ double sred[1024];  // [RPP][4 * TPR] of the current pass, for the cross-row reduction
     const int vec = ld >> 2;
     double cost = 0.0;
     for (int v0 = 0; v0 < vec; v0 += 256) {  // ld <= 1024 per pass of 256 float4 lanes
@@ -631,14 +631,15 @@ segment_sums_kernel(const float *__restrict__ X, const double *__restrict__ cent
 #undef KMB_ACC
         }
         // reduce the rpp row-lanes that share a column group (fixed order -> deterministic per chunk)
+        // (scratch laid out per pass: [rpp][4 * tpr] <= 1024 doubles whatever ld is)
         if (tr < rpp) {
-            double *dst = sred + (size_t)tr * ld + 4 * tv;
+            double *dst = sred + (size_t)tr * (4 * tpr) + 4 * (tv - v0);
             dst[0] = s0; dst[1] = s1; dst[2] = s2; dst[3] = s3;
         }
         __syncthreads();
         for (int c = threadIdx.x; c < 4 * tpr; c += blockDim.x) {
             double s = 0.0;
-            for (int r = 0; r < rpp; ++r) s += sred[(size_t)r * ld + 4 * v0 + c];
+            for (int r = 0; r < rpp; ++r) s += sred[(size_t)r * (4 * tpr) + c];
             part[(size_t)chunk * ld + 4 * v0 + c] = s;
         }
         __syncthreads();
@@ -698,7 +699,8 @@ __global__ void cost_sum_kernel(const double *__restrict__ costj, int k, int ld,
 __global__ void finalize_kernel(const double *__restrict__ red, const double *__restrict__ cent,
                                 double *__restrict__ cent_new, int k, int ld, int d, double tol, int32_t *flags) {
     const int j = blockIdx.x;
-    extern __shared__ double sdiff[];
+    constexpr int kCols = 2048;   // columns per pass (any d: the sum below continues across passes)
+    __shared__ double sdiff[kCols];
     const double cnt = red[(size_t)k * ld + j];
     if (cnt <= 0.0) {
         for (int c = threadIdx.x; c < d; c += blockDim.x) cent_new[(size_t)j * ld + c] = cent[(size_t)j * ld + c];
@@ -706,18 +708,21 @@ __global__ void finalize_kernel(const double *__restrict__ red, const double *__
         return;
     }
     const double inv = 1.0 / cnt;
-    for (int c = threadIdx.x; c < d; c += blockDim.x) {
-        const double nv = red[(size_t)j * ld + c] * inv;
-        const double df = nv - cent[(size_t)j * ld + c];
-        sdiff[c] = df * df;
-        cent_new[(size_t)j * ld + c] = nv;
+    double s = 0.0;   // thread 0 only: sequential over the columns, like the reference's loop
+    for (int c0 = 0; c0 < d; c0 += kCols) {
+        const int c1 = min(d, c0 + kCols);
+        for (int c = c0 + threadIdx.x; c < c1; c += blockDim.x) {
+            const double nv = red[(size_t)j * ld + c] * inv;
+            const double df = nv - cent[(size_t)j * ld + c];
+            sdiff[c - c0] = df * df;
+            cent_new[(size_t)j * ld + c] = nv;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            for (int c = c0; c < c1; ++c) s += sdiff[c - c0];
+        __syncthreads();
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double s = 0.0;
-        for (int c = 0; c < d; ++c) s += sdiff[c];
-        if (!(s <= tol * tol)) atomicAdd(&flags[0], 1);
-    }
+    if (threadIdx.x == 0 && !(s <= tol * tol)) atomicAdd(&flags[0], 1);
 }
 
 // ------------------------------------------------------------------ empty-cluster candidates

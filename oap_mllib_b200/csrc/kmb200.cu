@@ -83,8 +83,6 @@ static void env_overrides() {
     if (const char *e = getenv("KMB200_H16")) g_h16 = atoi(e) != 0;
 }
 static long long *g_role_prof = nullptr;  // device buffer, allocated by option "role_prof"
-static float *g_dbg_scores = nullptr;  // set only inside kmb200_debug_scores
-static cudaEvent_t *g_main_ev = nullptr;   // [2] events bracketing the main assign kernel of the current iteration (or null)
 
 // ------------------------------------------------------------------------------------ NCCL (dlopen)
 struct NcclApi {
@@ -92,6 +90,7 @@ struct NcclApi {
     ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
                               cudaStream_t) = nullptr;
     ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
@@ -116,6 +115,7 @@ static int nccl_load() {
     KMB_SYM(GetUniqueId, "ncclGetUniqueId")
     KMB_SYM(CommInitRank, "ncclCommInitRank")
     KMB_SYM(CommDestroy, "ncclCommDestroy")
+    KMB_SYM(CommAbort, "ncclCommAbort")
     KMB_SYM(AllReduce, "ncclAllReduce")
     KMB_SYM(AllGather, "ncclAllGather")
     KMB_SYM(GetErrorString, "ncclGetErrorString")
@@ -133,6 +133,7 @@ static int nccl_load() {
 struct kmb200_comm {
     ncclComm_t comm = nullptr;
     int world = 1, rank = 0;
+    bool broken = false;   // a collective or a kernel failed on it: destroy with ncclCommAbort (peers may never arrive)
 };
 
 // ------------------------------------------------------------------------------------ table
@@ -178,6 +179,10 @@ struct Workspace {
     bool scatter1 = false, scatter2 = false;   // labels_c -> (labels_c1 | labels) via cand_list; labels_c1 -> labels via cand1_list
     bool two_level_active = false;    // set by launch_assign for the launch_recheck that follows
     bool two_level_off = false;       // the candidate buffer overflowed once in this fit: full bookkeeping from then on
+    // per-call state (one fit / assign at a time per table)
+    float *dbg_scores = nullptr;      // set only inside kmb200_debug_scores
+    cudaEvent_t *main_ev = nullptr;   // [2] events bracketing the main assign kernel of the current iteration (or null)
+    bool ready = false;               // every buffer and tensor map below exists (set last by ws_prepare)
     // pinned host mirror read once per iteration
     struct Host {
         int32_t flags[2];
@@ -187,6 +192,26 @@ struct Workspace {
         int32_t cand1_count;
         double cost;
     } *host = nullptr;
+};
+
+// CUDA events of one table (created on the table's device), reused by every fit
+struct EventPool {
+    std::vector<cudaEvent_t> ev;
+    int per_iter = 9;   // 7 phase boundaries + 2 around the main assign kernel
+    int cap_iters = 0;
+    ~EventPool() {
+        for (auto e : ev) cudaEventDestroy(e);
+    }
+    int ensure(int iters) {
+        iters = std::min(iters, 1024);
+        while ((int)ev.size() < iters * per_iter) {
+            cudaEvent_t e;
+            CU_TRY(cudaEventCreate(&e));
+            ev.push_back(e);
+        }
+        cap_iters = iters;
+        return 0;
+    }
 };
 
 struct kmb200_table {
@@ -202,6 +227,7 @@ struct kmb200_table {
     cudaStream_t stream = nullptr;
     int num_sms = 0;
     Workspace ws;
+    EventPool events;
 };
 
 static void ws_free(Workspace &w) {
@@ -386,7 +412,7 @@ static int append_rows(kmb200_table *t, int64_t row0, const T *rows, int64_t nro
         }
     } else {
         // FP64 input: staged in device memory, rounded to FP32 by a kernel
-        const size_t want = std::min<size_t>((size_t)nrows * t->d * sizeof(T), (size_t)256 << 20);
+        const size_t want = std::min<size_t>((size_t)nrows * t->d * sizeof(T), std::max<size_t>(g_stage_bytes, (size_t)t->d * sizeof(T)));
         if (t->stage_bytes < want) {
             if (t->stage) cudaFree(t->stage);
             t->stage = nullptr;
@@ -615,7 +641,8 @@ extern "C" int32_t kmb200_comm_rank(const kmb200_comm *c) { return c ? c->rank :
 extern "C" int32_t kmb200_comm_size(const kmb200_comm *c) { return c ? c->world : 1; }
 extern "C" int kmb200_comm_destroy(kmb200_comm *c) {
     if (!c) return 0;
-    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    if (c->comm && c->broken && g_nccl.CommAbort) g_nccl.CommAbort(c->comm);
+    else if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     delete c;
     return 0;
 }
@@ -632,9 +659,19 @@ static int dmalloc(T **p, size_t count) {
     return 0;
 }
 
+static int ws_prepare_impl(kmb200_table *t, int k);
 static int ws_prepare(kmb200_table *t, int k) {
     Workspace &w = t->ws;
-    if (w.k == k && w.cent && w.bn == pick_bn(k)) return 0;
+    if (w.ready && w.k == k && w.bn == pick_bn(k)) return 0;
+    const int rc = ws_prepare_impl(t, k);
+    if (rc != 0) {   // e.g. out of memory half way: leave nothing behind that a later call could mistake for a workspace
+        cudaGetLastError();
+        ws_free(w);
+    }
+    return rc;
+}
+static int ws_prepare_impl(kmb200_table *t, int k) {
+    Workspace &w = t->ws;
     ws_free(w);
     w.k = k;
     w.bn = pick_bn(k);
@@ -681,6 +718,7 @@ static int ws_prepare(kmb200_table *t, int k) {
     KM_TRY(make_map(&w.tm_blo_half, w.blo, (uint64_t)w.kpad, ld, (uint32_t)std::max(w.bn / 2, 8)));
     KM_TRY(make_map_bf16(&w.tm_bcorr_half, w.bcorr, (uint64_t)w.kpad, 2 * ld, (uint32_t)std::max(w.bn / 2, 8)));
     KM_TRY(make_map_bf16(&w.tm_b16_half, w.b16, (uint64_t)w.kpad, 2 * ld64(t->ld), (uint32_t)std::max(w.bn / 2, 8), true));
+    w.ready = true;
     return 0;
 }
 
@@ -689,11 +727,10 @@ static int ws_prepare(kmb200_table *t, int k) {
 // accumulator in TMEM is updated 3*ld/8 times per score and each update may lose up to one ulp
 // (the tensor core truncates), plus the TF32 hi/lo split residuals (~3*2^-22) and the FP32 norm /
 // final add; measured maxima sit at ~0.35 of this (tests/test_gpu_parity.py).
-static bool g_eps_bf16 = false;   // set by the launcher that uses the BF16-correction kernel
-static float score_eps(int ld) {
+static float score_eps(int ld, bool bf16_corr = false) {
     // BF16 corrections: 2*ld/8 accumulator updates + split residuals (each correction product carries
     // two BF16 roundings on a term that is already 2^-11 of the main one: <= 2^-18 in total)
-    if (g_passes == 3 && g_eps_bf16) return (float)(g_eps_scale * ldexp(2.0 * ld / 8.0 + 16.0 + 64.0, -24));
+    if (g_passes == 3 && bf16_corr) return (float)(g_eps_scale * ldexp(2.0 * ld / 8.0 + 16.0 + 64.0, -24));
     if (g_passes == 3) return (float)(g_eps_scale * ldexp(3.0 * ld / 8.0 + 16.0, -24));
     return (float)(g_eps_scale * 1.25 * ldexp(1.0, -10));
 }
@@ -724,7 +761,7 @@ static int launch_assign_bn(kmb200_table *t) {
     p.stages = stages;
     p.passes = g_passes;
     p.eps = score_eps(t->ld);
-    p.dbg_scores = g_dbg_scores;
+    p.dbg_scores = w.dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;
     p.role_prof = g_role_prof;
@@ -762,7 +799,7 @@ static int launch_assign2_bn(kmb200_table *t) {
     p.stages = stages;
     p.passes = 3;
     p.eps = score_eps(t->ld);
-    p.dbg_scores = g_dbg_scores;
+    p.dbg_scores = w.dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;
     p.role_prof = g_role_prof;
@@ -820,10 +857,8 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     p.num_k_chunks = kc;
     p.stages = rb;
     p.passes = 3;
-    g_eps_bf16 = BF16C;
-    p.eps = score_eps(t->ld);
-    g_eps_bf16 = false;
-    p.dbg_scores = g_dbg_scores;
+    p.eps = score_eps(t->ld, BF16C);
+    p.dbg_scores = w.dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;
     p.role_prof = g_role_prof;
@@ -867,7 +902,7 @@ constexpr int64_t kTwoLevelMinRows = 1 << 18;
 // (Re)allocates the candidate buffers when the two-level scheme applies to this table; false = use full bookkeeping.
 static bool two_level_prepare(kmb200_table *t) {
     Workspace &w = t->ws;
-    if (!g_two_level || w.two_level_off || g_dbg_scores) return false;
+    if (!g_two_level || w.two_level_off || w.dbg_scores) return false;
     if (g_two_level == 1 && t->rows < kTwoLevelMinRows) return false;
     int64_t cap = g_cand_cap > 0 ? g_cand_cap : t->rows / 16;
     cap = std::max<int64_t>((cap + kTileM - 1) / kTileM * kTileM, 2 * kTileM);
@@ -964,7 +999,7 @@ static int launch_assign_h16_bn(kmb200_table *t, const H16Src &src) {
     p.stages = Cfg::x_slots(kc) | (Cfg::b_groups(kc) << 8);
     p.passes = 3;
     p.eps = NP == 1 ? score_eps_h16_one(t->ld) : score_eps_h16(t->ld);
-    p.dbg_scores = g_dbg_scores;
+    p.dbg_scores = w.dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;
     p.role_prof = src.prof ? g_role_prof : nullptr;
@@ -1029,11 +1064,11 @@ static int launch_h16_fine(kmb200_table *t, const H16Src &src, const float *srcX
     fast.cand_list = w.cand_list;
     fast.cand_count = w.flag_count + 2;
     fast.cand_cap = w.cand_cap;
-    if (bracket && g_main_ev) CU_TRY(cudaEventRecord(g_main_ev[0], t->stream));
+    if (bracket && w.main_ev) CU_TRY(cudaEventRecord(w.main_ev[0], t->stream));
     KM_TRY((launch_assign_h16_mode<2, 3>(t, fast)));
-    if (bracket && g_main_ev) {
-        CU_TRY(cudaEventRecord(g_main_ev[1], t->stream));
-        g_main_ev = nullptr;   // recorded: the caller must not bracket the whole phase
+    if (bracket && w.main_ev) {
+        CU_TRY(cudaEventRecord(w.main_ev[1], t->stream));
+        w.main_ev = nullptr;   // recorded: the caller must not bracket the whole phase
     }
     // The candidate count decides what runs next, so it is read back here: one short host round trip.  Overflow of
     // the candidate buffer (a large share of near-ties) switches this fit to the single-pass scheme on the spot.
@@ -1065,21 +1100,21 @@ static int launch_assign_h16(kmb200_table *t) {
     w.recheck_level = 0;
     w.scatter1 = w.scatter2 = false;
     H16Src table = {&w.tm_x, t->xnorm, w.labels, t->rows, nullptr, w.flag_count + 2, 0, true};
-    if (g_dbg_scores) return g_dbg_products == 1 ? launch_assign_h16_mode<1, 1>(t, table) : launch_assign_h16_mode<1, 3>(t, table);
+    if (w.dbg_scores) return g_dbg_products == 1 ? launch_assign_h16_mode<1, 1>(t, table) : launch_assign_h16_mode<1, 3>(t, table);
     const bool two_level = two_level_prepare(t);
     if (two_level && cascade_prepare(t)) {
         H16Src coarse = table;
         coarse.cand_list = w.cand1_list;
         coarse.cand_count = w.flag_count + 3;
         coarse.cand_cap = w.cand1_cap;
-        cudaEvent_t *ev = g_main_ev;
+        cudaEvent_t *ev = w.main_ev;
         if (ev) CU_TRY(cudaEventRecord(ev[0], t->stream));
         KM_TRY((launch_assign_h16_mode<2, 1>(t, coarse)));
         if (ev) CU_TRY(cudaEventRecord(ev[1], t->stream));
         KM_TRY(read_count(t, &w.host->cand1_count, w.flag_count + 3));
         if ((int64_t)w.host->cand1_count <= w.cand1_cap) {
             g_prof.coarse_undecided_rows += w.host->cand1_count;
-            g_main_ev = nullptr;   // bracketed above
+            w.main_ev = nullptr;   // bracketed above
             w.scatter1 = true;
             w.recheck_level = 1;
             if (w.host->cand1_count == 0) return 0;
@@ -1098,7 +1133,7 @@ static int launch_assign_pair(kmb200_table *t, bool *applicable) {
 #define KMB_PAIR(BN_) \
     return !g_corr ? launch_assign_pair_bn<BN_, 0>(t, applicable) \
                    : !g_ss ? launch_assign_pair_bn<BN_, 1>(t, applicable) \
-                   : g_dbg_scores ? launch_assign_pair_bn<BN_, 3>(t, applicable) : launch_assign_pair_bn<BN_, 2>(t, applicable)
+                   : t->ws.dbg_scores ? launch_assign_pair_bn<BN_, 3>(t, applicable) : launch_assign_pair_bn<BN_, 2>(t, applicable)
         case 32: KMB_PAIR(32);
         case 64: KMB_PAIR(64);
         case 128: KMB_PAIR(128);
@@ -1276,8 +1311,7 @@ static int launch_bucket(kmb200_table *t) {
 static int launch_accumulate(kmb200_table *t) {
     Workspace &w = t->ws;
     const int ld = t->ld;
-    const size_t sh = (size_t)std::max(8 * 1024, ld * 8);
-    segment_sums_kernel<<<(unsigned)w.max_chunks, 256, sh, t->stream>>>(t->X, w.cent, w.order, w.offsets, w.chunk_off,
+    segment_sums_kernel<<<(unsigned)w.max_chunks, 256, 0, t->stream>>>(t->X, w.cent, w.order, w.offsets, w.chunk_off,
                                                                         w.k, ld, w.part, w.cpart);
     CU_TRY(cudaGetLastError());
     segment_reduce_kernel<<<w.k, 128, 0, t->stream>>>(w.part, w.cpart, w.offsets, w.chunk_off, w.k, ld, w.red, w.costj);
@@ -1291,7 +1325,11 @@ static int launch_accumulate(kmb200_table *t) {
 static int do_allreduce(kmb200_table *t, kmb200_comm *comm) {
     if (!comm || comm->world == 1) return 0;
     Workspace &w = t->ws;
-    NCCL_TRY(g_nccl.AllReduce(w.red, w.red, (size_t)w.k * t->ld + w.k + 1, ncclDouble, ncclSum, comm->comm, t->stream));
+    const ncclResult_t r = g_nccl.AllReduce(w.red, w.red, (size_t)w.k * t->ld + w.k + 1, ncclDouble, ncclSum, comm->comm, t->stream);
+    if (r != ncclSuccess) {
+        comm->broken = true;
+        return fail(KMB200_ERR_COMM, "ncclAllReduce failed: %s", g_nccl.GetErrorString(r));
+    }
     return 0;
 }
 
@@ -1427,26 +1465,6 @@ static int handle_empty_clusters(kmb200_table *t, kmb200_comm *comm, int m, doub
 }
 
 // ------------------------------------------------------------------------------------ profile
-struct EventPool {
-    std::vector<cudaEvent_t> ev;
-    int per_iter = 9;   // 7 phase boundaries + 2 around the main assign kernel
-    int cap_iters = 0;
-    ~EventPool() {
-        for (auto e : ev) cudaEventDestroy(e);
-    }
-    int ensure(int iters) {
-        iters = std::min(iters, 1024);
-        while ((int)ev.size() < iters * per_iter) {
-            cudaEvent_t e;
-            CU_TRY(cudaEventCreate(&e));
-            ev.push_back(e);
-        }
-        cap_iters = iters;
-        return 0;
-    }
-};
-static thread_local EventPool g_events;
-
 static void prof_reset() { memset(&g_prof, 0, sizeof(g_prof)); }
 
 extern "C" int kmb200_get_profile(kmb200_profile *out) {
@@ -1456,6 +1474,14 @@ extern "C" int kmb200_get_profile(kmb200_profile *out) {
 }
 
 // ------------------------------------------------------------------------------------ the driver
+// Compute calls on one device run one at a time: the one-pass small-k kernel keeps its centres in __constant__
+// memory, which every table on a device shares, and the tunables of kmb200_set_option are process-wide.  Calls
+// on different devices run concurrently.
+static std::mutex g_device_mu[64];
+struct DeviceLock {
+    std::unique_lock<std::mutex> lk;
+    explicit DeviceLock(int dev) : lk(g_device_mu[dev & 63]) {}
+};
 static int check_fit_args(kmb200_table *t, const double *centers, int k, int d) {
     if (!t || !centers) return fail(KMB200_ERR_ARG, "null table or centres");
     if (k <= 0) return fail(KMB200_ERR_ARG, "k must be positive (got %d)", k);
@@ -1464,12 +1490,23 @@ static int check_fit_args(kmb200_table *t, const double *centers, int k, int d) 
     return 0;
 }
 
+static int fit_impl(kmb200_table *t, kmb200_comm *comm, const double *init_centers, int32_t k, int32_t d, double tol,
+                    int32_t max_iter, double *out_centers, double *out_cost, int32_t *out_iters);
 extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init_centers, int32_t k, int32_t d,
                           double tol, int32_t max_iter, double *out_centers, double *out_cost, int32_t *out_iters) {
+    const int rc = fit_impl(t, comm, init_centers, k, d, tol, max_iter, out_centers, out_cost, out_iters);
+    // a rank that fails inside the collective loop leaves its peers waiting: the communicator is torn down with
+    // ncclCommAbort rather than ncclCommDestroy
+    if (rc != 0 && rc != KMB200_ERR_ARG && rc != KMB200_ERR_LIMIT && comm) comm->broken = true;
+    return rc;
+}
+static int fit_impl(kmb200_table *t, kmb200_comm *comm, const double *init_centers, int32_t k, int32_t d, double tol,
+                    int32_t max_iter, double *out_centers, double *out_cost, int32_t *out_iters) {
     KM_TRY(check_fit_args(t, init_centers, k, d));
     if (!out_centers || !out_cost || !out_iters) return fail(KMB200_ERR_ARG, "fit: null output");
     if (max_iter < 0) return fail(KMB200_ERR_ARG, "fit: max_iter must be >= 0");
     if (comm && comm->world > 1) KM_TRY(nccl_load());
+    DeviceLock device_lock(t->device);
     CU_TRY(cudaSetDevice(t->device));
     KM_TRY(require_device());
     prof_reset();
@@ -1478,7 +1515,7 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
     cudaStream_t st = t->stream;
     KM_TRY(upload_centers(t, init_centers, k, d));
     KM_TRY(launch_split(t));
-    KM_TRY(g_events.ensure(max_iter));
+    KM_TRY(t->events.ensure(max_iter));
     w.two_level_off = false;
     w.cascade_off = false;
 
@@ -1486,11 +1523,11 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
     int it = 0;
     bool converged = false;
     const bool fused = fused_applies(t);
-    const int P = g_events.per_iter;
-    std::vector<char> main_timed((size_t)std::max(g_events.cap_iters, 1), 0);
+    const int P = t->events.per_iter;
+    std::vector<char> main_timed((size_t)std::max(t->events.cap_iters, 1), 0);
     for (it = 0; it < max_iter && !converged; ++it) {
-        const bool timed = it < g_events.cap_iters;
-        cudaEvent_t *ev = timed ? &g_events.ev[(size_t)it * P] : nullptr;
+        const bool timed = it < t->events.cap_iters;
+        cudaEvent_t *ev = timed ? &t->events.ev[(size_t)it * P] : nullptr;
         if (timed) CU_TRY(cudaEventRecord(ev[0], st));
         if (fused) {
             KM_TRY(launch_fused(t));   // distances + argmin + sums + cost in one read of X
@@ -1500,12 +1537,12 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
                 CU_TRY(cudaEventRecord(ev[3], st));
             }
         } else {
-            g_main_ev = timed ? ev + 7 : nullptr;
+            w.main_ev = timed ? ev + 7 : nullptr;
             KM_TRY(launch_assign(t));
             if (timed) CU_TRY(cudaEventRecord(ev[1], st));
-            // the two-level launcher brackets its main kernel itself (and clears g_main_ev); otherwise the phase IS the kernel
-            const bool main_separate = timed && g_main_ev == nullptr;
-            g_main_ev = nullptr;
+            // the two-level launcher brackets its main kernel itself (and clears w.main_ev); otherwise the phase IS the kernel
+            const bool main_separate = timed && w.main_ev == nullptr;
+            w.main_ev = nullptr;
             if (timed) main_timed[it] = main_separate;
             KM_TRY(launch_recheck(t));
             if (timed) CU_TRY(cudaEventRecord(ev[2], st));
@@ -1517,7 +1554,7 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
         KM_TRY(do_allreduce(t, comm));
         if (timed) CU_TRY(cudaEventRecord(ev[5], st));
         CU_TRY(cudaMemsetAsync(w.flags, 0, 4 * sizeof(int32_t), st));
-        finalize_kernel<<<k, 128, (size_t)d * sizeof(double), st>>>(w.red, w.cent, w.cent2, k, t->ld, d, tol, w.flags);
+        finalize_kernel<<<k, 128, 0, st>>>(w.red, w.cent, w.cent2, k, t->ld, d, tol, w.flags);
         CU_TRY(cudaGetLastError());
         g_prof.kernel_launches++;
         // one host round trip per iteration: the reference's iteration count must be reproduced
@@ -1545,9 +1582,9 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
     *out_cost = cost;
     *out_iters = it;
     g_prof.iterations = it;
-    const int timed_iters = std::min(it, g_events.cap_iters);
+    const int timed_iters = std::min(it, t->events.cap_iters);
     for (int i = 0; i < timed_iters; ++i) {
-        cudaEvent_t *ev = &g_events.ev[(size_t)i * P];
+        cudaEvent_t *ev = &t->events.ev[(size_t)i * P];
         float ms[6] = {0, 0, 0, 0, 0, 0};
         for (int s = 0; s < 6; ++s) cudaEventElapsedTime(&ms[s], ev[s], ev[s + 1]);
         g_prof.assign_ms += ms[0];
@@ -1562,7 +1599,7 @@ extern "C" int kmb200_fit(kmb200_table *t, kmb200_comm *comm, const double *init
     }
     if (timed_iters > 0) {
         float tot = 0.f;
-        cudaEventElapsedTime(&tot, g_events.ev[0], g_events.ev[(size_t)(timed_iters - 1) * P + 6]);
+        cudaEventElapsedTime(&tot, t->events.ev[0], t->events.ev[(size_t)(timed_iters - 1) * P + 6]);
         g_prof.total_ms = tot;
     }
     return 0;
@@ -1572,14 +1609,15 @@ extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *c
                              int32_t *labels_host, int64_t *sizes_host, double *cost_host) {
     KM_TRY(check_fit_args(t, centers, k, d));
     if (comm && comm->world > 1) KM_TRY(nccl_load());
+    DeviceLock device_lock(t->device);
     CU_TRY(cudaSetDevice(t->device));
     KM_TRY(require_device());
     prof_reset();
     KM_TRY(ws_prepare(t, k));
     Workspace &w = t->ws;
     cudaStream_t st = t->stream;
-    KM_TRY(g_events.ensure(1));
-    cudaEvent_t *ev = &g_events.ev[0];
+    KM_TRY(t->events.ensure(1));
+    cudaEvent_t *ev = &t->events.ev[0];
     KM_TRY(upload_centers(t, centers, k, d));
     w.two_level_off = false;
     w.cascade_off = false;
@@ -1633,6 +1671,7 @@ extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *c
 extern "C" int kmb200_debug_scores(kmb200_table *t, const double *centers, int32_t k, int32_t d, float *scores_host,
                                    int32_t *kpad_out) {
     KM_TRY(check_fit_args(t, centers, k, d));
+    DeviceLock device_lock(t->device);
     CU_TRY(cudaSetDevice(t->device));
     KM_TRY(require_device());
     KM_TRY(ws_prepare(t, k));
@@ -1645,9 +1684,9 @@ extern "C" int kmb200_debug_scores(kmb200_table *t, const double *centers, int32
     if (!rc) rc = launch_split(t);
     const int simt = g_force_simt;
     g_force_simt = 0;
-    g_dbg_scores = dev;
+    w.dbg_scores = dev;
     if (!rc) rc = launch_assign(t);
-    g_dbg_scores = nullptr;
+    w.dbg_scores = nullptr;
     g_force_simt = simt;
     cudaError_t e = cudaMemcpyAsync(scores_host, dev, (size_t)t->rows * w.kpad * sizeof(float), cudaMemcpyDeviceToHost, t->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
@@ -1678,6 +1717,8 @@ extern "C" int kmb200_cluster_sizes_noalloc(const int32_t *labels_dev, int64_t n
     if (!labels_dev && n > 0) return fail(KMB200_ERR_ARG, "cluster_sizes_noalloc: labels_dev is null");
     if (!sizes_dev) return fail(KMB200_ERR_ARG, "cluster_sizes_noalloc: sizes_dev is null");
     if (n < 0 || k <= 0) return fail(KMB200_ERR_ARG, "cluster_sizes_noalloc: n must be >= 0 and k > 0");
+    if (n > 2147483647LL)   // the built-in counters are 32-bit: one cluster could hold every row
+        return fail(KMB200_ERR_LIMIT, "cluster_sizes_noalloc: n = %lld is beyond the 2^31-1 rows the 32-bit scratch counters can hold", (long long)n);
     if (k > kNoAllocMaxClusters)
         return fail(KMB200_ERR_LIMIT,
                     "cluster_sizes_noalloc: k = %d is larger than the built-in scratch of %d counters; use "
@@ -1786,4 +1827,4 @@ extern "C" int kmb200_set_option(const char *name, double value) {
 }
 
 extern "C" const char *kmb200_last_error(void) { return g_err.c_str(); }
-extern "C" const char *kmb200_version(void) { return "kmeans_b200 0.1 (sm_100a; tcgen05 3xTF32 assign)"; }
+extern "C" const char *kmb200_version(void) { return "kmeans_b200 0.2 (sm_100a; tcgen05 cta_group::2 FP16-split assign with FP64 re-check, FP64 accumulate)"; }
