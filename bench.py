@@ -26,6 +26,20 @@ import sys
 import threading
 import time
 
+
+def _reference_arm_requested() -> bool:
+    a = sys.argv[1:]
+    return any(x == "--impl=reference" for x in a) or any(x == "--impl" and i + 1 < len(a) and a[i + 1] == "reference"
+                                                          for i, x in enumerate(a))
+
+
+if _reference_arm_requested():
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to its workers when nproc > 1; the CPU arm needs every host
+    # core (set before NumPy / OpenBLAS / OpenMP load)
+    _n = str(len(os.sched_getaffinity(0)))
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_v] = _n
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -96,36 +110,44 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------- CPU arm
-def cpu_lloyd_steps(d, k, rows_full, steps, warmup, sample_rows):
-    """Times `steps` Lloyd iterations of the FP64 oracle on a `sample_rows` sample of the workload
-    and returns iterations/s extrapolated linearly in N to the full workload."""
-    from oracle import kmeans_oracle as ko
-    try:
-        from threadpoolctl import threadpool_info
-        threads = max([p.get("num_threads", 1) for p in threadpool_info()] + [1])
-    except Exception:
-        threads = os.cpu_count() or 1
-    cores = len(os.sched_getaffinity(0))
-    rng = np.random.default_rng(42)
-    centres = rng.uniform(-10, 10, (k, d)).astype(np.float32)
-    lab = rng.integers(0, k, sample_rows)
-    X = centres[lab]
-    X += rng.standard_normal((sample_rows, d), dtype=np.float32)
-    X = X.astype(np.float64)          # the reference's path is FP64 end to end (KMeansDALImpl.cpp:32)
-    C = ko.row_init_centers(X, k)
-    times = []
-    for i in range(warmup + steps):
-        t0 = time.perf_counter()
-        C, _, _, _ = ko.lloyd_step([X], C)
-        if i >= warmup:
-            times.append(time.perf_counter() - t0)
-    t_step = float(np.mean(times))
-    value = (sample_rows / rows_full) / t_step
-    return {"value": value, "unit": UNIT, "cores": min(cores, threads) if threads else cores, "kind": "port",
-            "sample": f"{sample_rows} of {rows_full} rows x {d}, k={k}, FP64 numpy/OpenBLAS restatement of the "
-                      f"oneDAL step (oracle/kmeans_oracle.py), {steps} iteration(s) of {t_step:.2f} s, "
-                      f"extrapolated linearly in N",
-            "seconds_per_sample_iteration": t_step}
+def make_config(args, world):
+    """The `config` object, identical in both arms (the GPU arm and --impl reference)."""
+    rows, d, k, desc = WORKLOADS[args.workload]
+    if args.rows:
+        rows = args.rows
+    return {"workload": desc, "rows_total": rows, "rows_per_gpu": rows // world, "d": d, "k": k,
+            "parallelism": f"rows sharded over {world} GPU(s), 1 NCCL all-reduce / iteration",
+            "l2": "inputs (rows_per_gpu*d*4 bytes) far larger than the 126 MB L2; no flush needed",
+            "init": "rows floor(j*N/k) of the whole table (the same centres for every GPU count)",
+            "tol": "disabled (exactly K iterations)"}
+
+
+def cpu_baseline(d, k, rows_full, sample_rows=0, which=None):
+    """Lloyd iterations/s of the CPU stand-ins for the reference's oneDAL step (oracle/cpu_baselines.py) on a
+    bounded row sample, extrapolated linearly in N to the full workload; `value` is the FASTEST of them."""
+    from oracle import cpu_baselines as cb
+    if not sample_rows:
+        sample_rows = int(0.8e12 / (2.0 * d * k))                    # ~0.8 TFLOP of distance work per iteration
+        sample_rows = min(sample_rows, int(4e9 / (12.0 * d)))        # and <= 4 GB of host rows (FP32 + FP64 copies)
+    sample_rows = max(20_000, min(sample_rows, rows_full))
+    kw = {"which": which} if which else {}
+    secs, cores = cb.run_all(d, k, sample_rows, **kw)
+    flops = 2.0 * sample_rows * d * k
+    cand = {}
+    for name, t in secs.items():
+        if name.endswith("_error"):
+            cand[name] = t
+        elif t:
+            cand[name] = {"seconds_per_sample_iteration": t, "iter_per_s_full_workload": (sample_rows / rows_full) / t,
+                          "gflops": flops / t / 1e9, "gbytes_per_s": sample_rows * d * (4 if name.endswith("f32") else 8) / t / 1e9}
+    timed = {n: c for n, c in cand.items() if isinstance(c, dict)}
+    best = min(timed, key=lambda n: timed[n]["seconds_per_sample_iteration"])
+    return {"value": timed[best]["iter_per_s_full_workload"], "unit": UNIT, "cores": cores, "kind": "port",
+            "which": best, "gflops": timed[best]["gflops"],
+            "sample": f"{sample_rows} of {rows_full} rows x {d}, k={k}: one Lloyd iteration per stand-in, extrapolated "
+                      f"linearly in N; fastest = {best} ({timed[best]['seconds_per_sample_iteration']:.2f} s per sample "
+                      f"iteration on {cores} cores). oneDAL itself cannot run in this image (no oneDAL/oneCCL/JVM)",
+            "candidates": cand}
 
 
 def run_reference(args, rank, world):
@@ -134,18 +156,18 @@ def run_reference(args, rank, world):
     rows, d, k, desc = WORKLOADS[args.workload]
     if args.rows:
         rows = args.rows
-    sample = args.cpu_sample_rows or max(50_000, int(2.0e12 / (2.0 * d * k)))   # ~2 TFLOP of dgemm per step
-    sample = min(sample, rows)
-    res = cpu_lloyd_steps(d, k, rows, max(1, args.steps), min(args.warmup, 1), sample)
+    # bounded whatever --steps says: one sample iteration per stand-in (sklearn: 1 + 3), a few minutes at most
+    res = cpu_baseline(d, k, rows, args.cpu_sample_rows, which=("sklearn_f64", "sklearn_f32", "blocked_f64"))
     line = {"impl": "reference", "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1000.0 / res["value"], "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": desc, "rows": rows, "d": d, "k": k},
+            "vs_baseline": None, "dtype": "f32" if res["which"].endswith("f32") else "f64", "data": "synthetic",
+            "config": make_config(args, world),
             "cpu_baseline": res,
             "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "oneDAL/oneCCL/JVM are absent from this image: the reference's own build cannot run; this is "
-                    "the CPU restatement of its algorithm on the box's host cores"}
+                    "the fastest CPU stand-in for its algorithm on the box's host cores (each timed for a bounded "
+                    "number of iterations on a row sample, whatever --steps says)"}
     emit(line)
 
 
@@ -201,15 +223,15 @@ def run_ours(args, rank, local_rank, world):
         m.OneCCL.init(world, rank, ident[0])
         comm = m.OneCCL.comm()
 
-    # ---- initial centres: rows floor(j*n/k) of rank 0's shard, broadcast ------------------------
-    if rank == 0:
-        idx = (np.arange(k, dtype=np.int64) * n_local) // k
-        init = np.vstack([table.read_rows(int(i), 1) for i in idx]).astype(np.float64)
-    else:
-        init = np.empty((k, d), np.float64)
+    # ---- initial centres: rows floor(j*N/k) of the WHOLE table (each rank reads the ones it holds, the rest
+    # arrive by all-reduce), so every GPU count solves the same problem and final_cost must agree across N
+    init = np.zeros((k, d), np.float64)
+    for j, gi in enumerate(((np.arange(k, dtype=np.int64) * rows) // k).tolist()):
+        if row0 <= gi < row1:
+            init[j] = table.read_rows(gi - row0, 1)[0]
     if dist is not None:
         t = torch.from_numpy(init).cuda()
-        dist.broadcast(t, src=0)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
         init = t.cpu().numpy()
     init = np.ascontiguousarray(init)
 
@@ -248,9 +270,13 @@ def run_ours(args, rank, local_rank, world):
     launches = prof["kernel_launches"]
 
     peaks = load_peaks()
-    flops_per_launch = 2.0 * n_local * d * k           # ALGORITHMIC flops of one assign launch (one pass)
-    tf32_peak = 0.5 * peaks["bf16_sustained"]          # TF32 runs at half the bf16 tensor rate
-    achieved = flops_per_launch / (main_ms * 1e-3) / 1e12
+    variant = prof.get("assign_variant", -1)
+    acc_ms = max_over_ranks(prof["accumulate_ms"]) / args.steps
+    flops_per_launch = 2.0 * n_local * d * k           # ALGORITHMIC flops of one pass over this GPU's rows
+    bytes_per_launch = 4.0 * n_local * d               # ALGORITHMIC bytes of one pass
+    tf32_sus, tf32_burst = 0.5 * peaks["bf16_sustained"], 0.5 * peaks["bf16_burst"]   # TF32 = half the bf16 rate
+    # which roofline bounds this workload: the slower of 2ndk at the TF32 rate and 4nd at HBM bandwidth
+    bound = "tensor" if flops_per_launch / (tf32_sus * 1e12) >= bytes_per_launch / (peaks["hbm_gbs"] * 1e9) else "hbm"
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
@@ -258,44 +284,50 @@ def run_ours(args, rank, local_rank, world):
             tr = json.load(f)
         key = f"{args.workload}_n{world}"
         if key in tr and tr[key].get("rows") == n_local:
-            traffic = tr[key]["assign_dram_bytes_per_launch"]
-    h16 = d <= 256 and k > 16
-    cascade = h16 and prof.get("coarse_undecided_rows", 0) > 0
-    phase_achieved = flops_per_launch / (assign_ms * 1e-3) / 1e12
-    if cascade:
-        # The dominant kernel is the coarse pass: ONE FP16 product per score over all rows (the rows it cannot
-        # decide -- coarse_undecided_rows -- go through the three-product kernel afterwards, inside assign_phase_ms).
-        # Its hardware ceiling is the dense FP16/BF16 rate, i.e. MEASURED_PEAKS.json's own figure (no TF32 proxy).
-        peak = peaks["bf16_sustained"]
-        roofline = {"bound": "tensor",
-                    "kernel": "assign_pair_h16_kernel<128, 2, 1> (coarse pass of the cascade: tcgen05 cta_group::2, kind::f16, one product)",
-                    "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
-                    "peak_source": f"bf16_tflops_sustained of {peaks['source']} MEASURED_PEAKS.json (FP16 and BF16 MMAs run at the "
-                                   "same rate); kernel timed inside a long step",
-                    "algorithmic_flops_per_launch": flops_per_launch,
-                    "main_kernel_ms_per_launch": main_ms,
-                    "assign_phase_ms": assign_ms,
-                    "assign_phase_achieved": phase_achieved,
-                    "assign_phase_frac_of_tf32_proxy": phase_achieved / tf32_peak,
-                    "coarse_undecided_fraction": prof["coarse_undecided_rows"] / args.steps / n_local,
-                    "hbm_frac_of_step": (n_local * d * 4.0 / (ms_per_step * 1e-3) / 1e9) / peaks["hbm_gbs"]}
-        t32 = tf32_measured(phase_achieved)
-        if t32:
-            roofline["tf32_cublas_sustained_measured"] = t32["tf32_cublas_sustained_measured"]
-            roofline["assign_phase_frac_of_measured_tf32_sustained"] = t32["frac_of_measured_tf32_sustained"]
+            traffic = tr[key].get("dram_bytes_per_launch", tr[key].get("assign_dram_bytes_per_launch"))
+    names = {0: "fused_smallk_kernel (one read of X: distances, arg-min, FP64 sums and cost on the CUDA cores)",
+             1: "assign_pair_h16_kernel<BN, 2, 1> (coarse pass of the cascade: tcgen05 cta_group::2, kind::f16, one product)",
+             2: "assign_pair_h16_kernel<BN, 2, 3> (tcgen05 cta_group::2, kind::f16, three products, fast bookkeeping)",
+             3: "assign_pair_h16_kernel<BN, 0, 3> (tcgen05 cta_group::2, kind::f16, three products)",
+             4: "assign_pair_ss_kernel (tcgen05 cta_group::2, TF32 + BF16 corrections)",
+             5: "assign_tc2_kernel (tcgen05, 3xTF32, resident X)", 6: "assign_tc_kernel (tcgen05, 3xTF32, streaming)",
+             7: "recheck_kernel (FP64, CUDA cores)", 8: "assign_h16w_kernel (tcgen05 cta_group::2, kind::f16, d > 256)",
+             9: "fused_assign_accumulate (tcgen05 distances + FP64 accumulation in one read of X)"}
+    if variant != 0 and acc_ms > main_ms:
+        kern, kern_ms = "segment_sums_kernel (per-cluster FP64 sums and cost; second read of X)", acc_ms
     else:
-        roofline = {"bound": "tensor",
-                    "kernel": "assign_pair_h16_kernel<128, 2, 3> (tcgen05 cta_group::2, kind::f16, three products)" if h16 else "assign_tc_kernel (3xTF32)",
-                    "achieved": achieved, "peak": tf32_peak,
-                    "unit": "TFLOP/s", "frac": achieved / tf32_peak, "traffic": traffic,
-                    "peak_source": f"0.5 x bf16_tflops_sustained of {peaks['source']} MEASURED_PEAKS.json "
-                                   "(TF32 = half the bf16 rate); kernel timed inside a long step",
-                    "algorithmic_flops_per_launch": flops_per_launch,
-                    "tensor_time_in_tf32_passes": 1.5 if h16 else 3.0,   # three FP16 products = 1.5 TF32 passes of tensor time; 3xTF32 on the fallback kernel
-                    "main_kernel_ms_per_launch": main_ms,
-                    **tf32_measured(achieved),
-                    "assign_phase_ms": assign_ms,
-                    "hbm_frac_of_step": (n_local * d * 4.0 / (ms_per_step * 1e-3) / 1e9) / peaks["hbm_gbs"]}
+        kern, kern_ms = names.get(variant, "assign kernel"), main_ms
+    if bound == "hbm":
+        achieved, peak, unit = bytes_per_launch / (kern_ms * 1e-3) / 1e9, peaks["hbm_gbs"], "GB/s"
+        peak_source = f"hbm_gbs of {peaks['source']} MEASURED_PEAKS.json"
+    else:
+        achieved, unit = flops_per_launch / (kern_ms * 1e-3) / 1e12, "TFLOP/s"
+        if variant == 1:
+            # one FP16 product per score: the ceiling is the dense FP16/BF16 rate itself
+            peak, peak_source = peaks["bf16_sustained"], (f"bf16_tflops_sustained of {peaks['source']} MEASURED_PEAKS.json "
+                                                          "(FP16 and BF16 MMAs run at the same rate); kernel timed inside a long step")
+        else:
+            peak, peak_source = tf32_sus, (f"0.5 x bf16_tflops_sustained of {peaks['source']} MEASURED_PEAKS.json "
+                                           "(TF32 = half the bf16 rate); kernel timed inside a long step")
+    step_tflops_gpu = flops_per_launch / (ms_per_step * 1e-3) / 1e12        # per GPU, whole step, algorithmic
+    step_gbs_gpu = bytes_per_launch / (ms_per_step * 1e-3) / 1e9
+    roofline = {"bound": bound, "kernel": kern, "achieved": achieved, "peak": peak, "unit": unit,
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_source,
+                "algorithmic_flops_per_launch": flops_per_launch, "algorithmic_bytes_per_launch": bytes_per_launch,
+                "kernel_ms_per_launch": kern_ms, "main_assign_kernel_ms_per_launch": main_ms,
+                "assign_phase_ms": assign_ms,
+                # the whole step (every kernel, the all-reduce, the host round trips), per GPU, algorithmic work only
+                "step_tflops_per_gpu": step_tflops_gpu,
+                "step_frac_of_fp16_sustained": step_tflops_gpu / peaks["bf16_sustained"],
+                "step_frac_of_tf32_proxy_sustained": step_tflops_gpu / tf32_sus,
+                "step_frac_of_tf32_proxy_burst": step_tflops_gpu / tf32_burst,
+                "step_gbytes_per_s_per_gpu": step_gbs_gpu,
+                "step_frac_of_hbm": step_gbs_gpu / peaks["hbm_gbs"]}
+    if variant == 1:
+        roofline["coarse_undecided_fraction"] = prof["coarse_undecided_rows"] / args.steps / n_local
+    t32 = tf32_measured(achieved)
+    if t32:
+        roofline["tf32_cublas_sustained_measured"] = t32["tf32_cublas_sustained_measured"]
     phases = {kk: max_over_ranks(prof[kk]) / args.steps for kk in
               ("assign_ms", "recheck_ms", "bucket_ms", "accumulate_ms", "allreduce_ms", "finalize_ms")}
 
@@ -344,8 +376,7 @@ def run_ours(args, rank, local_rank, world):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        sample = args.cpu_sample_rows or max(50_000, int(2.0e12 / (2.0 * d * k)))
-        cpu = cpu_lloyd_steps(d, k, rows, 1, 0, min(sample, rows))
+        cpu = cpu_baseline(d, k, rows, args.cpu_sample_rows)
 
     if world > 1:
         m.OneCCL.cleanup()
@@ -355,16 +386,17 @@ def run_ours(args, rank, local_rank, world):
         return
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f16 two-term split products (fp32 accumulate), f64 re-check / sums / cost", "data": "synthetic",
-            "config": {"workload": desc, "rows_total": rows, "rows_per_gpu": n_local, "d": d, "k": k,
-                       "parallelism": f"rows sharded over {world} GPU(s), 1 NCCL all-reduce / iteration",
-                       "l2": "inputs (rows_per_gpu*d*4 bytes) far larger than the 126 MB L2; no flush needed",
-                       "init": "rows floor(j*n/k) of rank 0", "tol": "disabled (exactly K iterations)"},
+            "vs_baseline": None,
+            "dtype": ("f32 distances on the CUDA cores, f64 near-tie re-check / sums / cost" if variant == 0 else
+                      "f16 two-term split products (fp32 accumulate), f64 re-check / sums / cost"), "data": "synthetic",
+            "config": make_config(args, world),
             "tflops_algorithmic": 2.0 * rows * d * k / (ms_per_step * 1e-3) / 1e12,
             "wall_ms_per_step": wall_ms / args.steps, "phases_ms_per_step": phases,
             "rechecked_rows_per_step": prof["rechecked_rows"] / args.steps,
             "full_rechecks_per_step": prof["full_rechecks"] / args.steps,
             "coarse_undecided_rows_per_step": prof.get("coarse_undecided_rows", 0) / args.steps,
+            "assign_variant": variant, "cascade_dropped_at": prof.get("cascade_dropped_at", -1),
+            "empty_cluster_events": prof.get("empty_cluster_events", 0),
             "final_cost": cost, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cpu}
     emit(line)

@@ -156,6 +156,14 @@ typedef struct {
                                   second pass over the near-tie rows of the two-level scheme)    */
     int64_t coarse_undecided_rows; /* cascade: rows the one-product pass could not decide (summed over iterations;
                                       0 when the cascade is off)                                  */
+    int32_t cascade_dropped_at;    /* iteration (0-based) in which the coarse pass left more than cand1_frac of the
+                                      rows undecided and the fit went on without it; -1 = never     */
+    int32_t two_level_dropped_at;  /* iteration in which the near-tie copy overflowed and the fit went on with the
+                                      single-pass bookkeeping; -1 = never                            */
+    int32_t assign_variant;        /* what the LAST assignment step ran: 0 = one-pass small-k kernel (CUDA cores),
+                                      1 = FP16-split kernel, cascade, 2 = FP16-split, two-level, 3 = FP16-split, single
+                                      pass, 4 = CTA-pair TF32 kernels, 5 = single-CTA resident-X kernel, 6 = streaming
+                                      3xTF32 kernel, 7 = FP64 CUDA-core kernel ("force_simt")       */
 } kmb200_profile;
 int kmb200_get_profile(kmb200_profile *out);
 

@@ -22,7 +22,8 @@ class Profile(C.Structure):
     _fields_ = [("iterations", C.c_int32), ("kernel_launches", C.c_int32), ("rechecked_rows", C.c_int64),
                 ("empty_cluster_events", C.c_int32), ("full_rechecks", C.c_int64), ("total_ms", C.c_float), ("assign_ms", C.c_float),
                 ("recheck_ms", C.c_float), ("bucket_ms", C.c_float), ("accumulate_ms", C.c_float),
-                ("allreduce_ms", C.c_float), ("finalize_ms", C.c_float), ("assign_main_ms", C.c_float), ("coarse_undecided_rows", C.c_int64)]
+                ("allreduce_ms", C.c_float), ("finalize_ms", C.c_float), ("assign_main_ms", C.c_float), ("coarse_undecided_rows", C.c_int64),
+                ("cascade_dropped_at", C.c_int32), ("two_level_dropped_at", C.c_int32), ("assign_variant", C.c_int32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -1058,8 +1058,10 @@ static int launch_h16_fine(kmb200_table *t, const H16Src &src, const float *srcX
     Workspace &w = t->ws;
     if (!two_level) {
         w.recheck_level = level;
+        if (level == 0) g_prof.assign_variant = 3;
         return launch_assign_h16_mode<0, 3>(t, src);
     }
+    if (level == 0) g_prof.assign_variant = 2;
     H16Src fast = src;
     fast.cand_list = w.cand_list;
     fast.cand_count = w.flag_count + 2;
@@ -1075,6 +1077,7 @@ static int launch_h16_fine(kmb200_table *t, const H16Src &src, const float *srcX
     KM_TRY(read_count(t, &w.host->cand_count, w.flag_count + 2));
     if ((int64_t)w.host->cand_count > w.cand_cap) {
         w.two_level_off = true;
+        if (g_prof.two_level_dropped_at < 0) g_prof.two_level_dropped_at = g_prof.iterations;
         CU_TRY(cudaMemsetAsync(w.flag_count, 0, 3 * sizeof(int32_t), t->stream));   // [3] (the coarse count) stays
         w.recheck_level = level;
         return launch_assign_h16_mode<0, 3>(t, src);
@@ -1113,6 +1116,7 @@ static int launch_assign_h16(kmb200_table *t) {
         if (ev) CU_TRY(cudaEventRecord(ev[1], t->stream));
         KM_TRY(read_count(t, &w.host->cand1_count, w.flag_count + 3));
         if ((int64_t)w.host->cand1_count <= w.cand1_cap) {
+            g_prof.assign_variant = 1;
             g_prof.coarse_undecided_rows += w.host->cand1_count;
             w.main_ev = nullptr;   // bracketed above
             w.scatter1 = true;
@@ -1123,6 +1127,7 @@ static int launch_assign_h16(kmb200_table *t) {
             return launch_h16_fine(t, mid, w.xc1, 1, !w.two_level_off, false);
         }
         w.cascade_off = true;   // too many undecided rows: the coarse pass is not worth its time on this data
+        if (g_prof.cascade_dropped_at < 0) g_prof.cascade_dropped_at = g_prof.iterations;
         CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
     }
     return launch_h16_fine(t, table, t->X, 0, two_level && !w.two_level_off, true);
@@ -1191,6 +1196,7 @@ static int launch_fused_inst(kmb200_table *t, float eps) {
 // number of rows re-scored in FP64.
 static int launch_fused(kmb200_table *t) {
     Workspace &w = t->ws;
+    g_prof.assign_variant = 0;
     const int k = w.k, ld = t->ld, kp = fused_kp(k);
     CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
     const float eps = (float)(g_eps_scale * ldexp((double)ld + 4.0, -24));   // FP32 FMA chain of ld terms
@@ -1239,6 +1245,7 @@ static int launch_assign(kmb200_table *t) {
                                                              w.labels);
         CU_TRY(cudaGetLastError());
         g_prof.kernel_launches++;
+        g_prof.assign_variant = 7;
         return 0;
     }
     env_overrides();
@@ -1248,10 +1255,13 @@ static int launch_assign(kmb200_table *t) {
         if (g_cluster == 2 && row_tiles >= 2) {
             bool applicable = false;
             const int rc = launch_assign_pair(t, &applicable);
+            if (applicable) g_prof.assign_variant = 4;
             if (rc != 0 || applicable) return rc;
         }
+        g_prof.assign_variant = 5;
         return launch_assign2<1>(t);
     }
+    g_prof.assign_variant = 6;
     switch (w.bn) {
         case 16: return launch_assign_bn<16>(t);
         case 32: return launch_assign_bn<32>(t);
@@ -1465,7 +1475,10 @@ static int handle_empty_clusters(kmb200_table *t, kmb200_comm *comm, int m, doub
 }
 
 // ------------------------------------------------------------------------------------ profile
-static void prof_reset() { memset(&g_prof, 0, sizeof(g_prof)); }
+static void prof_reset() {
+    memset(&g_prof, 0, sizeof(g_prof));
+    g_prof.cascade_dropped_at = g_prof.two_level_dropped_at = -1;
+}
 
 extern "C" int kmb200_get_profile(kmb200_profile *out) {
     if (!out) return fail(KMB200_ERR_ARG, "get_profile: null");
@@ -1526,6 +1539,7 @@ static int fit_impl(kmb200_table *t, kmb200_comm *comm, const double *init_cente
     const int P = t->events.per_iter;
     std::vector<char> main_timed((size_t)std::max(t->events.cap_iters, 1), 0);
     for (it = 0; it < max_iter && !converged; ++it) {
+        g_prof.iterations = it;   // (the hand-off records of launch_assign_h16 read it)
         const bool timed = it < t->events.cap_iters;
         cudaEvent_t *ev = timed ? &t->events.ev[(size_t)it * P] : nullptr;
         if (timed) CU_TRY(cudaEventRecord(ev[0], st));
