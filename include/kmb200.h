@@ -217,6 +217,11 @@ int kmb200_cluster_sizes_noalloc(const int32_t *labels_dev, int64_t n, int32_t k
 int kmb200_debug_scores(kmb200_table *table, const double *centers, int32_t k, int32_t d, float *scores_host,
                         int32_t *kpad_out);
 
+/* Diagnostics (no reference counterpart): copies `bytes` bytes, starting `offset` bytes in, of one of the device
+ * arrays the last fit / assign on this table left behind ("labels", "flag_list", "flag_count", "cand_list",
+ * "labels_c", "cand1_list", "labels_c1", "xc", "xc1") to host memory.  Used by tools/repro_check.py. */
+int kmb200_debug_dump(kmb200_table *table, const char *name, size_t offset, void *out, size_t bytes);
+
 const char *kmb200_last_error(void);
 const char *kmb200_version(void);
 

@@ -39,14 +39,17 @@ struct PairH16Cfg {
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16 + kXchgBytes;
     static constexpr int kBudget = 227 * 1024 - 1024 - kTailBytes;
     static int group_bytes(int kc) { return ((kc + 1) / 2) * kBUnitBytes; }   // B operand of one centroid tile
-    // X ring slots (32-value chunks): as many as fit next to two B groups, at most one row tile, at most 8
+    // X ring slots (32-value chunks): as many as fit next to two B groups, at most one row tile, at most 8; an EVEN
+    // number >= 2, because each transform warpgroup owns half of them (see "xfull / xempty" in the barrier notes)
     static int x_slots(int kc) {
         int s = (kBudget - 2 * group_bytes(kc)) / kXStageBytes;
-        return s > kc ? kc : s;
+        if (s > kc) s = kc;
+        s &= ~1;
+        return s < 2 ? 2 : s;
     }
     static int b_groups(int kc) {
         int g = (kBudget - x_slots(kc) * kXStageBytes) / group_bytes(kc);
-        return g > 4 ? 4 : g;
+        return g >= 4 ? 4 : g == 3 ? 2 : g;   // 2 or 4: see "bfull" in the barrier notes of the kernel
     }
     static int smem_bytes(int kc) { return 1024 + x_slots(kc) * kXStageBytes + b_groups(kc) * group_bytes(kc) + kTailBytes; }
 };
@@ -66,6 +69,49 @@ struct PairH16Cfg {
 // NP: 3 = the three products above; 1 = h1.g1 ONLY (a third of the tensor work, score error ~2^-10 instead of
 // ~2^-20): the coarse first pass of the cascade in launch_assign_h16, always with MODE 2.  It needs neither h2 nor
 // g2, so h1 is double-buffered in TMEM for every ld <= 256 and only the g1 halves of the B units are loaded.
+//
+// ---- Barrier rings: why no parity wait can alias ------------------------------------------------------------------
+// An mbarrier parity wait for "completion number u" of a barrier is only right while the barrier has completed u or
+// u + 1 phases when the waiter looks: with u - 1 it passes too early, with u + 2 it blocks for good.  So for every
+// ring: (lo) completion u - 1 has happened before any waiter asks for u, and (hi) completion u + 1 cannot happen before
+// every waiter of u has passed.  T = running centroid-tile index (tile), owner(T) = issuer T & 1, NG in {2, 4} groups.
+// Two facts used throughout: (F1) an issuer handles its tiles in order; (F2) issuing tile T needs acc_empty of T - 2,
+// which the epilogue gives after draining T - 2, and the epilogue drains tiles in order after waiting for each, so
+// "T issued" implies "every tile <= T - 3 is complete, and T - 2 too (same owner)".
+//  * tile_done[8], slot T & 7, completion number T >> 3, one arrival (owner's multicast commit).
+//      - epilogue waiter of T: (lo) it passed T - 8 itself.  (hi) T + 8 uses the accumulator of T + 6, T + 4, ...: it
+//        cannot even be issued before the epilogue drained T + 6 > T.
+//      - B producer, before the LOAD for tile T, waits for q = T - NG, the previous user of that group (in forward and
+//        backward row tiles alike: a tile that needs a load has walk index i >= NG, and walk index i - NG holds the same
+//        group).  (lo) needs q - 8 complete: the producer's previous load was for T' >= T - RES - 1 >= T - 5 (at most RES
+//        <= 4 resident tiles, which need no load, lie between two loads) and it waited for T' - NG then; by F2 everything
+//        <= T' - NG - 3 is complete as well, and q - 8 = T - NG - 8 <= T' - NG - 3.  (hi) q + 8 >= T + 4 is not complete:
+//        T itself needs this load, the owner of T is stuck at T (F1), and the other issuer gets no further than T + 1
+//        (T + 3 needs the epilogue past T + 1, hence past T).
+//  * bfull[4] (leader), one completion per load into the group.  Waiter: owner(T) for the load of T, or -- resident
+//    tile -- for the load that filled the group.  (lo) the previous load into the group served tile T - NG, same owner
+//    because NG is even (b_groups() never returns 3): that issuer waited for it itself.  (hi) the next load into the
+//    group is issued only after tile_done of its previous user, i.e. of T or of a later tile.
+//    (The peer CTA's bytes may land before the leader arms the phase: its producer also waited for tile_done(T - NG),
+//    so the previous phase is complete and the transaction count is just negative for a moment.)
+//  * xfull / xempty[XS]: TWO full / empty rings of XS / 2 slots, one per transform warpgroup (even / odd chunks), each
+//    with its own running index: a slot is only ever consumed by one warpgroup, which therefore waits for every use of
+//    it in order.  (One ring shared by both warpgroups is NOT safe: the uses of a slot then alternate between them, a
+//    warpgroup asks for use u without ever having waited for use u - 1, and when the loads land out of order -- a mix of
+//    L2 hits and misses, e.g. on a freshly gathered copy -- it passes on the wrong phase and converts a chunk that has
+//    not landed yet.  Measured before the split: about one row tile in 10^5 with wrong low-order scores, and now and
+//    then a CTA that exited with a load still in flight -- "unspecified launch failure".)
+//  * a_full[buffer][chunk] (leader; 4 local + 4 remote transform warps), one completion per use of the A buffer.
+//    Waiters: BOTH issuers, in every row tile (their first own tile; with one tile per row tile the issuer without a tile
+//    waits too) -> (lo).  (hi) the next use is written only after a_free of this use, which needs both issuers' commits,
+//    which they make after their waits.
+//  * a_free[4] (both CTAs, 2 arrivals = both issuers' commits after their last tile of the row tile).  Waiters: the
+//    transform warps before rewriting the buffer.  (lo) they waited for the previous release before the previous write.
+//    (hi) the next release needs MMAs on the data they are about to write.
+//  * acc_empty[2] (leader; 8 local + 8 remote epilogue warps): owner(T) waits for the drain of T - 2; the epilogue
+//    drains T only after tile_done(T).  One phase per use on both sides.
+// Shapes that reach every branch: tools/stress.py (NT = 1, NT <= NG, NT > NG, odd / even row tiles per pair with a dummy
+// last tile, one / two A buffers, every BN), tests/test_gpu_production_path.py and tests/test_gpu_parity.py.
 template <int BN, int MODE, int NP = 3>
 __global__ void __launch_bounds__(kPairH16Threads, 1)
 assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_b,
@@ -83,6 +129,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
 
     const int XS = p.stages & 255, NG = p.stages >> 8;
+    const uint32_t XSW = XS >> 1;        // X ring slots per transform warpgroup
     const int NT = p.num_col_tiles;
     const int KC = p.num_k_chunks;       // 32-value chunks of X, <= 8
     const int C64 = (KC + 1) >> 1;       // 64-value units of B
@@ -189,10 +236,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         }
     } else if (warp == 3) {
         // ================================ X producer ==================================
-        uint32_t xi = 0;   // running chunk index: slot xi % XS
+        uint32_t xj[2] = {0, 0};   // running chunk index of each transform warpgroup's ring: slot wg * XSW + xj % XSW
         for (int rt = tile0; rt - (int)rank < num_row_tiles; rt += gridDim.x) {
-            for (int kc = 0; kc < KC; ++kc, ++xi) {
-                const uint32_t s = xi % XS, ph = (xi / XS) & 1;
+            for (int kc = 0; kc < KC; ++kc) {
+                const uint32_t wg = kc & 1, j = xj[wg]++;
+                const uint32_t s = wg * XSW + j % XSW, ph = (j / XSW) & 1;
                 mbar_wait(&xempty[s], ph ^ 1);
                 if (elect_one()) {
                     mbar_arrive_expect_tx(&xfull[s], kXStageBytes);
@@ -329,14 +377,14 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         const int r = threadIdx.x & 127;
         const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
         const float sx = p.cstats[3];
-        uint32_t rtn = 0;
+        uint32_t rtn = 0, xj = 0;   // xj: running index of this warpgroup's X ring (same sequence as the producer's)
         long long t_x = 0, t_free = 0, t_store = 0, t_mark = 0, n_chunks = 0;
         const bool prof = p.role_prof != nullptr && blockIdx.x < 2 && warp == 4;
         for (int base = base0; base < num_row_tiles; base += gridDim.x, ++rtn) {
-            for (int kc = wg; kc < KC; kc += 2) {
-                const uint32_t xi = rtn * KC + kc, xslot = xi % XS;
+            for (int kc = wg; kc < KC; kc += 2, ++xj) {
+                const uint32_t xslot = wg * XSW + xj % XSW;
                 if (prof) t_mark = clock64();
-                mbar_wait(&xfull[xslot], (xi / XS) & 1);
+                mbar_wait(&xfull[xslot], (xj / XSW) & 1);
                 const uint8_t *xrow = xs + xslot * kXStageBytes + r * 128;
                 float x[32];
 #pragma unroll

@@ -543,7 +543,7 @@ __global__ void scan_kernel(const int32_t *__restrict__ counts, int k, int32_t *
     if (threadIdx.x == 0) { offsets[k] = base_cnt; chunk_off[k] = base_chk; }
 }
 
-// order[] = row indices grouped by label (order inside a group follows atomic arrival).
+// order[] = row indices grouped by label (order inside a group follows atomic arrival): k > kHistSmemMax only.
 __global__ void scatter_kernel(const int32_t *__restrict__ labels, int64_t n, int k, int32_t *cursor,
                                int32_t *__restrict__ order) {
     extern __shared__ int32_t sh[];  // [k] counts -> bases (only when k <= kHistSmemMax)
@@ -569,6 +569,97 @@ __global__ void scatter_kernel(const int32_t *__restrict__ labels, int64_t n, in
     for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
         const int pos = atomicAdd(&sh[labels[r]], 1);
         order[pos] = (int32_t)r;
+    }
+}
+
+// ---- stable bucketing (k <= kHistSmemMax): the rows of a cluster appear in order[] in ROW ORDER, so every FP64 sum
+// downstream adds the same values in the same order on every run -- a fit is bit-reproducible.
+// (1) block_hist_kernel: hb[b][j] = rows of block b (kBucketRows consecutive rows) with label j;
+// (2) the column scan over blocks in three small kernels (segments of kScanSeg blocks): per-segment column sums,
+//     a scan over the segments, then the exclusive prefix inside every segment written back in place; counts[j]
+//     receives the column total;
+// (3) scan_kernel (above) turns counts into offsets / chunk offsets;
+// (4) scatter_stable_kernel: block b starts label j at offsets[j] + hb[b][j] and ranks its rows in row order.
+constexpr int kScanSeg = 128;   // blocks per segment of the column scan
+
+__global__ void block_hist_kernel(const int32_t *__restrict__ labels, int64_t n, int k, int32_t *__restrict__ hb) {
+    extern __shared__ int32_t sh[];
+    for (int j = threadIdx.x; j < k; j += blockDim.x) sh[j] = 0;
+    __syncthreads();
+    const int64_t r0 = (int64_t)blockIdx.x * kBucketRows;
+    const int64_t r1 = min(n, r0 + kBucketRows);
+    for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x) atomicAdd(&sh[labels[r]], 1);
+    __syncthreads();
+    for (int j = threadIdx.x; j < k; j += blockDim.x) hb[(size_t)blockIdx.x * k + j] = sh[j];
+}
+
+// grid (ceil(k / 256), nseg): segsum[s][j] = sum of hb[b][j] over the blocks of segment s
+__global__ void colsum_seg_kernel(const int32_t *__restrict__ hb, int nblocks, int k, int32_t *__restrict__ segsum) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= k) return;
+    const int b0 = blockIdx.y * kScanSeg, b1 = min(nblocks, b0 + kScanSeg);
+    int s = 0;
+    for (int b = b0; b < b1; ++b) s += hb[(size_t)b * k + j];
+    segsum[(size_t)blockIdx.y * k + j] = s;
+}
+// one thread per label: exclusive scan of segsum over the segments (in place); counts[j] = total
+__global__ void seg_scan_kernel(int32_t *__restrict__ segsum, int nseg, int k, int32_t *__restrict__ counts) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= k) return;
+    int run = 0;
+    for (int s = 0; s < nseg; ++s) {
+        const int v = segsum[(size_t)s * k + j];
+        segsum[(size_t)s * k + j] = run;
+        run += v;
+    }
+    counts[j] = run;
+}
+// grid (ceil(k / 256), nseg): hb[b][j] <- rows with label j in the blocks before b (exclusive, in place)
+__global__ void colscan_seg_kernel(int32_t *__restrict__ hb, int nblocks, int k, const int32_t *__restrict__ segsum) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= k) return;
+    const int b0 = blockIdx.y * kScanSeg, b1 = min(nblocks, b0 + kScanSeg);
+    int run = segsum[(size_t)blockIdx.y * k + j];
+    for (int b = b0; b < b1; ++b) {
+        const int v = hb[(size_t)b * k + j];
+        hb[(size_t)b * k + j] = run;
+        run += v;
+    }
+}
+
+// 256 threads, one block of kBucketRows rows.  The rows are taken 256 at a time; inside such a slice the rank of a
+// row among the rows of its label is: (lanes of the same warp with the same label and a lower lane id) + what the
+// lower warps of the slice added, which the warps publish one after the other through the shared cursor.
+__global__ void __launch_bounds__(256)
+scatter_stable_kernel(const int32_t *__restrict__ labels, int64_t n, int k, const int32_t *__restrict__ offsets,
+                      const int32_t *__restrict__ hb, int32_t *__restrict__ order) {
+    extern __shared__ int32_t cur[];   // [k] next position of label j for this block
+    for (int j = threadIdx.x; j < k; j += blockDim.x) cur[j] = offsets[j] + hb[(size_t)blockIdx.x * k + j];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t r0 = (int64_t)blockIdx.x * kBucketRows;
+    const int64_t r1 = min(n, r0 + kBucketRows);
+    for (int64_t s0 = r0; s0 < r1; s0 += 256) {
+        const int64_t r = s0 + threadIdx.x;
+        const bool valid = r < r1;
+        const int l = valid ? labels[r] : -1 - lane;   // (distinct negatives: lanes without a row match nobody)
+        const unsigned peers = __match_any_sync(0xffffffffu, l);
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        const int leader = __ffs(peers) - 1;
+        int pos = 0;
+        for (int w = 0; w < 8; ++w) {
+            if (warp == w) {
+                int base = 0;
+                if (valid && lane == leader) {   // one lane per distinct label of this warp: no conflicts
+                    base = cur[l];
+                    cur[l] = base + __popc(peers);
+                }
+                base = __shfl_sync(0xffffffffu, base, leader);
+                pos = base + rank;
+            }
+            __syncthreads();
+        }
+        if (valid) order[pos] = (int32_t)r;
     }
 }
 

@@ -54,6 +54,24 @@ static int fail(int code, const char *fmt, ...) {
         if (rc__ != 0) return rc__; \
     } while (0)
 
+// After every kernel launch.  KMB200_SYNC_CHECK=1 in the environment (diagnostics) also waits for the kernel and
+// names the launch site when it faulted -- asynchronous faults otherwise surface at some later, unrelated call.
+static int g_sync_check = -1;
+static int post_launch(int line) {
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) {
+        if (g_sync_check < 0) {
+            const char *v = getenv("KMB200_SYNC_CHECK");
+            g_sync_check = v && atoi(v) != 0;
+        }
+        if (g_sync_check) e = cudaDeviceSynchronize();
+    }
+    if (e != cudaSuccess)
+        return fail(e == cudaErrorMemoryAllocation ? KMB200_ERR_MEMORY : KMB200_ERR_DEVICE,
+                    "kernel launched at kmb200.cu:%d failed: %s", line, cudaGetErrorString(e));
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------ options
 static double g_eps_scale = 1.0;
 static int g_passes = 3;
@@ -150,6 +168,7 @@ struct Workspace {
     int32_t *labels = nullptr, *order = nullptr, *flag_count = nullptr;
     int2 *flag_list = nullptr;    // near-tie rows: (row, runner-up centre or -1)
     int32_t *counts = nullptr, *offsets = nullptr, *cursor = nullptr, *chunk_off = nullptr;
+    int32_t *hb = nullptr, *segsum = nullptr;   // stable bucketing: per-block label histograms [blocks x k], segment sums
     double *part = nullptr, *cpart = nullptr, *red = nullptr, *costj = nullptr;
     int32_t *flags = nullptr;      // [0] centres that moved > tol, [1] empty clusters
     double *fused_part = nullptr;  // per-CTA partials of the one-pass small-k kernel
@@ -232,7 +251,7 @@ struct kmb200_table {
 
 static void ws_free(Workspace &w) {
     void *ptrs[] = {w.cent, w.cent2, w.bhi, w.blo, w.bcorr, w.b16, w.cnorm64, w.rc_score, w.rc_idx, w.cnorm, w.cstats, w.labels, w.order, w.flag_list, w.flag_count,
-                    w.counts, w.offsets, w.cursor, w.chunk_off, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage,
+                    w.counts, w.offsets, w.cursor, w.chunk_off, w.hb, w.segsum, w.part, w.cpart, w.red, w.costj, w.flags, w.fused_part, w.fused_stage,
                     w.xc, w.xnc, w.cand_list, w.labels_c, w.xc1, w.xnc1, w.cand1_list, w.labels_c1};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -385,7 +404,7 @@ static int launch_rownorm(kmb200_table *t, int64_t row0, int64_t nrows) {
     int blocks = (int)std::min<int64_t>((warps * 32 + 255) / 256, (int64_t)t->num_sms * 16);
     if (blocks < 1) blocks = 1;
     rownorm_kernel<<<blocks, 256, 0, t->stream>>>(t->X, t->xnorm, t->xabs, row0, nrows, t->ld);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     return 0;
 }
 
@@ -429,7 +448,7 @@ static int append_rows(kmb200_table *t, int64_t row0, const T *rows, int64_t nro
             const int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)t->num_sms * 32);
             convert_rows_kernel<T><<<blocks, 256, 0, t->stream>>>(reinterpret_cast<const T *>(t->stage),
                                                                   t->X + (row0 + r) * t->ld, h, t->d, t->ld);
-            CU_TRY(cudaGetLastError());
+            KM_TRY(post_launch(__LINE__));
         }
     }
     KM_TRY(launch_rownorm(t, row0, nrows));
@@ -488,7 +507,7 @@ static int append_columns(kmb200_table *t, int64_t row0, const T *const *columns
         const int blocks = (int)std::min<int64_t>(tiles, (int64_t)t->num_sms * 16);
         transpose_columns_kernel<T><<<blocks, dim3(32, 8), 0, t->stream>>>(stage, chunk, t->X + (row0 + r) * t->ld, h, t->d,
                                                                            t->ld);
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
     }
     KM_TRY(launch_rownorm(t, row0, nrows));
     CU_TRY(cudaStreamSynchronize(t->stream));
@@ -538,7 +557,7 @@ extern "C" int kmb200_table_append_csr_f64(kmb200_table *t, int64_t row0, int64_
         const int blocks = (int)std::min<int64_t>((h * 32 + 255) / 256, (int64_t)t->num_sms * 16);
         csr_scatter_kernel<<<blocks, 256, 0, t->stream>>>(d_indptr, base, d_indices, d_values, t->X + (row0 + r) * t->ld, h,
                                                           t->d, t->ld, d_bad);
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
         CU_TRY(cudaStreamSynchronize(t->stream));   // the staging buffer is reused by the next chunk
         r += h;
     }
@@ -702,6 +721,11 @@ static int ws_prepare_impl(kmb200_table *t, int k) {
     KM_TRY(dmalloc(&w.offsets, (size_t)k + 1));
     KM_TRY(dmalloc(&w.cursor, (size_t)k + 1));
     KM_TRY(dmalloc(&w.chunk_off, (size_t)k + 1));
+    if (k <= kHistSmemMax) {
+        const size_t blocks = (n + kBucketRows - 1) / kBucketRows, nseg = (blocks + kScanSeg - 1) / kScanSeg;
+        KM_TRY(dmalloc(&w.hb, blocks * (size_t)k));
+        KM_TRY(dmalloc(&w.segsum, nseg * (size_t)k));
+    }
     KM_TRY(dmalloc(&w.part, (size_t)w.max_chunks * ld));
     KM_TRY(dmalloc(&w.cpart, (size_t)w.max_chunks));
     KM_TRY(dmalloc(&w.red, (size_t)k * ld + k + 1));
@@ -767,7 +791,7 @@ static int launch_assign_bn(kmb200_table *t) {
     p.role_prof = g_role_prof;
     const int grid = std::min(p.num_row_tiles, t->num_sms);
     assign_tc_kernel<BN><<<grid, kAssignThreads, smem, t->stream>>>(w.tm_x, w.tm_bhi, w.tm_blo, p);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
     return 0;
 }
@@ -818,6 +842,7 @@ static int launch_assign2_bn(kmb200_table *t) {
     cfg.numAttrs = 1;
     CU_TRY(cudaLaunchKernelEx(&cfg, assign_tc2_kernel<BN, CL>, w.tm_x, CL == 2 ? w.tm_bhi_half : w.tm_bhi,
                               CL == 2 ? w.tm_blo_half : w.tm_blo, p));
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
     return 0;
 }
@@ -877,6 +902,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     cfg.numAttrs = 1;
     CU_TRY(cudaLaunchKernelEx(&cfg, kernel, w.tm_x, w.tm_bhi_half,
                               BF16C ? w.tm_bcorr_half : w.tm_blo_half, p));
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
     return 0;
 }
@@ -1022,6 +1048,7 @@ static int launch_assign_h16_bn(kmb200_table *t, const H16Src &src) {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     CU_TRY(cudaLaunchKernelEx(&cfg, kernel, *src.tm, w.tm_b16_half, p));
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
     return 0;
 }
@@ -1044,7 +1071,7 @@ static int read_count(kmb200_table *t, int32_t *host_dst, const int32_t *dev_src
 static int launch_gather(kmb200_table *t, const float *X, const float *xnorm, const int32_t *list, const int32_t *count,
                          int64_t cap, float *xc, float *xnc) {
     gather_rows_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(X, xnorm, list, count, (int32_t)cap, t->ld, xc, xnc);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
     return 0;
 }
@@ -1188,7 +1215,7 @@ static int launch_fused_inst(kmb200_table *t, float eps) {
     auto *counter = reinterpret_cast<unsigned long long *>(w.flag_count);
     fused_smallk_kernel<LD, KP><<<w.fused_ctas, kFusedWarps * 32, fused_smem_bytes(w.k, LD), t->stream>>>(
         t->X, w.cent, w.cstats, t->rows, w.k, eps, w.labels, w.fused_part, counter);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     return 0;
 }
 
@@ -1202,7 +1229,7 @@ static int launch_fused(kmb200_table *t) {
     const float eps = (float)(g_eps_scale * ldexp((double)ld + 4.0, -24));   // FP32 FMA chain of ld terms
     float *stage_c = w.fused_stage, *stage_n = w.fused_stage + 1024;
     fused_prepare_kernel<<<1, 256, 0, t->stream>>>(w.cent, k, kp, ld, stage_c, stage_n);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     CU_TRY(cudaMemcpyToSymbolAsync(kc_cent, stage_c, (size_t)kp * ld * sizeof(float), 0, cudaMemcpyDeviceToDevice, t->stream));
     CU_TRY(cudaMemcpyToSymbolAsync(kc_norm, stage_n, 32 * sizeof(float), 0, cudaMemcpyDeviceToDevice, t->stream));
     int rc = 0;
@@ -1211,7 +1238,7 @@ static int launch_fused(kmb200_table *t) {
     KM_TRY(rc);
     const int psize1 = k * ld + k + 1;
     fused_reduce_kernel<<<(psize1 + 255) / 256, 256, 0, t->stream>>>(w.fused_part, w.fused_ctas, psize1, w.red);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches += 3;
     return 0;
 }
@@ -1223,16 +1250,16 @@ static int launch_split(kmb200_table *t) {
     if (h16_applies(t)) {
         const int64_t count = (int64_t)w.k * t->ld;
         cent_absmax_kernel<<<(int)std::min<int64_t>((count + 255) / 256, 1024), 256, 0, t->stream>>>(w.cent, count, w.cstats);
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
         split16_kernel<<<w.kpad, 128, 0, t->stream>>>(w.cent, w.b16, w.cnorm, w.cnorm64, w.cstats, t->xabs, w.k, t->ld,
                                                      (int)ld64(t->ld));
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
         g_prof.kernel_launches += 2;
         return 0;
     }
     split_centers_kernel<<<w.kpad, 128, 0, t->stream>>>(w.cent, w.bhi, w.blo, w.bcorr, w.cnorm, w.cnorm64, w.cstats,
                                                         w.k, t->ld);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
     return 0;
 }
@@ -1243,7 +1270,7 @@ static int launch_assign(kmb200_table *t) {
     if (g_force_simt) {
         recheck_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, w.cent, nullptr, nullptr, 0, t->rows, w.k, t->ld,
                                                              w.labels);
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
         g_prof.kernel_launches++;
         g_prof.assign_variant = 7;
         return 0;
@@ -1278,25 +1305,25 @@ static int launch_recheck(kmb200_table *t) {
     int32_t *labels = w.recheck_level == 2 ? w.labels_c : w.recheck_level == 1 ? w.labels_c1 : w.labels;
     recheck_kernel<<<t->num_sms * 4, 256, 0, t->stream>>>(X, w.cent, w.flag_list, w.flag_count, (int32_t)t->rows,
                                                          t->rows, w.k, t->ld, labels);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     const int rgrid = t->num_sms * 8;
     recheck_full_kernel<<<rgrid, 256, 0, t->stream>>>(X, w.cent, w.cnorm64, w.flag_list, w.flag_count + 1,
                                                      (int32_t)t->rows, w.k, t->ld, labels, w.rc_score, w.rc_idx);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     recheck_merge_kernel<<<8, 256, 0, t->stream>>>(w.flag_list, w.flag_count + 1, (int32_t)t->rows, rgrid, w.rc_score,
                                                   w.rc_idx, labels);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches += 3;
     if (w.scatter2 && w.recheck_level == 2) {   // decided labels of the near-tie copy -> the level they were gathered from
         scatter_labels_kernel<<<t->num_sms * 2, 256, 0, t->stream>>>(w.cand_list, w.flag_count + 2, (int32_t)w.cand_cap,
                                                                     w.labels_c, w.scatter1 ? w.labels_c1 : w.labels);
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
         g_prof.kernel_launches++;
     }
     if (w.scatter1) {   // labels of the coarse pass's undecided rows -> the table's labels
         scatter_labels_kernel<<<t->num_sms * 2, 256, 0, t->stream>>>(w.cand1_list, w.flag_count + 3, (int32_t)w.cand1_cap,
                                                                     w.labels_c1, w.labels);
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
         g_prof.kernel_launches++;
     }
     return 0;
@@ -1307,13 +1334,32 @@ static int launch_bucket(kmb200_table *t) {
     const int k = w.k;
     const int blocks = (int)((t->rows + kBucketRows - 1) / kBucketRows);
     const size_t sh = k <= kHistSmemMax ? (size_t)k * sizeof(int32_t) : 0;
+    if (k <= kHistSmemMax) {
+        // stable: the rows of a cluster keep their row order, so the FP64 sums are reproducible run to run
+        const int nseg = (blocks + kScanSeg - 1) / kScanSeg;
+        const dim3 sgrid((unsigned)((k + 255) / 256), (unsigned)nseg);
+        block_hist_kernel<<<blocks, 256, sh, t->stream>>>(w.labels, t->rows, k, w.hb);
+        KM_TRY(post_launch(__LINE__));
+        colsum_seg_kernel<<<sgrid, 256, 0, t->stream>>>(w.hb, blocks, k, w.segsum);
+        KM_TRY(post_launch(__LINE__));
+        seg_scan_kernel<<<(k + 255) / 256, 256, 0, t->stream>>>(w.segsum, nseg, k, w.counts);
+        KM_TRY(post_launch(__LINE__));
+        colscan_seg_kernel<<<sgrid, 256, 0, t->stream>>>(w.hb, blocks, k, w.segsum);
+        KM_TRY(post_launch(__LINE__));
+        scan_kernel<<<1, 1024, 0, t->stream>>>(w.counts, k, w.offsets, w.cursor, w.chunk_off);
+        KM_TRY(post_launch(__LINE__));
+        scatter_stable_kernel<<<blocks, 256, sh, t->stream>>>(w.labels, t->rows, k, w.offsets, w.hb, w.order);
+        KM_TRY(post_launch(__LINE__));
+        g_prof.kernel_launches += 6;
+        return 0;
+    }
     CU_TRY(cudaMemsetAsync(w.counts, 0, ((size_t)k + 1) * sizeof(int32_t), t->stream));
     label_hist_kernel<<<blocks, 256, sh, t->stream>>>(w.labels, t->rows, k, w.counts);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     scan_kernel<<<1, 1024, 0, t->stream>>>(w.counts, k, w.offsets, w.cursor, w.chunk_off);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     scatter_kernel<<<blocks, 256, sh, t->stream>>>(w.labels, t->rows, k, w.cursor, w.order);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches += 3;
     return 0;
 }
@@ -1323,11 +1369,11 @@ static int launch_accumulate(kmb200_table *t) {
     const int ld = t->ld;
     segment_sums_kernel<<<(unsigned)w.max_chunks, 256, 0, t->stream>>>(t->X, w.cent, w.order, w.offsets, w.chunk_off,
                                                                         w.k, ld, w.part, w.cpart);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     segment_reduce_kernel<<<w.k, 128, 0, t->stream>>>(w.part, w.cpart, w.offsets, w.chunk_off, w.k, ld, w.red, w.costj);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     cost_sum_kernel<<<1, 1024, 0, t->stream>>>(w.costj, w.k, ld, w.red);
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches += 3;
     return 0;
 }
@@ -1569,7 +1615,7 @@ static int fit_impl(kmb200_table *t, kmb200_comm *comm, const double *init_cente
         if (timed) CU_TRY(cudaEventRecord(ev[5], st));
         CU_TRY(cudaMemsetAsync(w.flags, 0, 4 * sizeof(int32_t), st));
         finalize_kernel<<<k, 128, 0, st>>>(w.red, w.cent, w.cent2, k, t->ld, d, tol, w.flags);
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
         g_prof.kernel_launches++;
         // one host round trip per iteration: the reference's iteration count must be reproduced
         // exactly, so the converged flag (and the rare empty-cluster count) is read every time
@@ -1710,6 +1756,26 @@ extern "C" int kmb200_debug_scores(kmb200_table *t, const double *centers, int32
     return 0;
 }
 
+// Diagnostics: copies one of the workspace arrays of the last fit / assign to the host (tools/repro_check.py).
+extern "C" int kmb200_debug_dump(kmb200_table *t, const char *name, size_t offset, void *out, size_t bytes) {
+    if (!t || !name || !out) return fail(KMB200_ERR_ARG, "debug_dump: null argument");
+    Workspace &w = t->ws;
+    const void *src = nullptr;
+    if (!strcmp(name, "cand_list")) src = w.cand_list;
+    else if (!strcmp(name, "labels_c")) src = w.labels_c;
+    else if (!strcmp(name, "cand1_list")) src = w.cand1_list;
+    else if (!strcmp(name, "labels_c1")) src = w.labels_c1;
+    else if (!strcmp(name, "flag_list")) src = w.flag_list;
+    else if (!strcmp(name, "flag_count")) src = w.flag_count;
+    else if (!strcmp(name, "xc")) src = w.xc;
+    else if (!strcmp(name, "xc1")) src = w.xc1;
+    else if (!strcmp(name, "labels")) src = w.labels;
+    if (!src) return fail(KMB200_ERR_ARG, "debug_dump: no array '%s'", name);
+    CU_TRY(cudaSetDevice(t->device));
+    CU_TRY(cudaMemcpy(out, static_cast<const uint8_t *>(src) + offset, bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------ no-allocation entry
 // Cluster sizes from a label vector without touching the device allocator.  The label histogram
 // needs k int32 counters of scratch; the regular path (launch_bucket) keeps them in the workspace
@@ -1760,10 +1826,10 @@ extern "C" int kmb200_cluster_sizes_noalloc(const int32_t *labels_dev, int64_t n
         if (blocks > 2147483647LL) return fail(KMB200_ERR_LIMIT, "cluster_sizes_noalloc: too many rows");
         const size_t sh = k <= kHistSmemMax ? (size_t)k * sizeof(int32_t) : 0;
         label_hist_kernel<<<(unsigned)blocks, 256, sh, st>>>(labels_dev, n, k, counters);
-        CU_TRY(cudaGetLastError());
+        KM_TRY(post_launch(__LINE__));
     }
     counts_to_i64_kernel<<<(k + 255) / 256, 256, 0, st>>>(counters, k, reinterpret_cast<unsigned long long *>(sizes_dev));
-    CU_TRY(cudaGetLastError());
+    KM_TRY(post_launch(__LINE__));
     return 0;
 }
 

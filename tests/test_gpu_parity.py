@@ -297,6 +297,17 @@ def test_every_kernel_variant_keeps_parity(m, options):
             m._lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
 
 
+@pytest.mark.parametrize("n,d,k", [(50000, 64, 100), (300_000, 256, 1000)])
+def test_repeated_fits_are_bit_identical(m, n, d, k):
+    """Rows are bucketed by label in row order and every FP64 reduction has a fixed tree, so the same fit twice
+    gives the same bytes (centres and cost), whatever order the CTAs ran in."""
+    X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + 1)
+    init = ko.row_init_centers(X, k)
+    a = gpu_fit(m, X, init, tol=-1.0, max_iter=4)
+    b = gpu_fit(m, X, init, tol=-1.0, max_iter=4)
+    assert a[1] == b[1] and np.array_equal(a[0], b[0])
+
+
 def test_empty_cluster_substitution(m):
     X = np.array([[0.0, 0], [1, 0], [0, 1], [10, 10], [11, 10]])
     init = np.array([[0.0, 0], [10, 10], [100, 100]])

@@ -86,6 +86,7 @@ def main():
         init = np.ascontiguousarray(t.cpu().numpy())
     t0 = time.time()
     first = None
+    bit_identical = True
     variants = set()
     for f in range(args.fits):
         cen, cost = fit(table, init, args.iters, comm)
@@ -93,6 +94,7 @@ def main():
         if first is None:
             first = (cen, cost)
         else:
+            bit_identical &= cost == first[1] and np.array_equal(cen, first[0])
             if not abs(cost - first[1]) <= 1e-12 * abs(first[1]) or not np.allclose(cen, first[0], rtol=1e-12, atol=0):
                 print(f"[stress] rank {rank}: fit {f} differs from fit 0: cost {cost!r} vs {first[1]!r}", flush=True)
                 sys.exit(1)
@@ -100,7 +102,7 @@ def main():
     if rank == 0:
         print(json.dumps({"part": "bench shard", "ranks": world, "rows_per_rank": n, "d": d, "k": k, "fits": args.fits,
                           "iterations_per_fit": args.iters, "assign_variants_seen": sorted(variants),
-                          "identical_results": True, "final_cost": first[1], "seconds": round(time.time() - t0, 1)}),
+                          "identical_results": True, "bit_identical": bool(bit_identical), "final_cost": first[1], "seconds": round(time.time() - t0, 1)}),
               flush=True)
     if dist is not None:
         dist.barrier()
