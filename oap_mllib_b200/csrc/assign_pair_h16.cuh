@@ -1,4 +1,5 @@
-// CTA-pair assign kernel, "H16" variant (ld <= 256, BN >= 32): two-term FP16 splits of both operands.
+// CTA-pair assign kernel, "H16" variant (ld <= 256, BN >= 32; the one-product pass alone up to ld = 512): two-term FP16
+// splits of both operands.
 //
 //   x * sx = h1 + h2 (+ <= 2^-22 |x sx|),   -2c * sw = g1 + g2 (+ <= 2^-22 |2c sw|)      (sx, sw powers of two)
 //   -2 x.c  ~=  (h2.g1 + h1.g2 + h1.g1) / (sx sw)        three kind::f16 products, FP32 accumulation in TMEM
@@ -38,7 +39,9 @@ struct PairH16Cfg {
     static constexpr int kXchgBytes = 2 * 128 * 5 * 4;
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16 + kXchgBytes;
     static constexpr int kBudget = 227 * 1024 - 1024 - kTailBytes;
-    static int group_bytes(int kc) { return ((kc + 1) / 2) * kBUnitBytes; }   // B operand of one centroid tile
+    // ld > 256 (more than 8 chunks; one-product pass only, see the kernel): the units hold g1 alone
+    static int unit_bytes(int kc) { return kc > 8 ? kBHalfBytes : kBUnitBytes; }
+    static int group_bytes(int kc) { return ((kc + 1) / 2) * unit_bytes(kc); }   // B operand of one centroid tile
     // X ring slots (32-value chunks): as many as fit next to two B groups, at most one row tile, at most 8; an EVEN
     // number >= 2, because each transform warpgroup owns half of them (see "xfull / xempty" in the barrier notes)
     static int x_slots(int kc) {
@@ -69,6 +72,10 @@ struct PairH16Cfg {
 // NP: 3 = the three products above; 1 = h1.g1 ONLY (a third of the tensor work, score error ~2^-10 instead of
 // ~2^-20): the coarse first pass of the cascade in launch_assign_h16, always with MODE 2.  It needs neither h2 nor
 // g2, so h1 is double-buffered in TMEM for every ld <= 256 and only the g1 halves of the B units are loaded.
+// NP = 1 also runs with 256 < ld <= 512 ("wide": up to 16 chunks): h1 of a row tile then fills all 256 A columns (one
+// buffer, released in two halves like the three-product kernel's), and the B units are packed g1 only.  The three-
+// product kernel cannot (h1 and h2 of 512 values would need all 512 TMEM columns): the rows this pass leaves undecided
+// go through the streaming 3xTF32 kernel (launch_assign_h16_wide).
 //
 // ---- Barrier rings: why no parity wait can alias ------------------------------------------------------------------
 // An mbarrier parity wait for "completion number u" of a barrier is only right while the barrier has completed u or
@@ -131,16 +138,18 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     const int XS = p.stages & 255, NG = p.stages >> 8;
     const uint32_t XSW = XS >> 1;        // X ring slots per transform warpgroup
     const int NT = p.num_col_tiles;
-    const int KC = p.num_k_chunks;       // 32-value chunks of X, <= 8
+    const int KC = p.num_k_chunks;       // 32-value chunks of X, <= 8 (one-product pass: <= 16)
+    const bool WIDE = KC > 8;
+    const int unit_bytes = WIDE ? Cfg::kBHalfBytes : Cfg::kBUnitBytes;
     const int C64 = (KC + 1) >> 1;       // 64-value units of B
     const int C64a = C64 >> 1;           // units [0, C64a) of A are released first in a row tile's last centroid tile
     const int ld64 = C64 * 64;
-    const int group_bytes = C64 * Cfg::kBUnitBytes;
+    const int group_bytes = C64 * unit_bytes;
     const int RES = NG < NT ? NG : NT;   // centroid tiles still resident in the B groups at a row-tile switch
     // ld <= 128: h1 / h2 of a row tile take at most 64 columns each, so there are TWO A buffers (row tile parity)
     // and the transform of the next row tile overlaps this one's MMAs completely -- with few centroid tiles per
     // row tile (k <= 128: one) the a_free -> transform -> a_full handshake would otherwise be the critical path.
-    const bool ADB = ONE || KC <= 4;
+    const bool ADB = (ONE && !WIDE) || KC <= 4;
     const uint32_t abuf_cols = ONE ? 128 : 64;   // columns between the two A buffers
     uint8_t *xs = smem;                                  // [XS][128 rows x 128 B], swizzled
     uint8_t *bs = smem + XS * kXStageBytes;              // [NG][C64][g1 chunk | g2 chunk] (this CTA's rows)
@@ -223,11 +232,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     if (p.knockout & 1) {   // timing experiments only: no B traffic
                         if (leader) mbar_arrive(&bfull[g]);
                     } else {
-                        if (leader) mbar_arrive_expect_tx(&bfull[g], ONE ? group_bytes : 2 * group_bytes);
+                        if (leader) mbar_arrive_expect_tx(&bfull[g], ONE ? 2 * C64 * Cfg::kBHalfBytes : 2 * group_bytes);
                         for (int c = 0; c < C64; ++c) {
-                            tma_load_2d_pair(&tm_b, &bfull[g], st + c * Cfg::kBUnitBytes, c * 64, brow);
+                            tma_load_2d_pair(&tm_b, &bfull[g], st + c * unit_bytes, c * 64, brow);
                             if constexpr (!ONE)
-                                tma_load_2d_pair(&tm_b, &bfull[g], st + c * Cfg::kBUnitBytes + Cfg::kBHalfBytes, ld64 + c * 64, brow);
+                                tma_load_2d_pair(&tm_b, &bfull[g], st + c * unit_bytes + Cfg::kBHalfBytes, ld64 + c * 64, brow);
                         }
                     }
                 }
@@ -304,7 +313,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     // one unit (64 K-values) of this tile: its MMAs and whatever is committed after them
                     auto issue_unit = [&](int c) {
                         const int nk = (2 * c + 1 < KC) ? 4 : 2;   // 16-value steps in this unit
-                        const uint32_t bsm = bsm0 + c * Cfg::kBUnitBytes;
+                        const uint32_t bsm = bsm0 + c * unit_bytes;
                         const uint64_t d1 = make_kmajor_sw128_desc(bsm);
                         const uint64_t d2 = make_kmajor_sw128_desc(bsm + Cfg::kBHalfBytes);
                         const uint32_t a1 = tmem_base + abuf * abuf_cols + c * 32, a2 = a1 + Cfg::kA2Col0;

@@ -759,8 +759,20 @@ static float score_eps(int ld, bool bf16_corr = false) {
     return (float)(g_eps_scale * 1.25 * ldexp(1.0, -10));
 }
 
+// What one launch of an assign kernel reads and writes: the table itself or one of the gathered copies.
+struct H16Src {
+    const CUtensorMap *tm;    // rows to score
+    const float *xnorm;
+    int32_t *labels;
+    int64_t rows;
+    int32_t *cand_list;       // MODE 2: where the undecided rows are listed
+    int32_t *cand_count;
+    int64_t cand_cap;
+    bool prof;                // role counters (diagnostics) for this launch
+};
+
 template <int BN>
-static int launch_assign_bn(kmb200_table *t) {
+static int launch_assign_bn(kmb200_table *t, const H16Src *src = nullptr) {
     Workspace &w = t->ws;
     using Cfg = AssignCfg<BN>;
     static bool attr_set[64] = {false};
@@ -770,16 +782,17 @@ static int launch_assign_bn(kmb200_table *t) {
         CU_TRY(cudaFuncSetAttribute(assign_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_set[t->device & 63] = true;
     }
+    const int64_t rows = src ? src->rows : t->rows;
     AssignParams p;
     p.cnorm = w.cnorm;
-    p.xnorm = t->xnorm;
+    p.xnorm = src ? src->xnorm : t->xnorm;
     p.cstats = w.cstats;
-    p.labels = w.labels;
+    p.labels = src ? src->labels : w.labels;
     p.flag_count = w.flag_count;
     p.flag_list = w.flag_list;
     p.flag_cap = (int32_t)t->rows;
-    p.n = (int32_t)t->rows;
-    p.num_row_tiles = (int32_t)((t->rows + kTileM - 1) / kTileM);
+    p.n = (int32_t)rows;
+    p.num_row_tiles = (int32_t)((rows + kTileM - 1) / kTileM);
     p.num_col_tiles = w.kpad / BN;
     p.num_k_chunks = t->ld / kChunkK;
     p.stages = stages;
@@ -790,7 +803,7 @@ static int launch_assign_bn(kmb200_table *t) {
     p.knockout = g_knockout;
     p.role_prof = g_role_prof;
     const int grid = std::min(p.num_row_tiles, t->num_sms);
-    assign_tc_kernel<BN><<<grid, kAssignThreads, smem, t->stream>>>(w.tm_x, w.tm_bhi, w.tm_blo, p);
+    assign_tc_kernel<BN><<<grid, kAssignThreads, smem, t->stream>>>(src ? *src->tm : w.tm_x, w.tm_bhi, w.tm_blo, p);
     KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
     return 0;
@@ -925,6 +938,18 @@ static bool h16_applies(const kmb200_table *t) {
 
 constexpr int64_t kTwoLevelMinRows = 1 << 18;
 
+// 256 < ld <= 512 (BASELINE config 4, d = 512): the three-product kernel does not fit (h1 and h2 of a row tile would
+// take all 512 TMEM columns), the one-product pass does.  Large tables get the cascade with the streaming 3xTF32
+// kernel as its second stage (launch_assign_h16_wide); everything else stays on the streaming kernel alone.
+static bool h16_wide_applies(const kmb200_table *t) {
+    const Workspace &w = t->ws;
+    if (!g_h16 || !g_cascade || !g_two_level || g_force_simt || g_kernel != 2 || g_passes != 3 || g_cluster != 2) return false;
+    if (t->ld <= 256 || t->ld > 512 || w.bn < 32 || w.dbg_scores || w.cascade_off) return false;
+    if (g_two_level == 1 && t->rows < kTwoLevelMinRows) return false;
+    if ((t->rows + kTileM - 1) / kTileM < 2) return false;
+    return w.bn == 32 ? h16_fits<32>(t) : w.bn == 64 ? h16_fits<64>(t) : h16_fits<128>(t);
+}
+
 // (Re)allocates the candidate buffers when the two-level scheme applies to this table; false = use full bookkeeping.
 static bool two_level_prepare(kmb200_table *t) {
     Workspace &w = t->ws;
@@ -981,18 +1006,6 @@ static bool cascade_prepare(kmb200_table *t) {
     w.cand1_cap = cap;
     return true;
 }
-
-// What one launch of the FP16-split kernel reads and writes: the table itself or one of the gathered copies.
-struct H16Src {
-    const CUtensorMap *tm;    // rows to score
-    const float *xnorm;
-    int32_t *labels;
-    int64_t rows;
-    int32_t *cand_list;       // MODE 2: where the undecided rows are listed
-    int32_t *cand_count;
-    int64_t cand_cap;
-    bool prof;                // role counters (diagnostics) for this launch
-};
 
 // Score error of the one-product pass: both operands rounded to 11 bits (2^-11 each, relative to |x||w| element
 // by element, so 2^-10 of 2|x||c| by Cauchy-Schwarz), ld/16 accumulator updates, FP32 norm and final FMA.
@@ -1160,6 +1173,49 @@ static int launch_assign_h16(kmb200_table *t) {
     return launch_h16_fine(t, table, t->X, 0, two_level && !w.two_level_off, true);
 }
 
+static int launch_assign_stream(kmb200_table *t, const H16Src *src) {
+    switch (t->ws.bn) {
+        case 16: return launch_assign_bn<16>(t, src);
+        case 32: return launch_assign_bn<32>(t, src);
+        case 64: return launch_assign_bn<64>(t, src);
+        default: return launch_assign_bn<128>(t, src);
+    }
+}
+
+// 256 < ld <= 512: coarse one-product pass of the FP16-split kernel over all rows, then the streaming 3xTF32 kernel
+// (full bookkeeping) over the gathered copy of the rows it left undecided, then the FP64 re-check as everywhere.
+// *done = false: the cascade does not apply (any more) and nothing was launched.
+static int launch_assign_h16_wide(kmb200_table *t, bool *done) {
+    Workspace &w = t->ws;
+    *done = false;
+    w.two_level_active = false;
+    w.recheck_level = 0;
+    w.scatter1 = w.scatter2 = false;
+    if (!cascade_prepare(t)) return 0;
+    H16Src coarse = {&w.tm_x, t->xnorm, w.labels, t->rows, w.cand1_list, w.flag_count + 3, w.cand1_cap, true};
+    cudaEvent_t *ev = w.main_ev;
+    if (ev) CU_TRY(cudaEventRecord(ev[0], t->stream));
+    KM_TRY((launch_assign_h16_mode<2, 1>(t, coarse)));
+    if (ev) CU_TRY(cudaEventRecord(ev[1], t->stream));
+    KM_TRY(read_count(t, &w.host->cand1_count, w.flag_count + 3));
+    if ((int64_t)w.host->cand1_count > w.cand1_cap) {
+        w.cascade_off = true;   // too many undecided rows: the streaming kernel alone from here on
+        if (g_prof.cascade_dropped_at < 0) g_prof.cascade_dropped_at = g_prof.iterations;
+        CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
+        return 0;
+    }
+    *done = true;
+    g_prof.assign_variant = 8;
+    g_prof.coarse_undecided_rows += w.host->cand1_count;
+    w.main_ev = nullptr;   // bracketed above
+    w.scatter1 = true;
+    w.recheck_level = 1;
+    if (w.host->cand1_count == 0) return 0;
+    KM_TRY(launch_gather(t, t->X, t->xnorm, w.cand1_list, w.flag_count + 3, w.cand1_cap, w.xc1, w.xnc1));
+    H16Src mid = {&w.tm_xc1, w.xnc1, w.labels_c1, (int64_t)w.host->cand1_count, nullptr, nullptr, 0, false};
+    return launch_assign_stream(t, &mid);
+}
+
 static int launch_assign_pair(kmb200_table *t, bool *applicable) {
     switch (t->ws.bn) {
 #define KMB_PAIR(BN_) \
@@ -1247,7 +1303,8 @@ static int launch_split(kmb200_table *t) {
     Workspace &w = t->ws;
     CU_TRY(cudaMemsetAsync(w.cstats, 0, 8 * sizeof(float), t->stream));
     env_overrides();
-    if (h16_applies(t)) {
+    const bool narrow = h16_applies(t);
+    if (narrow || h16_wide_applies(t)) {
         const int64_t count = (int64_t)w.k * t->ld;
         cent_absmax_kernel<<<(int)std::min<int64_t>((count + 255) / 256, 1024), 256, 0, t->stream>>>(w.cent, count, w.cstats);
         KM_TRY(post_launch(__LINE__));
@@ -1255,7 +1312,7 @@ static int launch_split(kmb200_table *t) {
                                                      (int)ld64(t->ld));
         KM_TRY(post_launch(__LINE__));
         g_prof.kernel_launches += 2;
-        return 0;
+        if (narrow) return 0;   // (the wide cascade also needs the TF32 operands of its second stage)
     }
     split_centers_kernel<<<w.kpad, 128, 0, t->stream>>>(w.cent, w.bhi, w.blo, w.bcorr, w.cnorm, w.cnorm64, w.cstats,
                                                         w.k, t->ld);
@@ -1288,13 +1345,13 @@ static int launch_assign(kmb200_table *t) {
         g_prof.assign_variant = 5;
         return launch_assign2<1>(t);
     }
-    g_prof.assign_variant = 6;
-    switch (w.bn) {
-        case 16: return launch_assign_bn<16>(t);
-        case 32: return launch_assign_bn<32>(t);
-        case 64: return launch_assign_bn<64>(t);
-        default: return launch_assign_bn<128>(t);
+    if (h16_wide_applies(t)) {
+        bool done = false;
+        KM_TRY(launch_assign_h16_wide(t, &done));
+        if (done) return 0;
     }
+    g_prof.assign_variant = 6;
+    return launch_assign_stream(t, nullptr);
 }
 
 static int launch_recheck(kmb200_table *t) {
@@ -1573,10 +1630,10 @@ static int fit_impl(kmb200_table *t, kmb200_comm *comm, const double *init_cente
     Workspace &w = t->ws;
     cudaStream_t st = t->stream;
     KM_TRY(upload_centers(t, init_centers, k, d));
-    KM_TRY(launch_split(t));
-    KM_TRY(t->events.ensure(max_iter));
     w.two_level_off = false;
     w.cascade_off = false;
+    KM_TRY(launch_split(t));
+    KM_TRY(t->events.ensure(max_iter));
 
     double cost = 0.0;
     int it = 0;

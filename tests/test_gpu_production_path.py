@@ -126,3 +126,26 @@ def test_wide_rows_beyond_one_accumulate_pass(m, d):
     """d > 1024: the accumulate kernel walks a row in several passes of 256 float4 lanes, the last one partial."""
     X, _, _ = ko.gaussian_blobs(3000, d, 12, seed=d)
     check_fit_parity(m, X, ko.row_init_centers(X, 12), tol=1e-4, max_iter=4)
+
+
+def test_c4_geometry_wide_cascade(m):
+    """d = 512 (C4's shape): the one-product pass of the FP16-split kernel over all rows, the streaming 3xTF32 kernel over
+    the rows it leaves undecided."""
+    X, _, _ = ko.gaussian_blobs(270_000, 512, 2000, seed=36)
+    # (centres after one oracle step: from raw rows the first pass leaves more than cand1_frac of the rows undecided
+    # and the fit drops the cascade at once -- that hand-off is test_hard_data_hand_offs' business)
+    init, _, _, _ = ko.lloyd_step([X.astype(np.float64)], ko.row_init_centers(X, 2000))
+    prof = fit_labels_profile(m, X, init, max_iter=3)
+    assert prof["assign_variant"] == 8 and prof["coarse_undecided_rows"] > 0 and prof["cascade_dropped_at"] == -1
+
+
+@pytest.mark.parametrize("n,d,k", [(9000, 384, 200), (6000, 512, 700), (5000, 288, 40), (4000, 480, 1100)])
+def test_wide_cascade_forced_on_small_tables(m, n, d, k):
+    """The same scheme forced onto small tables (10 to 16 chunks of 32 columns, every BN, ragged row tiles)."""
+    X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + d)
+    try:
+        m._lib.check(m.lib().kmb200_set_option(b"two_level", 2.0))
+        check_fit_parity(m, X, ko.row_init_centers(X, k), tol=1e-4, max_iter=5)
+        assert m.kmeans.profile()["assign_variant"] == 8
+    finally:
+        m._lib.check(m.lib().kmb200_set_option(b"two_level", 1.0))
