@@ -35,7 +35,7 @@ struct PairH16Cfg {
     static constexpr int kA2Col0 = 128;                  // h1 at columns [0, 128), h2 at [128, 256)
     static constexpr int kAccCol0 = 256;
     static constexpr int kTmemCols = 512;
-    static constexpr int kNumBars = 4 /*bfull*/ + 8 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 16 /*a_full*/ + 4 /*a_free*/ + 2 /*acc_empty*/;
+    static constexpr int kNumBars = 4 /*bfull*/ + 8 /*tile_done*/ + 8 /*xfull*/ + 8 /*xempty*/ + 16 /*a_full*/ + 4 /*a_free*/ + 3 /*acc_empty*/;
     static constexpr int kXchgBytes = 2 * 128 * 5 * 4;
     static constexpr int kTailBytes = 2 * BN * 4 + kNumBars * 8 + 16 + kXchgBytes;
     static constexpr int kBudget = 227 * 1024 - 1024 - kTailBytes;
@@ -82,19 +82,19 @@ struct PairH16Cfg {
 // u + 1 phases when the waiter looks: with u - 1 it passes too early, with u + 2 it blocks for good.  So for every
 // ring: (lo) completion u - 1 has happened before any waiter asks for u, and (hi) completion u + 1 cannot happen before
 // every waiter of u has passed.  T = running centroid-tile index (tile), owner(T) = issuer T & 1, NG in {2, 4} groups.
-// Two facts used throughout: (F1) an issuer handles its tiles in order; (F2) issuing tile T needs acc_empty of T - 2,
-// which the epilogue gives after draining T - 2, and the epilogue drains tiles in order after waiting for each, so
-// "T issued" implies "every tile <= T - 3 is complete, and T - 2 too (same owner)".
+// Two facts used throughout: (F1) an issuer handles its tiles in order; (F2) issuing tile T needs acc_empty of T - A
+// (A = 2 or 3 accumulator buffers), which the epilogue gives after draining T - A, and the epilogue drains tiles in order
+// after waiting for each, so "T issued" implies "every tile <= T - A is complete".
 //  * tile_done[8], slot T & 7, completion number T >> 3, one arrival (owner's multicast commit).
-//      - epilogue waiter of T: (lo) it passed T - 8 itself.  (hi) T + 8 uses the accumulator of T + 6, T + 4, ...: it
-//        cannot even be issued before the epilogue drained T + 6 > T.
+//      - epilogue waiter of T: (lo) it passed T - 8 itself.  (hi) T + 8 uses the accumulator of T + 8 - A >= T + 5: it
+//        cannot even be issued before the epilogue drained that tile, which comes after T.
 //      - B producer, before the LOAD for tile T, waits for q = T - NG, the previous user of that group (in forward and
 //        backward row tiles alike: a tile that needs a load has walk index i >= NG, and walk index i - NG holds the same
 //        group).  (lo) needs q - 8 complete: the producer's previous load was for T' >= T - RES - 1 >= T - 5 (at most RES
 //        <= 4 resident tiles, which need no load, lie between two loads) and it waited for T' - NG then; by F2 everything
 //        <= T' - NG - 3 is complete as well, and q - 8 = T - NG - 8 <= T' - NG - 3.  (hi) q + 8 >= T + 4 is not complete:
 //        T itself needs this load, the owner of T is stuck at T (F1), and the other issuer gets no further than T + 1
-//        (T + 3 needs the epilogue past T + 1, hence past T).
+//        (T + 3 needs the accumulator of T + 1 or of T, i.e. the epilogue past T).
 //  * bfull[4] (leader), one completion per load into the group.  Waiter: owner(T) for the load of T, or -- resident
 //    tile -- for the load that filled the group.  (lo) the previous load into the group served tile T - NG, same owner
 //    because NG is even (b_groups() never returns 3): that issuer waited for it itself.  (hi) the next load into the
@@ -115,8 +115,9 @@ struct PairH16Cfg {
 //  * a_free[4] (both CTAs, 2 arrivals = both issuers' commits after their last tile of the row tile).  Waiters: the
 //    transform warps before rewriting the buffer.  (lo) they waited for the previous release before the previous write.
 //    (hi) the next release needs MMAs on the data they are about to write.
-//  * acc_empty[2] (leader; 8 local + 8 remote epilogue warps): owner(T) waits for the drain of T - 2; the epilogue
-//    drains T only after tile_done(T).  One phase per use on both sides.
+//  * acc_empty[A] (leader; 8 local + 8 remote epilogue warps): owner(T) waits for the drain of T - A (buffer T mod A,
+//    completion number T div A); the epilogue drains T only after tile_done(T).  One phase per use on both sides; the
+//    two owners alternate on a buffer when A = 3, and each has seen the other's previous use complete through F2.
 // Shapes that reach every branch: tools/stress.py (NT = 1, NT <= NG, NT > NG, odd / even row tiles per pair with a dummy
 // last tile, one / two A buffers, every BN), tests/test_gpu_production_path.py and tests/test_gpu_parity.py.
 template <int BN, int MODE, int NP = 3>
@@ -125,6 +126,8 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                        const AssignParams p) {
     using Cfg = PairH16Cfg<BN>;
     constexpr bool DBG = MODE == 1, FAST = MODE == 2, ONE = NP == 1;
+    // One-product FAST pass: the column index rides in the low mantissa bits of the (quantised) score, see the epilogue.
+    constexpr bool PACK = FAST && ONE;
     int n_rows = p.n;
     if (p.n_dev != nullptr) {
         const int c = *p.n_dev;
@@ -149,8 +152,18 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     // ld <= 128: h1 / h2 of a row tile take at most 64 columns each, so there are TWO A buffers (row tile parity)
     // and the transform of the next row tile overlaps this one's MMAs completely -- with few centroid tiles per
     // row tile (k <= 128: one) the a_free -> transform -> a_full handshake would otherwise be the critical path.
-    const bool ADB = (ONE && !WIDE) || KC <= 4;
-    const uint32_t abuf_cols = ONE ? 128 : 64;   // columns between the two A buffers
+    // (knockout bit 32, experiments: the one-product pass with two A buffers and two accumulators instead of one and three)
+    const bool ALT = ONE && !WIDE && (p.knockout & 32);
+    const bool ADB = KC <= 4 || ALT;
+    const uint32_t abuf_cols = (ALT && KC > 4) ? 128 : 64;       // columns between the two A buffers
+    // TMEM columns: three-product kernel: h1 [0, 128), h2 [128, 256), two accumulators [256, 512).  One-product pass,
+    // ld <= 256: h1 alone in [0, 128) and THREE accumulators [128, 512) -- with two, the MMAs of tile T + 2 wait for the
+    // epilogue of tile T, and its latency chain (commit -> wait -> tcgen05.ld -> 64 scores -> arrive -> wait) is about
+    // two tiles of tensor time (round-2 ncu: tensor pipe 50 % active, the kernel ran at 41 ms without any epilogue
+    // work against 59 ms with it, and 25 % fewer epilogue instructions bought 4 %); a third buffer gives the chain a
+    // whole extra tile.  One-product pass, ld > 256: h1 [0, 256), two accumulators.
+    const uint32_t NACC = (ONE && !WIDE && !ALT) ? 3u : 2u;
+    const uint32_t acc_col0 = NACC == 3 ? 128u : 256u;
     uint8_t *xs = smem;                                  // [XS][128 rows x 128 B], swizzled
     uint8_t *bs = smem + XS * kXStageBytes;              // [NG][C64][g1 chunk | g2 chunk] (this CTA's rows)
     uint8_t *tail = bs + NG * group_bytes;
@@ -163,7 +176,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
     uint64_t *a_full = bars + 28;     // [2][8]  h1/h2 of a 32-value chunk written (leader: its 4 warps + the peer's 4)
     uint64_t *a_free = bars + 44;     // [4]  units [0, C64a) / [C64a, C64) of A were read for the last time in this row
                                       //      tile (multicast); with two A buffers: [2 * buffer + 1], once per row tile
-    uint64_t *acc_empty = bars + 48;  // [2]  accumulator drained (leader: 8 local + 8 remote warps)
+    uint64_t *acc_empty = bars + 48;  // [3]  accumulator drained (leader: 8 local + 8 remote warps)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::kNumBars);
     uint32_t *xchg = tmem_slot + 4;   // [2][5][128]
 
@@ -194,7 +207,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             mbar_init(&a_full[8 + s], leader ? 8 : 4);
         }
         for (int s = 0; s < 4; ++s) mbar_init(&a_free[s], 2);   // both MMA issuers commit
-        for (int b = 0; b < 2; ++b) mbar_init(&acc_empty[b], leader ? 16 : 8);   // two epilogue warpgroups per CTA
+        for (int b = 0; b < 3; ++b) mbar_init(&acc_empty[b], leader ? 16 : 8);   // two epilogue warpgroups per CTA
         fence_mbar_init();
     }
     cluster_sync_all();
@@ -222,7 +235,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 const bool resident = rtn > 0 && i < RES;
                 if (!resident && tile >= (uint32_t)NG) {
                     const uint32_t q = tile - NG;
-                    mbar_wait(&tile_done[q & 7], (q >> 3) & 1);
+                    mbar_wait_parked(&tile_done[q & 7], (q >> 3) & 1);
                 }
                 if (!resident && elect_one()) {
                     uint8_t *st = bs + g * group_bytes;
@@ -250,7 +263,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             for (int kc = 0; kc < KC; ++kc) {
                 const uint32_t wg = kc & 1, j = xj[wg]++;
                 const uint32_t s = wg * XSW + j % XSW, ph = (j / XSW) & 1;
-                mbar_wait(&xempty[s], ph ^ 1);
+                mbar_wait_parked(&xempty[s], ph ^ 1);
                 if (elect_one()) {
                     mbar_arrive_expect_tx(&xfull[s], kXStageBytes);
                     tma_load_2d(&tm_x, &xfull[s], xs + s * kXStageBytes, kc * kChunkK, rt * kTileM);
@@ -282,12 +295,12 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     // NT <= NG the whole B operand stays resident).  Which of two exactly tied columns is met
                     // first now depends on the direction; tied rows are re-checked in FP64 with the index rule.
                     const int nt = (rtn & 1) ? NT - 1 - i : i;
-                    const uint32_t ab = tile & 1, aph = (tile >> 1) & 1;
+                    const uint32_t own = tile & 1, ab = tile % NACC, aph = (tile / NACC) & 1;
                     const uint32_t g = nt % NG;
                     const bool resident = rtn > 0 && i < RES;
                     const uint32_t bfull_par = resident ? ((bpar >> g) & 1) ^ 1 : (bpar >> g) & 1;   // resident: the load that filled it
                     if (!resident) bpar ^= 1u << g;
-                    if (ab != issuer) {
+                    if (own != issuer) {
                         // not this issuer's tile; a row tile of ONE tile leaves this issuer without any MMA on its
                         // A operand, but the release barriers still expect its arrival
                         if (NT == 1) {
@@ -306,7 +319,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     mbar_wait2(&acc_empty[ab], aph ^ 1, &bfull[g], bfull_par);
                     if (prof) { const long long t = clock64(); t_wait_acc += t - t_mark; t_mark = t; }
                     tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + Cfg::kAccCol0 + ab * BN;
+                    const uint32_t d_tmem = tmem_base + acc_col0 + ab * BN;
                     const uint32_t bsm0 = smem_u32(bs + g * group_bytes);
                     const bool last_tile = i == NT - 1;           // of the row tile
                     const bool my_last = last_tile || i == NT - 2;   // this issuer's last tile of the row tile
@@ -393,7 +406,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             for (int kc = wg; kc < KC; kc += 2, ++xj) {
                 const uint32_t xslot = wg * XSW + xj % XSW;
                 if (prof) t_mark = clock64();
-                mbar_wait(&xfull[xslot], (xj / XSW) & 1);
+                mbar_wait_parked(&xfull[xslot], (xj / XSW) & 1);
                 const uint8_t *xrow = xs + xslot * kXStageBytes + r * 128;
                 float x[32];
 #pragma unroll
@@ -421,15 +434,19 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 const uint32_t abuf = ADB ? (rtn & 1) : 0;
                 if (prof) { const long long t = clock64(); t_x += t - t_mark; t_mark = t; }
                 if (ADB) {
-                    if (rtn >= 2) mbar_wait(&a_free[abuf * 2 + 1], ((rtn >> 1) - 1) & 1);
+                    if (rtn >= 2) mbar_wait_parked(&a_free[abuf * 2 + 1], ((rtn >> 1) - 1) & 1);
                 } else if (rtn > 0) {
-                    mbar_wait(&a_free[(kc >> 1) < C64a ? 0 : 1], (rtn - 1) & 1);
+                    mbar_wait_parked(&a_free[(kc >> 1) < C64a ? 0 : 1], (rtn - 1) & 1);
                 }
                 tc_fence_after();
                 if (prof) {
                     const long long t = clock64();
                     t_free += t - t_mark;
                     t_mark = t;
+                }
+                if (p.knockout & 128) {   // timing experiments: the stores as usual, but of zeros
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) h1[i] = 0u;
                 }
                 if (!(p.knockout & 2)) {
                     tmem_st16(tmem_base + lane_addr + abuf * abuf_cols + kc * 16, h1);
@@ -468,7 +485,10 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
         const float cmax = p.cstats[0];
         const float unscale = p.cstats[2];
         const bool stages_cn = eg == 0 && r < BN;
-        if (stages_cn) cn_s[r] = p.cnorm[r];   // row tile 0 starts with centroid tile 0
+        // (PACK: the +inf norm of a padding column becomes a huge finite one -- a column byte inserted into the bits of
+        //  +inf would make a NaN, and two NaNs in one pair would pull `second` down to `best`)
+        constexpr float kPadNorm = 3.0e38f;
+        if (stages_cn) cn_s[r] = PACK ? fminf(p.cnorm[r], kPadNorm) : p.cnorm[r];   // row tile 0 starts with centroid tile 0
         asm volatile("bar.sync 1, 256;" ::: "memory");   // both epilogue warpgroups
         uint32_t tile = 0, rtn = 0;
         for (int rt = tile0; rt - (int)rank < num_row_tiles; rt += gridDim.x, ++rtn) {
@@ -482,21 +502,36 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             for (int q = 0; q < NS; ++q) { best[q] = second[q] = third[q] = inf; bidxf[q] = sidxf[q] = 0.f; }
             // ||x||^2 of this thread's row (near-tie bound at the end of the row tile): fetched now, off the critical path
             float xnsq = 0.f;
-            if (eg == 0 && rt * kTileM + r < n_rows) xnsq = __ldg(p.xnorm + rt * kTileM + r);
+            if ((eg == 0 || PACK) && rt * kTileM + r < n_rows) xnsq = __ldg(p.xnorm + rt * kTileM + r);
+            // PACK: the column's position in this warpgroup's half of the tile (0..63) replaces the low mantissa byte of
+            // the score (one LOP3; the value moves by < 2^-16 of itself, which the near-tie bound below allows for).  The
+            // minimum of such values carries its own arg-min, so the running update needs no compare and no select: per
+            // PAIR of scores min, max, max, 3-input min, min -- 4.5 instructions per score instead of 6, 3.5 instead of 5
+            // of them on the ALU pipe, which is the busiest unit of this kernel (68 % in the round-2 ncu capture).
+            // Equal packed values of one row tile differ in the column byte; which of them wins does not matter, the
+            // row is inside the bound and is decided later in FP64.
+            float bprev[NS], btile[NS];
+            const uint32_t keep = p.keep_mask;   // 0xffffff00, from a kernel parameter so that it lives in a register and
+                                                 // "mask, then insert the column" is ONE 3-input LOP3 with the column as immediate
+            if constexpr (PACK) {
+#pragma unroll
+                for (int q = 0; q < NS; ++q) { bprev[q] = inf; btile[q] = 0.f; }
+            }
             for (int i = 0; i < NT; ++i, ++tile) {
                 const int nt = (rtn & 1) ? NT - 1 - i : i;   // serpentine order, see the MMA issuer
-                const uint32_t ab = tile & 1;
-                const float *cn = cn_s + ab * BN;
+                const uint32_t ab = tile % NACC, cb = tile & 1;   // accumulator buffer, buffer of the staged norms
+                const float *cn = cn_s + cb * BN;
                 float cn_next = 0.f;
                 if (stages_cn) {
                     // the next tile in the walk (the next row tile starts where this one ends)
                     const int nn = i + 1 == NT ? nt : ((rtn & 1) ? nt - 1 : nt + 1);
                     cn_next = __ldg(p.cnorm + nn * BN + r);
+                    if constexpr (PACK) cn_next = fminf(cn_next, kPadNorm);
                 }
-                mbar_wait(&tile_done[tile & 7], (tile >> 3) & 1);
+                mbar_wait_parked(&tile_done[tile & 7], (tile >> 3) & 1);
                 tc_fence_after();
                 if (has_cols && !(p.knockout & 4)) {
-                    const uint32_t acc = tmem_base + lane_addr + Cfg::kAccCol0 + ab * BN + col0;
+                    const uint32_t acc = tmem_base + lane_addr + acc_col0 + ab * BN + col0;
                     uint32_t va[16], vb[16];
                     auto consume = [&](const uint32_t (&v)[16], int c0) {
                         const float basef = (float)(nt * BN + c0);
@@ -524,6 +559,21 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                             }
                         }
                     };
+                    // PACK (see above): B = first column of the batch inside this warpgroup's half, a literal at every
+                    // call so that the column numbers below are immediates
+                    auto consume_pack = [&](const uint32_t (&v)[16], const int B) {
+#pragma unroll
+                        for (int i = 0; i < 16; i += 2) {
+                            const int q = (i >> 1) & (NS - 1);
+                            const uint32_t ua = __float_as_uint(fmaf(__uint_as_float(v[i]), unscale, cn[col0 + B + i]));
+                            const uint32_t ub = __float_as_uint(fmaf(__uint_as_float(v[i + 1]), unscale, cn[col0 + B + i + 1]));
+                            const float sa = __uint_as_float((ua & keep) | (uint32_t)(B + i));
+                            const float sb = __uint_as_float((ub & keep) | (uint32_t)(B + i + 1));
+                            const float lo = fminf(sa, sb), hi = fmaxf(sa, sb);
+                            second[q] = fmin3(second[q], fmaxf(best[q], lo), hi);
+                            best[q] = fminf(best[q], lo);
+                        }
+                    };
                     if constexpr (FAST) {
                         // The fast update is short enough that the drain is bound by the LATENCY of tcgen05.ld (one
                         // load per 16 columns, each issued after the previous wait): up to three loads in flight.
@@ -533,13 +583,25 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                         tmem_ld16(acc + 16, vb);
                         if constexpr (NB > 2) tmem_ld16(acc + 32, vc);
                         tmem_wait_ld();
-                        consume(va, col0);
+                        if (p.knockout & 64) {   // timing experiments: the TMEM loads without the bookkeeping
+                            if constexpr (NB > 3) { tmem_ld16(acc + 48, va); tmem_wait_ld(); }
+                            best[0] = fminf(best[0], __uint_as_float(va[0] ^ vb[1] ^ vc[2]));
+                        } else {
+                        if constexpr (PACK) consume_pack(va, 0); else consume(va, col0);
                         if constexpr (NB > 3) tmem_ld16(acc + 48, va);
-                        consume(vb, col0 + 16);
-                        if constexpr (NB > 2) consume(vc, col0 + 32);
+                        if constexpr (PACK) consume_pack(vb, 16); else consume(vb, col0 + 16);
+                        if constexpr (NB > 2) { if constexpr (PACK) consume_pack(vc, 32); else consume(vc, col0 + 32); }
                         if constexpr (NB > 3) {
                             tmem_wait_ld();
-                            consume(va, col0 + 48);
+                            if constexpr (PACK) consume_pack(va, 48); else consume(va, col0 + 48);
+                        }
+                        }
+                        if constexpr (PACK) {   // which centroid tile the running minimum of every set comes from
+#pragma unroll
+                            for (int q = 0; q < NS; ++q) {
+                                btile[q] = best[q] < bprev[q] ? (float)nt : btile[q];
+                                bprev[q] = best[q];
+                            }
                         }
                     } else {
                         tmem_ld16(acc, va);
@@ -560,12 +622,17 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     if (leader) mbar_arrive(&acc_empty[ab]);
                     else mbar_arrive_remote_relaxed(&acc_empty[ab], 0);
                 }
-                if (stages_cn) cn_s[(ab ^ 1) * BN + r] = cn_next;   // last read one tile ago, before the previous bar.sync
+                if (stages_cn) cn_s[(cb ^ 1) * BN + r] = cn_next;   // last read one tile ago, before the previous bar.sync
                 asm volatile("bar.sync 1, 256;" ::: "memory");
             }
             int bidx[NS], sidx[NS];
 #pragma unroll
             for (int q = 0; q < NS; ++q) { bidx[q] = (int)bidxf[q]; sidx[q] = (int)sidxf[q]; }
+            if constexpr (PACK) {
+#pragma unroll
+                for (int q = 0; q < NS; ++q)
+                    bidx[q] = best[q] < inf ? (int)btile[q] * BN + col0 + (int)(__float_as_uint(best[q]) & 0xffu) : 0;
+            }
             // merge sets 1..3 into set 0: lower value first, equal values -> lower index first
             float mb = best[0], ms = second[0], mt = third[0];
             int mbi = bidx[0], msi = sidx[0];
@@ -613,8 +680,11 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                     p.labels[row] = mbi;
                     const float xn = sqrtf(xnsq);
                     // relative part (accumulation, split residuals) + absolute part (FP16 subnormal range)
-                    const float bound = 2.0f * (p.eps * (2.0f * xn * cmax + cmax * cmax) +
-                                                p.sqrt_ld * (p.cstats[4] * 2.0f * cmax + p.cstats[5] * xn));
+                    // (eps_x: the part of the error that is proportional to the cross term alone -- the operand
+                    //  roundings of the one-product pass -- and not to the centre norm, which is added exactly)
+                    float bound = 2.0f * (p.eps_x * 2.0f * xn * cmax + p.eps * (2.0f * xn * cmax + cmax * cmax) +
+                                          p.sqrt_ld * (p.cstats[4] * 2.0f * cmax + p.cstats[5] * xn));
+                    if constexpr (PACK) bound += 3.1e-5f * (2.0f * xn * cmax + cmax * cmax);   // 2 x 2^-16: the packed byte
                     if constexpr (FAST) {
                         // (in FAST mode `ms` is exact -- the merge below only needs values for it -- msi / mt are not)
                         if (ms - mb <= bound) {

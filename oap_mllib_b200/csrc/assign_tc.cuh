@@ -60,6 +60,8 @@ struct AssignParams {
     int32_t stages;
     int32_t passes;        // 3 = 3xTF32, 1 = single TF32 pass
     float eps;             // relative error bound of one score
+    uint32_t keep_mask = 0xffffff00u;   // (see the one-product epilogue of assign_pair_h16.cuh)
+    float eps_x = 0.f;     // FP16-split kernel, one-product pass: error relative to 2 |x| |c| alone (operand roundings)
     float *dbg_scores;     // optional [n x kpad] dump of the tensor-core scores (tests only), else nullptr
     int32_t kpad;
     long long *role_prof;  // optional cycle counters of the MMA-issuer warp of CTA 0 (diagnostics), else nullptr

@@ -1007,9 +1007,13 @@ static bool cascade_prepare(kmb200_table *t) {
     return true;
 }
 
-// Score error of the one-product pass: both operands rounded to 11 bits (2^-11 each, relative to |x||w| element
-// by element, so 2^-10 of 2|x||c| by Cauchy-Schwarz), ld/16 accumulator updates, FP32 norm and final FMA.
-static float score_eps_h16_one(int ld) { return (float)(g_eps_scale * (ldexp(1.0, -10) + ldexp(ld / 16.0 + 32.0, -24))); }
+// Score error of the one-product pass, the part relative to (2|x||c| + |c|^2): ld/16 accumulator updates, FP32 norm
+// and final FMA ...
+static float score_eps_h16_one(int ld) { return (float)(g_eps_scale * ldexp(ld / 16.0 + 32.0, -24)); }
+// ... and its operand roundings: x sx -> h1 and -2c sw -> g1 are each within 2^-11 (relative, element by element), so every
+// product is within 2^-10 + 2^-22 and the cross term -2 x.c within (2^-10 + 2^-22) * 2 |x| |c| (Cauchy-Schwarz).  The
+// centre norm is added in FP32 and carries no such error, so this part of the bound scales with 2 |x| |c| alone.
+static float score_eps_h16_one_x() { return (float)(g_eps_scale * (ldexp(1.0, -10) + ldexp(1.0, -22))); }
 
 template <int BN, int MODE, int NP>
 static int launch_assign_h16_bn(kmb200_table *t, const H16Src &src) {
@@ -1038,6 +1042,7 @@ static int launch_assign_h16_bn(kmb200_table *t, const H16Src &src) {
     p.stages = Cfg::x_slots(kc) | (Cfg::b_groups(kc) << 8);
     p.passes = 3;
     p.eps = NP == 1 ? score_eps_h16_one(t->ld) : score_eps_h16(t->ld);
+    p.eps_x = NP == 1 ? score_eps_h16_one_x() : 0.f;
     p.dbg_scores = w.dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;

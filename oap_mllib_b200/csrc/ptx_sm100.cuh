@@ -47,6 +47,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
 }
+// The same wait with a suspend-time hint: the hardware parks the warp until the phase completes (or the hint, in
+// nanoseconds, runs out) instead of handing the test back at once.  For the warps that wait for long stretches
+// (producers, transform, epilogue): a bare try_wait loop re-issues every ~25 cycles, and in the one-product kernel those
+// polls were a quarter of all instructions issued (round-2 ncu capture), taken from the warps that had work to do.
+__device__ __forceinline__ void mbar_wait_parked(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity), "r"(1000000u)
+            : "memory");
+    } while (!ok);
+}
 
 // Two barriers polled together so their try_wait latencies overlap (the MMA queue is shallow: every
 // exposed wait leaves the tensor pipe idle).
@@ -351,6 +367,13 @@ __device__ __forceinline__ float to_tf32_rna(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
     return __uint_as_float(r);
+}
+
+// 3-input minimum (FMNMX3, sm_100)
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
 }
 
 __device__ __forceinline__ bool elect_one() {

@@ -247,12 +247,13 @@ def test_coarse_pass_score_error_is_inside_its_bound(m):
             t.release()
         exact = (Cn ** 2).sum(1)[None, :] - 2.0 * X64 @ Cn.T
         cmax = np.sqrt((Cn ** 2).sum(1).max())
-        scale = 2.0 * np.sqrt((X64 ** 2).sum(1))[:, None] * cmax + cmax ** 2
-        err = np.abs(sc[:, :k].astype(np.float64) - exact) / scale
+        cross = 2.0 * np.sqrt((X64 ** 2).sum(1))[:, None] * cmax
         ld = (d + 31) // 32 * 32
-        eps = 2.0 ** -10 + 2.0 ** -24 * (ld / 16.0 + 32.0)
-        print(f"coarse score error d={d} k={k}: max {err.max():.3e} (bound {eps:.3e})")
-        assert 1e-7 < err.max() <= 0.5 * eps    # well inside the bound, and really the coarse product (not the fine one)
+        # the kernel's bound: operand roundings relative to the cross term alone, accumulation relative to cross + norm
+        bound = (2.0 ** -10 + 2.0 ** -22) * cross + 2.0 ** -24 * (ld / 16.0 + 32.0) * (cross + cmax ** 2)
+        err = np.abs(sc[:, :k].astype(np.float64) - exact) / bound
+        print(f"coarse score error d={d} k={k}: max {err.max():.3f} of the bound, {(np.abs(sc[:, :k] - exact) / cross).max():.3e} of 2|x||c|max")
+        assert 1e-4 < err.max() <= 0.5    # well inside the bound, and really the coarse product (not the fine one)
 
 
 def test_force_simt_path_agrees(m):
