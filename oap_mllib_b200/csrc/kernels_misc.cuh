@@ -835,46 +835,76 @@ __global__ void rowdist_kernel(const float *__restrict__ X, const double *__rest
     }
 }
 
-// Arg-max of dist over rows not in excl[0..nexcl): stage 1 per CTA, stage 2 single CTA (nblk1 == 0
-// means "reduce the nb stage-1 results").  Ties -> lowest row index.
-__global__ void argmax_kernel(const double *__restrict__ dist, int64_t n, const int32_t *__restrict__ excl,
-                              int nexcl, double *__restrict__ bval, int32_t *__restrict__ bidx, int stage2_nb) {
-    __shared__ double sv[256];
-    __shared__ int32_t si[256];
-    double v = -1.0;
-    int32_t idx = -1;
-    if (stage2_nb == 0) {
-        for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
-            bool skip = false;
-            for (int e = 0; e < nexcl; ++e) skip |= (excl[e] == (int32_t)r);
-            const double dv = dist[r];
-            if (!skip && (dv > v || (dv == v && (int32_t)r < idx))) { v = dv; idx = (int32_t)r; }
-        }
-    } else {
-        for (int b = threadIdx.x; b < stage2_nb; b += blockDim.x) {
-            const double dv = bval[b];
-            const int32_t di = bidx[b];
-            if (di >= 0 && (dv > v || (dv == v && di < idx))) { v = dv; idx = di; }
-        }
-    }
-    sv[threadIdx.x] = v;
-    si[threadIdx.x] = idx;
+// ---- the m largest distances without a host round trip per candidate: radix select on the bits of the (non-negative)
+// FP64 distances, 12 bits per round.  Round r looks at the rows whose key agrees with `prefix` above bit shift + 12 and
+// histograms the digit (key >> shift) & 0xfff; digit_select_kernel then finds the digit that holds the `need`-th
+// largest of them.  Typically two rounds narrow the threshold bin to a handful of rows; dist_collect_kernel lists every
+// row at or above the bin and the host orders that short list (distance descending, row ascending).
+constexpr int kDigitBits = 12;
+__global__ void dist_digit_hist_kernel(const double *__restrict__ dist, int64_t n, unsigned long long prefix, int shift,
+                                       int first_round, unsigned int *__restrict__ hist) {
+    __shared__ unsigned int sh[1 << kDigitBits];
+    for (int i = threadIdx.x; i < (1 << kDigitBits); i += blockDim.x) sh[i] = 0;
     __syncthreads();
-    for (int o = 128; o > 0; o >>= 1) {
-        if ((int)threadIdx.x < o) {
-            const double ov = sv[threadIdx.x + o];
-            const int32_t oi = si[threadIdx.x + o];
-            if (oi >= 0 && (ov > sv[threadIdx.x] || (ov == sv[threadIdx.x] && (si[threadIdx.x] < 0 || oi < si[threadIdx.x])))) {
-                sv[threadIdx.x] = ov;
-                si[threadIdx.x] = oi;
-            }
-        }
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long key = (unsigned long long)__double_as_longlong(dist[r]);
+        if (first_round || (key >> (shift + kDigitBits)) == prefix)
+            atomicAdd(&sh[(unsigned)(key >> shift) & ((1u << kDigitBits) - 1u)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < (1 << kDigitBits); i += blockDim.x)
+        if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+// One CTA of 1024 threads.  out[0] = the digit d whose bin holds the need-th largest key, out[1] = keys in higher
+// bins, out[2] = keys in bin d.
+__global__ void digit_select_kernel(const unsigned int *__restrict__ hist, unsigned int need, unsigned int *__restrict__ out) {
+    __shared__ unsigned int part[1024];
+    constexpr int PER = (1 << kDigitBits) / 1024;   // digits per thread, highest digits in thread 0
+    const int t = threadIdx.x;
+    unsigned int mine = 0;
+    for (int i = 0; i < PER; ++i) mine += hist[(1 << kDigitBits) - 1 - (t * PER + i)];
+    part[t] = mine;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {   // inclusive scan over the threads (descending digits)
+        const unsigned int a = t >= o ? part[t - o] : 0u;
+        __syncthreads();
+        part[t] += a;
         __syncthreads();
     }
-    if (threadIdx.x == 0) {
-        const int out = stage2_nb == 0 ? blockIdx.x : stage2_nb;  // stage 2 writes slot [nb]
-        bval[out] = sv[0];
-        bidx[out] = si[0];
+    const unsigned int before = part[t] - mine;   // keys in the digits above this thread's
+    if (before < need && need <= part[t]) {
+        unsigned int above = before;
+        for (int i = 0; i < PER; ++i) {
+            const int d = (1 << kDigitBits) - 1 - (t * PER + i);
+            const unsigned int c = hist[d];
+            if (need <= above + c) {
+                out[0] = (unsigned)d;
+                out[1] = above;
+                out[2] = c;
+                break;
+            }
+            above += c;
+        }
+    }
+}
+// Lists (key, row) of every row whose key is at or above the threshold bin: (key >> shift) >= prefix.
+__global__ void dist_collect_kernel(const double *__restrict__ dist, int64_t n, unsigned long long prefix, int shift,
+                                    unsigned long long *__restrict__ keys, int32_t *__restrict__ rows, unsigned int *count,
+                                    unsigned int cap) {
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long key = (unsigned long long)__double_as_longlong(dist[r]);
+        if ((key >> shift) >= prefix) {
+            const unsigned int pos = atomicAdd(count, 1u);
+            if (pos < cap) { keys[pos] = key; rows[pos] = (int32_t)r; }
+        }
+    }
+}
+// out[i][0..d) = X[rows[i]][0..d)
+__global__ void gather_list_kernel(const float *__restrict__ X, const int32_t *__restrict__ rows, int m, int d, int ld,
+                                   float *__restrict__ out) {
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < (int64_t)m * d; e += (int64_t)gridDim.x * blockDim.x) {
+        const int i = (int)(e / d), c = (int)(e % d);
+        out[e] = X[(size_t)rows[i] * ld + c];
     }
 }
 

@@ -1467,82 +1467,141 @@ static int download_centers(kmb200_table *t, double *out, int k, int d) {
 
 // ------------------------------------------------------------------------------------ empty clusters
 // oneDAL's finalizeCompute gives an empty cluster the farthest remaining candidate row and takes that
-// row's distance out of the objective.  Rare, host-driven: m = number of
-// empty clusters; every rank finds its m farthest rows, the lists are all-gathered and merged in
-// (distance desc, rank asc, row asc) order identically on every rank.
+// row's distance out of the objective (recalled from the published source, pinned by no vector
+// of the reference's tests).  m = number of empty clusters; every rank finds its m farthest rows ON THE DEVICE -- FP64
+// distance of every row to its own centre, then a radix select over the bits of those distances (12 bits per round,
+// one small read-back per round, typically two rounds) and a short list of the rows at or above the threshold --
+// the lists are all-gathered and merged in (distance desc, rank asc, row asc) order identically on every rank.
+struct DevBuf {   // frees what it holds on every exit path
+    std::vector<void *> ptrs;
+    ~DevBuf() { for (void *p : ptrs) if (p) cudaFree(p); }
+    template <typename T> int alloc(T **p, size_t count) {
+        *p = nullptr;
+        CU_TRY(cudaMalloc(reinterpret_cast<void **>(p), std::max<size_t>(count, 1) * sizeof(T)));
+        ptrs.push_back(*p);
+        return 0;
+    }
+};
+
+// The m rows with the largest dist (ties: lower row first), as (distance, row) in that order; fewer than m when the
+// table is shorter.
+static int select_farthest(kmb200_table *t, const double *dist, int m, std::vector<std::pair<double, int32_t>> *out) {
+    const int64_t n = t->rows;
+    cudaStream_t st = t->stream;
+    const unsigned want = (unsigned)std::min<int64_t>(m, n);
+    const unsigned cap = want + 16384;   // the threshold bin may hold this many rows beyond the ones wanted
+    DevBuf buf;
+    unsigned int *hist = nullptr, *sel = nullptr, *count = nullptr;
+    unsigned long long *keys = nullptr;
+    int32_t *rows = nullptr;
+    KM_TRY(buf.alloc(&hist, 1 << kDigitBits));
+    KM_TRY(buf.alloc(&sel, 4));
+    KM_TRY(buf.alloc(&count, 1));
+    KM_TRY(buf.alloc(&keys, cap));
+    KM_TRY(buf.alloc(&rows, cap));
+    out->clear();
+    if (want == 0) return 0;
+    const int grid = std::min<int64_t>((n + 255) / 256, (int64_t)t->num_sms * 8);
+    unsigned long long prefix = 0;
+    unsigned need = want;
+    // digits at bits 52..63 (the sign bit of a distance is 0), 40..51, 28..39, 16..27, 4..15; what is left below bit 4
+    // is 16 ulps of an FP64 distance: rows that close count as tied and are listed together
+    int shift = 64 - kDigitBits;
+    for (int round = 0;; ++round) {
+        CU_TRY(cudaMemsetAsync(hist, 0, sizeof(unsigned int) << kDigitBits, st));
+        dist_digit_hist_kernel<<<grid, 256, 0, st>>>(dist, n, prefix, shift, round == 0, hist);
+        KM_TRY(post_launch(__LINE__));
+        digit_select_kernel<<<1, 1024, 0, st>>>(hist, need, sel);
+        KM_TRY(post_launch(__LINE__));
+        g_prof.kernel_launches += 2;
+        unsigned h[3];
+        CU_TRY(cudaMemcpyAsync(h, sel, sizeof(h), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaStreamSynchronize(st));
+        prefix = (prefix << kDigitBits) | h[0];
+        need -= h[1];                      // still wanted from the threshold bin, 1 <= need <= h[2]
+        if (h[2] - need <= 16384 || shift < kDigitBits) break;   // the bin is small enough to be listed whole
+        shift -= kDigitBits;
+    }
+    CU_TRY(cudaMemsetAsync(count, 0, sizeof(unsigned int), st));
+    dist_collect_kernel<<<grid, 256, 0, st>>>(dist, n, prefix, shift, keys, rows, count, cap);
+    KM_TRY(post_launch(__LINE__));
+    g_prof.kernel_launches++;
+    unsigned got = 0;
+    CU_TRY(cudaMemcpyAsync(&got, count, sizeof(got), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    if (got > cap)
+        return fail(KMB200_ERR_LIMIT, "empty-cluster candidates: %u rows tie for the farthest %u (exactly equal distances); "
+                                      "more than the %u the candidate list holds", got, want, cap);
+    std::vector<unsigned long long> hk(got);
+    std::vector<int32_t> hr(got);
+    CU_TRY(cudaMemcpyAsync(hk.data(), keys, (size_t)got * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(hr.data(), rows, (size_t)got * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    std::vector<int> idx(got);
+    for (unsigned i = 0; i < got; ++i) idx[i] = (int)i;
+    std::sort(idx.begin(), idx.end(), [&](int a, int b) { return hk[a] != hk[b] ? hk[a] > hk[b] : hr[a] < hr[b]; });
+    for (unsigned i = 0; i < std::min(got, want); ++i) {
+        double v;
+        memcpy(&v, &hk[idx[i]], sizeof(v));
+        out->emplace_back(v, hr[idx[i]]);
+    }
+    return 0;
+}
+
 static int handle_empty_clusters(kmb200_table *t, kmb200_comm *comm, int m, double tol, double *cost,
                                  int *moved_extra) {
     Workspace &w = t->ws;
     const int k = w.k, ld = t->ld, d = t->d;
     const int world = comm ? comm->world : 1;
     const int64_t n = t->rows;
+    cudaStream_t st = t->stream;
     g_prof.empty_cluster_events++;
-    double *dist = nullptr, *bval = nullptr, *dgather = nullptr;
-    int32_t *bidx = nullptr, *excl = nullptr;
-    const int nb = std::min<int>(t->num_sms * 4, 1024);
     const int rec = 2 + d;  // distance, local row, row values
     std::vector<double> mine((size_t)m * rec, 0.0), all((size_t)m * rec * world, 0.0);
-    std::vector<int32_t> chosen;
-    std::vector<float> rowbuf(d);
-    int rc = 0;
-    auto cleanup = [&]() {
-        if (dist) cudaFree(dist);
-        if (bval) cudaFree(bval);
-        if (bidx) cudaFree(bidx);
-        if (excl) cudaFree(excl);
-        if (dgather) cudaFree(dgather);
-    };
-#define EC_TRY(expr)                                                                     \
-    do {                                                                                 \
-        cudaError_t e__ = (expr);                                                        \
-        if (e__ != cudaSuccess) {                                                        \
-            cleanup();                                                                   \
-            return fail(KMB200_ERR_DEVICE, "%s failed: %s", #expr, cudaGetErrorString(e__)); \
-        }                                                                                \
-    } while (0)
-    EC_TRY(cudaMalloc(&dist, (size_t)n * sizeof(double)));
-    EC_TRY(cudaMalloc(&bval, (size_t)(nb + 1) * sizeof(double)));
-    EC_TRY(cudaMalloc(&bidx, (size_t)(nb + 1) * sizeof(int32_t)));
-    EC_TRY(cudaMalloc(&excl, (size_t)std::max(m, 1) * sizeof(int32_t)));
+    for (int e = 0; e < m; ++e) mine[(size_t)e * rec] = mine[(size_t)e * rec + 1] = -1.0;   // "no candidate"
+    DevBuf buf;
+    double *dist = nullptr, *dgather = nullptr;
+    int32_t *drows = nullptr;
+    float *dvals = nullptr;
+    KM_TRY(buf.alloc(&dist, (size_t)n));
     // distances to the centres this iteration's assignment used: w.cent still holds them (finalize
     // wrote the new centres to w.cent2)
-    rowdist_kernel<<<t->num_sms * 8, 256, 0, t->stream>>>(t->X, w.cent, w.labels, n, ld, dist);
-    EC_TRY(cudaGetLastError());
+    rowdist_kernel<<<t->num_sms * 8, 256, 0, st>>>(t->X, w.cent, w.labels, n, ld, dist);
+    KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
-    for (int e = 0; e < m; ++e) {
-        if (e > 0) EC_TRY(cudaMemcpyAsync(excl, chosen.data(), chosen.size() * sizeof(int32_t), cudaMemcpyHostToDevice, t->stream));
-        argmax_kernel<<<nb, 256, 0, t->stream>>>(dist, n, excl, (int)chosen.size(), bval, bidx, 0);
-        argmax_kernel<<<1, 256, 0, t->stream>>>(nullptr, 0, nullptr, 0, bval, bidx, nb);
-        g_prof.kernel_launches += 2;
-        double v;
-        int32_t idx;
-        EC_TRY(cudaMemcpyAsync(&v, bval + nb, sizeof(double), cudaMemcpyDeviceToHost, t->stream));
-        EC_TRY(cudaMemcpyAsync(&idx, bidx + nb, sizeof(int32_t), cudaMemcpyDeviceToHost, t->stream));
-        EC_TRY(cudaStreamSynchronize(t->stream));
-        double *r = &mine[(size_t)e * rec];
-        if (idx < 0) {
-            r[0] = -1.0;
-            r[1] = -1.0;
-            continue;
+    std::vector<std::pair<double, int32_t>> far;
+    KM_TRY(select_farthest(t, dist, m, &far));
+    if (!far.empty()) {
+        const int got = (int)far.size();
+        std::vector<int32_t> hrows(got);
+        for (int e = 0; e < got; ++e) hrows[e] = far[e].second;
+        KM_TRY(buf.alloc(&drows, (size_t)got));
+        KM_TRY(buf.alloc(&dvals, (size_t)got * d));
+        CU_TRY(cudaMemcpyAsync(drows, hrows.data(), (size_t)got * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        gather_list_kernel<<<std::min(got, 1024), 256, 0, st>>>(t->X, drows, got, d, ld, dvals);
+        KM_TRY(post_launch(__LINE__));
+        g_prof.kernel_launches++;
+        std::vector<float> hvals((size_t)got * d);
+        CU_TRY(cudaMemcpyAsync(hvals.data(), dvals, hvals.size() * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaStreamSynchronize(st));
+        for (int e = 0; e < got; ++e) {
+            double *r = &mine[(size_t)e * rec];
+            r[0] = far[e].first;
+            r[1] = (double)far[e].second;
+            for (int c = 0; c < d; ++c) r[2 + c] = (double)hvals[(size_t)e * d + c];
         }
-        chosen.push_back(idx);
-        EC_TRY(cudaMemcpyAsync(rowbuf.data(), t->X + (size_t)idx * t->ld, (size_t)d * sizeof(float), cudaMemcpyDeviceToHost, t->stream));
-        EC_TRY(cudaStreamSynchronize(t->stream));
-        r[0] = v;
-        r[1] = (double)idx;
-        for (int c = 0; c < d; ++c) r[2 + c] = (double)rowbuf[c];
     }
     if (world > 1) {
         const size_t cnt = (size_t)m * rec;
-        EC_TRY(cudaMalloc(&dgather, cnt * (world + 1) * sizeof(double)));
-        EC_TRY(cudaMemcpyAsync(dgather, mine.data(), cnt * sizeof(double), cudaMemcpyHostToDevice, t->stream));
-        ncclResult_t r = g_nccl.AllGather(dgather, dgather + cnt, cnt, ncclDouble, comm->comm, t->stream);
+        KM_TRY(buf.alloc(&dgather, cnt * (world + 1)));
+        CU_TRY(cudaMemcpyAsync(dgather, mine.data(), cnt * sizeof(double), cudaMemcpyHostToDevice, st));
+        ncclResult_t r = g_nccl.AllGather(dgather, dgather + cnt, cnt, ncclDouble, comm->comm, st);
         if (r != ncclSuccess) {
-            cleanup();
+            comm->broken = true;
             return fail(KMB200_ERR_COMM, "ncclAllGather failed: %s", g_nccl.GetErrorString(r));
         }
-        EC_TRY(cudaMemcpyAsync(all.data(), dgather + cnt, cnt * world * sizeof(double), cudaMemcpyDeviceToHost, t->stream));
-        EC_TRY(cudaStreamSynchronize(t->stream));
+        CU_TRY(cudaMemcpyAsync(all.data(), dgather + cnt, cnt * world * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CU_TRY(cudaStreamSynchronize(st));
     } else {
         all = mine;
     }
@@ -1551,35 +1610,29 @@ static int handle_empty_clusters(kmb200_table *t, kmb200_comm *comm, int m, doub
     std::vector<int> idx((size_t)m * world);
     for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
     std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return all[(size_t)a * rec] > all[(size_t)b * rec]; });
-    // substitute in cluster-index order
-    std::vector<double> red_counts(k);
-    EC_TRY(cudaMemcpyAsync(red_counts.data(), w.red + (size_t)k * t->ld, (size_t)k * sizeof(double), cudaMemcpyDeviceToHost, t->stream));
-    EC_TRY(cudaStreamSynchronize(t->stream));
-    std::vector<double> oldc(d);
+    // counts and the centres of this iteration, one read-back each; then substitute in cluster-index order
+    std::vector<double> red_counts(k), oldc((size_t)k * ld);
+    CU_TRY(cudaMemcpyAsync(red_counts.data(), w.red + (size_t)k * ld, (size_t)k * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaMemcpyAsync(oldc.data(), w.cent, (size_t)k * ld * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
     int used = 0;
     for (int j = 0; j < k; ++j) {
         if (red_counts[j] > 0.0) continue;
-        if (used >= (int)idx.size() || !(all[(size_t)idx[used] * rec] > 0.0)) {
-            rc = fail(KMB200_ERR_EMPTY, "cluster %d is empty and no positive-distance candidate row is left", j);
-            break;
-        }
-        const double *r = &all[(size_t)idx[used] * rec];
+        if (used >= (int)idx.size() || !(all[(size_t)idx[used] * rec] > 0.0))
+            return fail(KMB200_ERR_EMPTY, "cluster %d is empty and no positive-distance candidate row is left", j);
+        const double *r = &all[(size_t)idx[used] * rec];   // (`all` outlives the copies below: synchronised before return)
         ++used;
-        EC_TRY(cudaMemcpyAsync(oldc.data(), w.cent + (size_t)j * t->ld, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, t->stream));
-        EC_TRY(cudaStreamSynchronize(t->stream));
         double s = 0.0;
         for (int c = 0; c < d; ++c) {
-            const double df = r[2 + c] - oldc[c];
+            const double df = r[2 + c] - oldc[(size_t)j * ld + c];
             s += df * df;
         }
         if (!(s <= tol * tol)) (*moved_extra)++;
-        EC_TRY(cudaMemcpyAsync(w.cent2 + (size_t)j * t->ld, r + 2, (size_t)d * sizeof(double), cudaMemcpyHostToDevice, t->stream));
-        EC_TRY(cudaStreamSynchronize(t->stream));
+        CU_TRY(cudaMemcpyAsync(w.cent2 + (size_t)j * ld, r + 2, (size_t)d * sizeof(double), cudaMemcpyHostToDevice, st));
         *cost -= r[0];
     }
-#undef EC_TRY
-    cleanup();
-    return rc;
+    CU_TRY(cudaStreamSynchronize(st));
+    return 0;
 }
 
 // ------------------------------------------------------------------------------------ profile

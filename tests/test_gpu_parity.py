@@ -317,6 +317,17 @@ def test_empty_cluster_substitution(m):
     np.testing.assert_allclose(c[2], [1.0, 0.0])
 
 
+@pytest.mark.parametrize("n,d,k,empties", [(50000, 16, 160, 60), (300_000, 64, 300, 120)])
+def test_many_empty_clusters_at_once(m, n, d, k, empties):
+    """Dozens of clusters empty in the same iteration (the benchmark's own warm-up produces 59): the farthest rows are
+    picked on the device by a radix select over the FP64 distances and must be the oracle's, in the oracle's order."""
+    X, _, _ = ko.gaussian_blobs(n, d, k - empties, seed=n + empties)
+    init = ko.row_init_centers(X, k)
+    init[::k // empties][:empties] = 1.0e3 + np.arange(empties)[:, None]     # far from every row: empty at once
+    check_fit_parity(m, X, init, tol=1e-4, max_iter=4)
+    assert m.kmeans.profile()["empty_cluster_events"] >= 1
+
+
 def test_max_iter_zero_and_tol_semantics(m):
     X, _, _ = ko.gaussian_blobs(3000, 8, 4, seed=9)
     init = ko.row_init_centers(X, 4)

@@ -23,7 +23,9 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     failures = []
     cases = [("blobs", 60000, 64, 100, 8), ("blobs", 30011, 256, 300, 6), ("blobs", 200000, 32, 16, 6), ("empty", 0, 0, 0, 5),
-             ("blobs2", 30011, 256, 300, 6)]   # blobs2: two-level bookkeeping forced on (fast pass + near-tie pass)
+             ("blobs2", 30011, 256, 300, 6),   # blobs2: two-level bookkeeping forced on (fast pass + near-tie pass)
+             ("many_empty", 60000, 16, 160, 4),  # 60 clusters empty at once: candidates from every rank, merged
+             ("blobs", 600000, 256, 1000, 4)]    # >= 2^18 rows per rank at 2 ranks: the cascade with its default options
     for kind, n, d, k, iters in cases:
         m._lib.check(m.lib().kmb200_set_option(b"two_level", 2.0 if kind == "blobs2" else 1.0))
         if kind == "blobs2":
@@ -31,6 +33,10 @@ def main():
         if kind == "blobs":
             X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + k)
             init = ko.row_init_centers(X, k)
+        elif kind == "many_empty":
+            X, _, _ = ko.gaussian_blobs(n, d, k - 60, seed=n + k)
+            init = ko.row_init_centers(X, k)
+            init[::2][:60] = 1.0e3 + np.arange(60)[:, None]
         else:
             X = np.array([[0.0, 0], [1, 0], [0, 1], [10, 10], [11, 10], [0.5, 0.5], [10.5, 10.2], [3, 3]], np.float32)
             init = np.array([[0.0, 0], [10, 10], [100, 100], [-50, -50]])
