@@ -217,6 +217,29 @@ int kmb200_cluster_sizes_noalloc(const int32_t *labels_dev, int64_t n, int32_t k
 int kmb200_debug_scores(kmb200_table *table, const double *centers, int32_t k, int32_t d, float *scores_host,
                         int32_t *kpad_out);
 
+/* ---- k-means|| initialisation passes --------------------------------------------
+ * Replace the JVM passes over every row in initKMeansParallel (scala/org/apache/spark-3.1.1/mllib/clustering/
+ * KMeans.scala:370-432); the driver-side logic (the loop over initSteps, de-duplication, the weighted local k-means++
+ * over the ~2k candidates) stays with the caller.
+ *   init_costs   :395-401  cost_i = min(cost_i, min_j ||x_i - c_j||^2) over the m centres added in the last step (first_step
+ *                != 0: the costs start at +infinity), kept on the device per table; *sum_costs = the sum over all
+ *                ranks (`costs.sum()`).  Collective when comm is given.
+ *   init_sample  :406-410  the rows kept by `rand.nextDouble() < 2.0 * c * k / sumCosts` with
+ *                rand = XORShiftRandom(seed ^ (step << 16) ^ partitionIndex), one draw per row in row order;
+ *                part_rows[0..nparts] are the row offsets of the Spark partitions inside this table (part_rows[0] = 0,
+ *                part_rows[nparts] = rows), part_index0 the Spark index of the first.  Up to cap row numbers are
+ *                written to rows_out in ascending order, *count_out is the number kept (it may exceed cap).
+ * xorshift_next_int / next_double: Spark's XORShiftRandom(seed).nextInt() and the (skip + 1)-th nextDouble(), for the
+ * caller's own seed derivation (`new XORShiftRandom(this.seed).nextInt()`, :377) and for tests.  XORShiftRandom is
+ * restated from Spark's published source (it is not in the reference tree, nor are vectors for it): unpinned. */
+int kmb200_init_costs(kmb200_table *table, kmb200_comm *comm, const double *new_centers, int32_t m, int32_t d,
+                      int32_t first_step, double *sum_costs);
+int kmb200_init_sample(kmb200_table *table, int32_t seed, int32_t step, int32_t k, double sum_costs,
+                       const int64_t *part_rows, int32_t nparts, int32_t part_index0, int64_t *rows_out, int64_t cap,
+                       int64_t *count_out);
+int32_t kmb200_xorshift_next_int(int64_t seed);
+double kmb200_xorshift_next_double(int64_t seed, int32_t skip);
+
 /* Diagnostics (no reference counterpart): copies `bytes` bytes, starting `offset` bytes in, of one of the device
  * arrays the last fit / assign on this table left behind ("labels", "flag_list", "flag_count", "cand_list",
  * "labels_c", "cand1_list", "labels_c1", "xc", "xc1") to host memory.  Used by tools/repro_check.py. */

@@ -61,6 +61,11 @@ SIGNATURES = {
     "kmb200_set_option": (C.c_int, [C.c_char_p, C.c_double]),
     "kmb200_cluster_sizes_noalloc": (C.c_int, [_P, C.c_int64, C.c_int32, _P, _P]),
     "kmb200_debug_scores": (C.c_int, [_P, _P, C.c_int32, C.c_int32, _P, C.POINTER(C.c_int32)]),
+    "kmb200_init_costs": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_double)]),
+    "kmb200_init_sample": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_double, _P, C.c_int32, C.c_int32, _P, C.c_int64,
+                                    C.POINTER(C.c_int64)]),
+    "kmb200_xorshift_next_int": (C.c_int32, [C.c_int64]),
+    "kmb200_xorshift_next_double": (C.c_double, [C.c_int64, C.c_int32]),
     "kmb200_debug_dump": (C.c_int, [_P, C.c_char_p, C.c_size_t, _P, C.c_size_t]),
     "kmb200_last_error": (C.c_char_p, []),
     "kmb200_version": (C.c_char_p, []),

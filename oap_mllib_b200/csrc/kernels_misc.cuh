@@ -908,6 +908,35 @@ __global__ void gather_list_kernel(const float *__restrict__ X, const int32_t *_
     }
 }
 
+// ------------------------------------------------------------------ k-means|| initialisation passes
+// cost[i] = min(cost[i], dist[i]) (first: cost[i] = dist[i]); part[block] = sum of the block's new costs in a fixed order.
+__global__ void init_min_kernel(double *__restrict__ cost, const double *__restrict__ dist, int64_t n, int first,
+                                double *__restrict__ part) {
+    __shared__ double sh[256];
+    const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+    const int64_t r0 = blockIdx.x * per, r1 = min(n, r0 + per);
+    double s = 0.0;
+    for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
+        const double c = first ? dist[r] : fmin(cost[r], dist[r]);
+        cost[r] = c;
+        s += c;
+    }
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) part[blockIdx.x] = sh[0];
+}
+__global__ void sum_parts_kernel(const double *__restrict__ part, int nparts, double *__restrict__ out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        double s = 0.0;
+        for (int i = 0; i < nparts; ++i) s += part[i];
+        out[0] = s;
+    }
+}
+
 // ------------------------------------------------------------------ cluster sizes (kmb200_assign)
 __global__ void counts_to_i64_kernel(const int32_t *__restrict__ counts, int k, unsigned long long *out) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;

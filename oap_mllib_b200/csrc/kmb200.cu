@@ -243,6 +243,8 @@ struct kmb200_table {
     float *xabs = nullptr;   // [1] max |x_ij| over everything ever appended (scale of the FP16 split)
     void *stage = nullptr;
     size_t stage_bytes = 0;
+    double *init_cost = nullptr;   // [rows] k-means|| initialisation: cost of every row to the nearest centre chosen so far
+    double *init_tmp = nullptr;    // [rows + 1024] scratch of those passes
     cudaStream_t stream = nullptr;
     int num_sms = 0;
     Workspace ws;
@@ -388,6 +390,8 @@ extern "C" int kmb200_table_free(kmb200_table *t) {
     cudaStreamSynchronize(t->stream);
     ws_free(t->ws);
     if (t->stage) cudaFree(t->stage);
+    if (t->init_cost) cudaFree(t->init_cost);
+    if (t->init_tmp) cudaFree(t->init_tmp);
     cudaFree(t->X);
     cudaFree(t->xnorm);
     cudaFree(t->xabs);
@@ -578,6 +582,9 @@ extern "C" int kmb200_table_truncate(kmb200_table *t, int64_t rows) {
     if (rows == t->rows) return 0;
     CU_TRY(cudaSetDevice(t->device));
     ws_free(t->ws);   // tensor maps and per-row buffers depend on the row count
+    if (t->init_cost) cudaFree(t->init_cost);
+    if (t->init_tmp) cudaFree(t->init_tmp);
+    t->init_cost = t->init_tmp = nullptr;
     t->rows = rows;
     return 0;
 }
@@ -1839,6 +1846,151 @@ extern "C" int kmb200_assign(kmb200_table *t, kmb200_comm *comm, const double *c
     cudaEventElapsedTime(&g_prof.allreduce_ms, ev[4], ev[5]);
     cudaEventElapsedTime(&g_prof.total_ms, ev[0], ev[5]);
     return 0;
+}
+
+// ------------------------------------------------------------------------------------ k-means|| initialisation (f3)
+// Spark's java.util.Random with XORShiftRandom's next(bits) (org.apache.spark.util.random.XORShiftRandom: the seed goes
+// through two MurmurHash3.bytesHash rounds of its big-endian bytes, then x ^= x << 21; x ^= x >>> 35; x ^= x << 4).
+// Restated from the published Spark source; the reference tree does not hold that file or test vectors for it.
+namespace {
+inline uint32_t rotl32(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+uint32_t murmur3_bytes_hash(const uint8_t *data, int len, uint32_t seed) {   // scala.util.hashing.MurmurHash3.bytesHash
+    uint32_t h = seed;
+    int i = 0, left = len;
+    auto mix_last = [](uint32_t hash, uint32_t k) { k *= 0xcc9e2d51u; k = rotl32(k, 15); k *= 0x1b873593u; return hash ^ k; };
+    while (left >= 4) {
+        const uint32_t k = data[i] | (data[i + 1] << 8) | (data[i + 2] << 16) | ((uint32_t)data[i + 3] << 24);
+        h = mix_last(h, k);
+        h = rotl32(h, 13);
+        h = h * 5 + 0xe6546b64u;
+        i += 4;
+        left -= 4;
+    }
+    uint32_t k = 0;
+    if (left == 3) k ^= data[i + 2] << 16;
+    if (left >= 2) k ^= data[i + 1] << 8;
+    if (left >= 1) { k ^= data[i]; h = mix_last(h, k); }
+    h ^= (uint32_t)len;
+    h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+    return h;
+}
+struct XorShiftRandom {
+    uint64_t seed;
+    explicit XorShiftRandom(int64_t init) {
+        uint8_t bytes[8];
+        for (int i = 0; i < 8; ++i) bytes[i] = (uint8_t)((uint64_t)init >> (56 - 8 * i));   // ByteBuffer.putLong: big-endian
+        const uint32_t low = murmur3_bytes_hash(bytes, 8, 0x3c074a61u);   // MurmurHash3.arraySeed
+        const uint32_t high = murmur3_bytes_hash(bytes, 8, low);
+        seed = ((uint64_t)high << 32) | low;
+    }
+    int32_t next(int bits) {
+        uint64_t x = seed ^ (seed << 21);
+        x ^= x >> 35;
+        x ^= x << 4;
+        seed = x;
+        return (int32_t)(x & ((1ull << bits) - 1));
+    }
+    int32_t next_int() { return next(32); }
+    double next_double() { return (double)(((int64_t)next(26) << 27) + next(27)) * 0x1.0p-53; }   // java.util.Random.nextDouble
+};
+}  // namespace
+
+extern "C" int32_t kmb200_xorshift_next_int(int64_t seed) { return XorShiftRandom(seed).next_int(); }
+extern "C" double kmb200_xorshift_next_double(int64_t seed, int32_t skip) {
+    XorShiftRandom r(seed);
+    for (int i = 0; i < skip; ++i) r.next_double();
+    return r.next_double();
+}
+
+// One distance pass of initKMeansParallel (spark-3.1.1/mllib/clustering/KMeans.scala:395-401): cost_i = min(cost_i,
+// min_j ||x_i - c_j||^2) over the m centres added in the last step, and the sum of the new costs over all ranks.  The
+// nearest of the m centres comes from the assign path (FP64-faithful labels), the distance to it is FP64 direct-form.
+extern "C" int kmb200_init_costs(kmb200_table *t, kmb200_comm *comm, const double *new_centers, int32_t m, int32_t d,
+                                 int32_t first_step, double *sum_costs) {
+    KM_TRY(check_fit_args(t, new_centers, m, d));
+    if (!sum_costs) return fail(KMB200_ERR_ARG, "init_costs: null output");
+    if (comm && comm->world > 1) KM_TRY(nccl_load());
+    DeviceLock device_lock(t->device);
+    CU_TRY(cudaSetDevice(t->device));
+    KM_TRY(require_device());
+    prof_reset();
+    if (!t->init_cost) {
+        CU_TRY(cudaMalloc(&t->init_cost, (size_t)t->rows * sizeof(double)));
+        CU_TRY(cudaMalloc(&t->init_tmp, ((size_t)t->rows + 1024 + 8) * sizeof(double)));
+        first_step = 1;
+    }
+    KM_TRY(ws_prepare(t, m));
+    Workspace &w = t->ws;
+    cudaStream_t st = t->stream;
+    KM_TRY(upload_centers(t, new_centers, m, d));
+    w.two_level_off = false;
+    w.cascade_off = false;
+    KM_TRY(launch_split(t));
+    if (fused_applies(t)) {
+        KM_TRY(launch_fused(t));
+    } else {
+        KM_TRY(launch_assign(t));
+        KM_TRY(launch_recheck(t));
+    }
+    rowdist_kernel<<<t->num_sms * 8, 256, 0, st>>>(t->X, w.cent, w.labels, t->rows, t->ld, t->init_tmp);
+    KM_TRY(post_launch(__LINE__));
+    const int blocks = (int)std::min<int64_t>(1024, (t->rows + 255) / 256);
+    double *part = t->init_tmp + t->rows, *total = part + 1024;
+    init_min_kernel<<<blocks, 256, 0, st>>>(t->init_cost, t->init_tmp, t->rows, first_step != 0, part);
+    KM_TRY(post_launch(__LINE__));
+    sum_parts_kernel<<<1, 32, 0, st>>>(part, blocks, total);
+    KM_TRY(post_launch(__LINE__));
+    g_prof.kernel_launches += 3;
+    if (comm && comm->world > 1) {
+        const ncclResult_t r = g_nccl.AllReduce(total, total, 1, ncclDouble, ncclSum, comm->comm, st);
+        if (r != ncclSuccess) {
+            comm->broken = true;
+            return fail(KMB200_ERR_COMM, "ncclAllReduce failed: %s", g_nccl.GetErrorString(r));
+        }
+    }
+    CU_TRY(cudaMemcpyAsync(sum_costs, total, sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// The sampling step of initKMeansParallel (KMeans.scala:406-410): partition p of this table (rows part_rows[p] ..
+// part_rows[p + 1], Spark partition index part_index0 + p) draws one nextDouble per row, in row order, from
+// XORShiftRandom(seed ^ (step << 16) ^ index), and keeps the rows with u < 2.0 * cost * k / sumCosts.  The costs come
+// back from the device in pinned chunks; the generator is sequential by definition and runs on the host.
+extern "C" int kmb200_init_sample(kmb200_table *t, int32_t seed, int32_t step, int32_t k, double sum_costs,
+                                  const int64_t *part_rows, int32_t nparts, int32_t part_index0, int64_t *rows_out,
+                                  int64_t cap, int64_t *count_out) {
+    if (!t || !part_rows || !count_out || nparts < 1 || (cap > 0 && !rows_out))
+        return fail(KMB200_ERR_ARG, "init_sample: bad argument");
+    if (!t->init_cost) return fail(KMB200_ERR_ARG, "init_sample: kmb200_init_costs has not run on this table");
+    if (part_rows[0] != 0 || part_rows[nparts] != t->rows)
+        return fail(KMB200_ERR_ARG, "init_sample: the partitions must cover the table's rows");
+    DeviceLock device_lock(t->device);
+    CU_TRY(cudaSetDevice(t->device));
+    const int64_t chunk = 1 << 22;
+    double *host = nullptr;
+    CU_TRY(cudaMallocHost(reinterpret_cast<void **>(&host), (size_t)chunk * sizeof(double)));
+    int64_t count = 0;
+    int rc = 0;
+    for (int p = 0; p < nparts && rc == 0; ++p) {
+        if (part_rows[p + 1] < part_rows[p]) { rc = fail(KMB200_ERR_ARG, "init_sample: partition offsets decrease"); break; }
+        XorShiftRandom rand((int64_t)(seed ^ (step << 16) ^ (part_index0 + p)));   // Int arithmetic, widened like Scala does
+        for (int64_t r0 = part_rows[p]; r0 < part_rows[p + 1]; r0 += chunk) {
+            const int64_t h = std::min(chunk, part_rows[p + 1] - r0);
+            cudaError_t e = cudaMemcpyAsync(host, t->init_cost + r0, (size_t)h * sizeof(double), cudaMemcpyDeviceToHost, t->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(t->stream);
+            if (e != cudaSuccess) { rc = fail(KMB200_ERR_DEVICE, "init_sample: %s", cudaGetErrorString(e)); break; }
+            for (int64_t i = 0; i < h; ++i) {
+                if (rand.next_double() < 2.0 * host[i] * k / sum_costs) {
+                    if (count < cap) rows_out[count] = r0 + i;
+                    ++count;
+                }
+            }
+        }
+    }
+    cudaFreeHost(host);
+    *count_out = count;
+    return rc;
 }
 
 // Test hook: the raw tensor-core scores ||c_j||^2 - 2 x.c_j (FP32) of every row against every padded

@@ -347,8 +347,8 @@ class KMeansModel:
 
 class KMeans:
     """Estimator with the reference's parameter surface.  ``fit`` = KMeans.fit -> trainWithDAL
-    (KMeans.scala:330-439): initial centres on the host (Spark does this in the JVM and it stays
-    out of the accelerated path), Lloyd iterations in libkmeans_b200.so, summary pass on the GPU."""
+    (KMeans.scala:330-439): initial centres with their row passes on the GPU (init.py), Lloyd iterations
+    in libkmeans_b200.so, summary pass on the GPU."""
 
     def __init__(self, k: int = 2, maxIter: int = 20, tol: float = 1e-4, initMode: str = "k-means||",
                  initSteps: int = 2, seed: int = 1, distanceMeasure: str = "euclidean"):
@@ -377,42 +377,14 @@ class KMeans:
 
     def setWeightCol(self, v): self.weightCol = v; return self
 
-    def _init_centers(self, X: np.ndarray) -> np.ndarray:
-        rng = np.random.default_rng(self.seed)
-        n = X.shape[0]
+    def _init_centers(self, table: Table) -> np.ndarray:
+        """Initial centres (KMeans.scala:388-408 -> mllib initRandom / initKMeansParallel): every pass over the rows
+        runs on the GPU (oap_mllib_b200/init.py), the driver-side logic on the host."""
+        from . import init as _init
         if self.initMode == "random":
-            idx = rng.choice(n, size=min(self.k, n), replace=False)
-            return np.unique(np.asarray(X[idx], dtype=np.float64), axis=0)
-        # k-means|| on the host (mllib/clustering/KMeans.scala:370-432): initSteps oversampling rounds,
-        # then weighted k-means++ over the candidates.  Caller-side logic, as in the reference.
-        Xd = np.asarray(X, dtype=np.float64)
-        cand = Xd[rng.integers(n)][None, :]
-        cost = ((Xd - cand[0]) ** 2).sum(1)
-        for _ in range(self.initSteps):
-            tot = cost.sum()
-            if not tot > 0:
-                break
-            pick = rng.random(n) < np.minimum(1.0, 2.0 * self.k * cost / tot)
-            if pick.any():
-                new = Xd[pick]
-                cand = np.vstack([cand, new])
-                for c in new:
-                    cost = np.minimum(cost, ((Xd - c) ** 2).sum(1))
-        cand = np.unique(cand, axis=0)
-        if cand.shape[0] <= self.k:
-            return cand
-        d2 = ((Xd[:, None, :] - cand[None, :, :]) ** 2).sum(2) if n * cand.shape[0] * X.shape[1] < 5e7 else None
-        owner = d2.argmin(1) if d2 is not None else np.array([((cand - x) ** 2).sum(1).argmin() for x in Xd])
-        w = np.bincount(owner, minlength=cand.shape[0]).astype(np.float64)
-        centers = [cand[rng.choice(cand.shape[0], p=w / w.sum())]]
-        dist = ((cand - centers[0]) ** 2).sum(1)
-        while len(centers) < self.k:
-            p = w * dist
-            if not p.sum() > 0:
-                break
-            centers.append(cand[rng.choice(cand.shape[0], p=p / p.sum())])
-            dist = np.minimum(dist, ((cand - centers[-1]) ** 2).sum(1))
-        return np.unique(np.array(centers), axis=0)
+            return _init.init_random(table, self.k, self.seed)
+        centers, _ = _init.init_kmeans_parallel(table, self.k, self.initSteps, self.seed)
+        return centers
 
     def fit(self, X, initialCenters=None) -> KMeansModel:
         if self.distanceMeasure != "euclidean" or self.weightCol is not None:
@@ -422,9 +394,9 @@ class KMeans:
         if not OneDAL.cCheckPlatformCompatibility():
             raise Kmb200Error(-2, "no sm_100 GPU: the accelerated path is unavailable and there is no CPU fallback")
         X = np.asarray(X)
-        centers = np.asarray(initialCenters, dtype=np.float64) if initialCenters is not None else self._init_centers(X)
         table = OneDAL.vectorsToMergedNumericTables(X)
         try:
+            centers = np.asarray(initialCenters, dtype=np.float64) if initialCenters is not None else self._init_centers(table)
             impl = KMeansDALImpl(self.k, self.maxIter, self.tol, self.distanceMeasure, centers, 1, 1)
             parent = impl.train(table)
             model = KMeansModel(parent.clusterCenters, parent.trainingCost, parent.numIter)

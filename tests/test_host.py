@@ -83,16 +83,6 @@ def test_estimator_parameter_surface():
     assert (km.k, km.maxIter, km.tol, km.seed, km.initMode, km.initSteps) == (9, 33, 1e-3, 7, "random", 3)
 
 
-def test_init_centers_are_rows_and_deduplicated():
-    from oap_mllib_b200 import KMeans
-    X = np.array([[float(i % 5)] * 3 for i in range(1, 51)])
-    for mode in ("random", "k-means||"):
-        c = KMeans(k=5, initMode=mode, seed=1)._init_centers(X)
-        assert 1 <= c.shape[0] <= 5 and c.shape[1] == 3
-        assert len(np.unique(c, axis=0)) == c.shape[0]
-        assert all(any((r == x).all() for x in X) for r in c)
-
-
 def test_dal_impl_rejects_non_euclidean():
     from oap_mllib_b200 import KMeansDALImpl
     with pytest.raises(ValueError):
