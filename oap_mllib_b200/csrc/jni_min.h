@@ -44,6 +44,7 @@ enum JniSlot {
     kJniGetArrayLength = 171,
     kJniGetObjectArrayElement = 173,
     kJniNewByteArray = 176,
+    kJniNewLongArray = 180,
     kJniNewDoubleArray = 182,
     kJniGetByteArrayRegion = 200,
     kJniSetByteArrayRegion = 208,

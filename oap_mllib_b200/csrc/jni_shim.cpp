@@ -420,4 +420,50 @@ JNIEXPORT jdouble JNICALL Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMe
     return cost;
 }
 
+// ---- initialisation passes (no counterpart in the reference's natives: its initialisation
+// runs as Spark jobs on the JVM, mllib/clustering/KMeans.scala:370-432).  The Scala loop of initKMeansParallel stays;
+// its three row passes call these instead of `data.zip(costs).map`, `mapPartitionsWithIndex { filter }` and `countByValue`.
+JNIEXPORT jdouble JNICALL Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansInitCosts(
+    JNIEnvPtr env, jobject, jlong pNumTabData, jlong pNewCenters, jboolean firstStep) {
+    kmb200_table *table = reinterpret_cast<kmb200_table *>(pNumTabData);
+    Centers *cen = reinterpret_cast<Centers *>(pNewCenters);
+    if (!table || !cen) {
+        throw_runtime(env, "null table or centres handle");
+        return 0.0;
+    }
+    double sum = 0.0;
+    if (kmb200_init_costs(table, g_comm, cen->v.data(), cen->k, cen->d, firstStep ? 1 : 0, &sum) != 0) throw_runtime(env, kmb200_last_error());
+    return sum;
+}
+
+// partRows: long[numPartitions + 1] row offsets of this executor's Spark partitions inside the table; returns the kept
+// rows (table row numbers, ascending)
+JNIEXPORT jlongArray JNICALL Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansInitSample(
+    JNIEnvPtr env, jobject, jlong pNumTabData, jint seed, jint step, jint k, jdouble sumCosts, jlongArray partRows,
+    jint numPartitions, jint partIndex0) {
+    kmb200_table *table = reinterpret_cast<kmb200_table *>(pNumTabData);
+    if (!table || numPartitions < 1) {
+        throw_runtime(env, "cKMeansInitSample: bad argument");
+        return nullptr;
+    }
+    std::vector<int64_t> parts((size_t)numPartitions + 1);
+    if (!copy_from_array<int64_t>(env, partRows, 0, parts.size(), parts.data())) return nullptr;
+    std::vector<int64_t> rows((size_t)std::max(16 * k, 1024));
+    int64_t count = 0;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        if (kmb200_init_sample(table, seed, step, k, sumCosts, parts.data(), numPartitions, partIndex0, rows.data(),
+                               (int64_t)rows.size(), &count) != 0) {
+            throw_runtime(env, kmb200_last_error());
+            return nullptr;
+        }
+        if (count <= (int64_t)rows.size()) break;
+        rows.resize((size_t)count);
+    }
+    auto mk = slot<jlongArray (*)(JNIEnvPtr, jsize)>(env, kJniNewLongArray);
+    auto setl = slot<void (*)(JNIEnvPtr, jlongArray, jsize, jsize, const jlong *)>(env, kJniSetLongArrayRegion);
+    jlongArray arr = mk(env, (jsize)count);
+    if (arr && count > 0) setl(env, arr, 0, (jsize)count, reinterpret_cast<const jlong *>(rows.data()));
+    return arr;
+}
+
 }  // extern "C"

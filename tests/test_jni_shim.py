@@ -9,8 +9,8 @@ import pytest
 
 SLOTS = dict(FindClass=6, ThrowNew=14, GetObjectClass=31, GetFieldID=94, SetIntField=109, SetLongField=110,
              SetDoubleField=112, GetStringUTFChars=169, ReleaseStringUTFChars=170, GetArrayLength=171, GetObjectArrayElement=173,
-             NewByteArray=176, NewDoubleArray=182, GetByteArrayRegion=200, SetByteArrayRegion=208,
-             SetDoubleArrayRegion=214, GetPrimitiveArrayCritical=222, ReleasePrimitiveArrayCritical=223)
+             NewByteArray=176, NewLongArray=180, NewDoubleArray=182, GetByteArrayRegion=200, SetByteArrayRegion=208,
+             SetIntArrayRegion=211, SetLongArrayRegion=212, SetDoubleArrayRegion=214, GetPrimitiveArrayCritical=222, ReleasePrimitiveArrayCritical=223)
 P = C.c_void_p
 
 
@@ -36,6 +36,11 @@ class FakeJvm:
         put("ReleaseStringUTFChars", None, [P, P, P], lambda env, s, c: None)
         put("NewByteArray", P, [P, C.c_int32], lambda env, n: self.new(np.zeros(n, np.int8)))
         put("NewDoubleArray", P, [P, C.c_int32], lambda env, n: self.new(np.zeros(n, np.float64)))
+        put("NewLongArray", P, [P, C.c_int32], lambda env, n: self.new(np.zeros(n, np.int64)))
+        put("SetIntArrayRegion", None, [P, P, C.c_int32, C.c_int32, P],
+            lambda env, a, s, n, buf: C.memmove(self.objs[a].ctypes.data + 4 * s, buf, 4 * n) and None)
+        put("SetLongArrayRegion", None, [P, P, C.c_int32, C.c_int32, P],
+            lambda env, a, s, n, buf: C.memmove(self.objs[a].ctypes.data + 8 * s, buf, 8 * n) and None)
         put("GetByteArrayRegion", None, [P, P, C.c_int32, C.c_int32, P],
             lambda env, a, s, n, buf: C.memmove(buf, self.objs[a].ctypes.data + s, n) and None)
         put("SetByteArrayRegion", None, [P, P, C.c_int32, C.c_int32, P],
@@ -189,3 +194,138 @@ def test_jni_columnar_sparse_and_truncate(jni):
     truncate(vm.env, None, table, 10 ** 9)                      # beyond the capacity: a Java exception, not a crash
     assert vm.thrown and "truncate" in vm.thrown[-1]
     free_tab(vm.env, None, table)
+
+
+@pytest.mark.gpu
+def test_jni_summary_and_init_natives(jni):
+    """cKMeansDALAssign (the summary pass of KMeans.fit on the table that is still resident), cKMeansInitCosts and
+    cKMeansInitSample (the row passes of initKMeansParallel) against the oracle."""
+    from oracle import kmeans_oracle as ko
+    from oracle import spark_init as si
+    h, vm = jni
+    n, d, k = 8000, 12, 7
+    X, _, _ = ko.gaussian_blobs(n, d, k, seed=5)
+    X64 = X.astype(np.float64)
+    new_table = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cNewTable", C.c_int64, [P, P, C.c_int64, C.c_int32])
+    set_batch = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cSetDoubleBatch", None,
+                   [P, P, C.c_int64, C.c_int32, P, C.c_int32, C.c_int32])
+    new_cent = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cNewCenters", C.c_int64, [P, P, C.c_int32, C.c_int32])
+    set_val = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_setNumericTableValue", None,
+                 [P, P, C.c_int64, C.c_int32, C.c_int32, C.c_double])
+    free_cent = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cFreeCenters", None, [P, P, C.c_int64])
+    free_tab = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cFreeDataMemory", None, [P, P, C.c_int64])
+    assign = fn(h, "Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansDALAssign", C.c_double, [P, P, C.c_int64, C.c_int64, P, P])
+    init_costs = fn(h, "Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansInitCosts", C.c_double, [P, P, C.c_int64, C.c_int64, C.c_uint8])
+    init_sample = fn(h, "Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansInitSample", P,
+                     [P, P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_double, P, C.c_int32, C.c_int32])
+
+    def centres_handle(cen):
+        hd = new_cent(vm.env, None, cen.shape[0], d)
+        for i in range(cen.shape[0]):
+            for j in range(d):
+                set_val(vm.env, None, hd, i, j, float(cen[i, j]))
+        return hd
+
+    table = new_table(vm.env, None, n, d)
+    set_batch(vm.env, None, table, 0, vm.new(np.ascontiguousarray(X64)), n, d)
+    # summary pass
+    cen = ko.row_init_centers(X, k)
+    hc = centres_handle(cen)
+    pred, sizes = vm.new(np.zeros(n, np.int32)), vm.new(np.zeros(k, np.int64))
+    cost = assign(vm.env, None, table, hc, pred, sizes)
+    assert not vm.thrown, vm.thrown
+    want_labels, best, _ = ko.assign(X64, cen)
+    assert np.array_equal(vm.objs[pred], want_labels)
+    assert np.array_equal(vm.objs[sizes], np.bincount(want_labels, minlength=k))
+    assert abs(cost - best.sum()) <= 1e-5 * best.sum()
+    free_cent(vm.env, None, hc)
+    # one k-means|| step: costs to the first centre, then the sampling filter over two partitions
+    first = X64[si.first_center_row(123, n)][None, :]
+    hf = centres_handle(first)
+    total = init_costs(vm.env, None, table, hf, 1)
+    want_costs = ((X64 - first[0]) ** 2).sum(1)
+    assert abs(total - want_costs.sum()) <= 1e-12 * want_costs.sum()
+    parts = np.array([0, 3000, n], np.int64)
+    got = init_sample(vm.env, None, table, 123, 0, k, total, vm.new(parts), 2, 4)
+    want = []
+    for p in range(2):
+        rand = si.XORShiftRandom(si._to_i32(123 ^ (0 << 16) ^ (4 + p)))
+        for r in range(parts[p], parts[p + 1]):
+            if rand.next_double() < 2.0 * want_costs[r] * k / total:
+                want.append(r)
+    assert not vm.thrown, vm.thrown
+    assert vm.objs[got].tolist() == want and len(want) > 0
+    free_cent(vm.env, None, hf)
+    free_tab(vm.env, None, table)
+
+
+def _jni_rank(rank, world, lib_path, q_id, q_out):
+    """One executor process: device, table, rendezvous through the JNI natives, collective compute."""
+    from oracle import kmeans_oracle as ko
+    h, vm = C.CDLL(lib_path), FakeJvm()
+    n, d, k = 40000, 32, 20
+    X, _, _ = ko.gaussian_blobs(n, d, k, seed=77)
+    init = ko.row_init_centers(X, k)
+    r0, r1 = (n * rank) // world, (n * (rank + 1)) // world
+    set_dev = fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_c_1setDevice", C.c_int32, [P, P, C.c_int32])
+    get_id = fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_c_1getUniqueId", P, [P, P])
+    c_init = fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_c_1init", C.c_int32, [P, P, C.c_int32, C.c_int32, P, P])
+    cleanup = fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_c_1cleanup", None, [P, P])
+    is_root = fn(h, "Java_org_apache_spark_ml_util_OneCCL_00024_isRoot", C.c_uint8, [P, P])
+    new_table = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cNewTable", C.c_int64, [P, P, C.c_int64, C.c_int32])
+    set_batch = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cSetDoubleBatch", None,
+                   [P, P, C.c_int64, C.c_int32, P, C.c_int32, C.c_int32])
+    new_cent = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cNewCenters", C.c_int64, [P, P, C.c_int32, C.c_int32])
+    set_val = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_setNumericTableValue", None,
+                 [P, P, C.c_int64, C.c_int32, C.c_int32, C.c_double])
+    get_cent = fn(h, "Java_org_apache_spark_ml_util_OneDAL_00024_cGetCenters", P, [P, P, C.c_int64])
+    compute = fn(h, "Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansDALComputeWithInitCenters", C.c_int64,
+                 [P, P, C.c_int64, C.c_int64, C.c_int32, C.c_double, C.c_int32, C.c_int32, C.c_int32, P])
+    assert set_dev(vm.env, None, rank) == rank
+    if rank == 0:
+        ident = bytes(vm.objs[get_id(vm.env, None)].view(np.uint8))
+        for _ in range(world - 1):
+            q_id.put(ident)
+    else:
+        ident = q_id.get(timeout=120)
+    table = new_table(vm.env, None, r1 - r0, d)
+    set_batch(vm.env, None, table, 0, vm.new(np.ascontiguousarray(X[r0:r1], np.float64)), r1 - r0, d)
+    cent = new_cent(vm.env, None, k, d)
+    for i in range(k):
+        for j in range(d):
+            set_val(vm.env, None, cent, i, j, float(init[i, j]))
+    param, result = vm.new(object()), vm.new(object())
+    assert c_init(vm.env, None, world, rank, vm.new(np.frombuffer(ident, np.int8).copy()), param) == 1
+    assert vm.fields[param] == {"commSize": world, "rankId": rank}
+    out = compute(vm.env, None, table, cent, k, 1e-4, 10, world, 1, result)
+    ok = not vm.thrown
+    if rank == 0:
+        assert is_root(vm.env, None) == 1 and out != 0
+        got = vm.objs[get_cent(vm.env, None, out)].reshape(k, d)
+        want_c, want_cost, want_it = ko.lloyd(X.astype(np.float64), init, 1e-4, 10, n_ranks=world)
+        ok = ok and vm.fields[result]["iterationNum"] == want_it and abs(vm.fields[result]["totalCost"] - want_cost) <= 1e-5 * want_cost \
+            and np.allclose(got, want_c, rtol=1e-5, atol=1e-5)
+    else:
+        ok = ok and out == 0
+    cleanup(vm.env, None)
+    q_out.put((rank, bool(ok), vm.thrown))
+
+
+@pytest.mark.gpu
+def test_jni_two_executors_rendezvous_and_fit(built_lib):
+    """Two executor processes, one GPU each: c_setDevice, c_getUniqueId on rank 0 (the bytes travel to rank 1 the way
+    the Spark closure would carry them), c_init(size = 2), the collective compute native, c_cleanup."""
+    import multiprocessing as mp
+
+    import oap_mllib_b200 as m
+    if m.lib().kmb200_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ctx = mp.get_context("spawn")
+    q_id, q_out = ctx.Queue(), ctx.Queue()
+    procs = [ctx.Process(target=_jni_rank, args=(r, 2, built_lib, q_id, q_out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q_out.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok, _ in res), res
