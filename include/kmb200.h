@@ -174,7 +174,8 @@ int kmb200_get_profile(kmb200_profile *out);
  * variant gives the same fit, tests/test_gpu_parity.py): "h16" (1 = FP16-split CTA-pair kernel for
  * d <= 256), "two_level" (1 = fast pass + full bookkeeping over the near-tie rows for tables of
  * >= 2^18 rows, 2 = always, 0 = never), "cand_cap" (rows of the near-tie copy, 0 = rows/16),
- * "cascade" (1 = coarse one-product pass first, wherever the two-level scheme runs), "cand1_frac"
+ * "cascade" (1 = coarse one-product pass first, wherever the two-level scheme runs and a row tile carries enough tensor
+ * work for it -- at least four 64-value units over all its centroid tiles; 2 = regardless of that; 0 = never), "cand1_frac"
  * (rows of the coarse pass's copy as a fraction of the table, default 0.3), "stage_mb" (device
  * staging buffer of the columnar / sparse / FP64 uploads, default 256), "dbg_products" (1 = the
  * score dump of kmb200_debug_scores shows the coarse pass),

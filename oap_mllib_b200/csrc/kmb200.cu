@@ -1157,7 +1157,11 @@ static int launch_assign_h16(kmb200_table *t) {
     H16Src table = {&w.tm_x, t->xnorm, w.labels, t->rows, nullptr, w.flag_count + 2, 0, true};
     if (w.dbg_scores) return g_dbg_products == 1 ? launch_assign_h16_mode<1, 1>(t, table) : launch_assign_h16_mode<1, 3>(t, table);
     const bool two_level = two_level_prepare(t);
-    if (two_level && cascade_prepare(t)) {
+    // The coarse pass pays when a row tile carries real tensor work.  With one centroid tile and one or two chunks (C2:
+    // d = 64, k = 100) a pass costs the same ~3000 cycles of hand-offs per row tile whatever it multiplies, so a second
+    // pass over 13 % of the rows only adds to the first: such shapes go straight to the three-product fast pass.
+    const bool worth = (w.kpad / w.bn) * ((t->ld / kChunkK + 1) / 2) >= 4 || g_cascade == 2;
+    if (two_level && worth && cascade_prepare(t)) {
         H16Src coarse = table;
         coarse.cand_list = w.cand1_list;
         coarse.cand_count = w.flag_count + 3;
@@ -2147,7 +2151,7 @@ extern "C" int kmb200_set_option(const char *name, double value) {
     } else if (!strcmp(name, "dbg_products")) {
         g_dbg_products = value == 1 ? 1 : 3;
     } else if (!strcmp(name, "cascade")) {
-        g_cascade = value != 0;
+        g_cascade = value == 2 ? 2 : value != 0;   // 2 = also where the shape makes it unprofitable (tests)
     } else if (!strcmp(name, "cand1_frac")) {
         if (!(value > 0.0 && value <= 1.0)) return fail(KMB200_ERR_ARG, "cand1_frac must be in (0, 1]");
         g_cand1_frac = value;

@@ -277,9 +277,10 @@ def test_force_simt_path_agrees(m):
     {"h16": 0, "bf16_corr": 0},           # CTA pairs, plain 3xTF32
     {"h16": 0, "ss": 0},                  # CTA pairs, BF16 corrections, A operand entirely in TMEM
     {"fused": 0},                         # tensor-core path even where the one-pass small-k kernel applies
-    {"two_level": 2},                     # coarse one-product pass + fast pass + full bookkeeping over the near-tie rows, forced on small tables
+    {"two_level": 2, "cascade": 2},       # coarse one-product pass + fast pass + full bookkeeping over the near-tie rows, forced on small tables and shapes
+    {"two_level": 2},                     # ... the coarse pass only where the shape makes it worth its while
     {"two_level": 2, "cascade": 0},       # ... without the coarse pass
-    {"two_level": 2, "cand1_frac": 0.002},  # ... with a coarse-pass copy that overflows: the fit drops the coarse pass
+    {"two_level": 2, "cascade": 2, "cand1_frac": 0.002},  # ... with a coarse-pass copy that overflows: the fit drops the coarse pass
     {"two_level": 2, "cand_cap": 256},    # ... with a candidate buffer that overflows: falls back to the single pass
     {"two_level": 0},                     # single pass with full bookkeeping
 ])

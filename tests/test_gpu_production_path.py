@@ -79,10 +79,19 @@ def test_headline_geometry_near_duplicate_centres(m):
     fit_labels_profile(m, X, init, max_iter=5)
 
 
-def test_c2_geometry_default_cascade(m):
+@pytest.mark.parametrize("force_cascade", [False, True])
+def test_c2_geometry(m, force_cascade):
+    """d = 64, k = 100 (C2's shape): one centroid tile and two chunks per row tile -- by default the fit skips the coarse
+    pass there (three-product fast pass + near-tie pass); with "cascade" = 2 the coarse pass runs all the same."""
     X, _, _ = ko.gaussian_blobs(300_000, 64, 100, seed=33)
-    prof = fit_labels_profile(m, X, ko.row_init_centers(X, 100), max_iter=8)
-    assert prof["coarse_undecided_rows"] > 0
+    try:
+        if force_cascade:
+            m._lib.check(m.lib().kmb200_set_option(b"cascade", 2.0))
+        prof = fit_labels_profile(m, X, ko.row_init_centers(X, 100), max_iter=8)
+    finally:
+        m._lib.check(m.lib().kmb200_set_option(b"cascade", 1.0))
+    assert prof["assign_variant"] == (1 if force_cascade else 2)
+    assert (prof["coarse_undecided_rows"] > 0) == force_cascade
 
 
 @pytest.mark.parametrize("kind", ["overlapping", "uniform", "integers"])
@@ -103,7 +112,11 @@ def test_hard_data_hand_offs(m, kind):
         n, d, k = 270_000, 16, 48
         X = rng.integers(0, 4, (n, d)).astype(np.float32)
         init = unique_row_init(X, k)
-    prof = fit_labels_profile(m, X, init, max_iter=6)
+    try:
+        m._lib.check(m.lib().kmb200_set_option(b"cascade", 2.0))   # (these shapes would skip the coarse pass by default)
+        prof = fit_labels_profile(m, X, init, max_iter=6)
+    finally:
+        m._lib.check(m.lib().kmb200_set_option(b"cascade", 1.0))
     if kind == "integers":
         assert prof["rechecked_rows"] > n // 16     # far more near-ties than the near-tie copy holds
 
