@@ -13,9 +13,13 @@ Prints ONE JSON line (rank 0).  `value` = iterations/s with the rows already res
 timed on the device (CUDA events on the library's stream, max over ranks).  `e2e` = the same
 metric through the reference-facing call KMeansDALImpl.train(host rows): upload of this rank's
 rows from PINNED host memory + K iterations + read-back of centres/cost, all inside the timed
-region.  `cpu_baseline` / `--impl reference` = the FP64 CPU restatement of the reference's oneDAL
-path (oracle/kmeans_oracle.py, OpenBLAS dgemm on all host cores) on a bounded row sample -- the
-reference's own oneDAL build cannot run in this image.
+region.  `cpu_baseline` / `--impl reference` = the fastest of the CPU stand-ins for the reference's
+oneDAL step (oracle/cpu_baselines.py: scikit-learn's Lloyd in FP64 and FP32, a blocked dgemm +
+fused argmin / segmented-sum loop over a thread pool, the FP64 oracle itself) on all host cores,
+each timed for one iteration on a bounded row sample and extrapolated linearly in N -- the
+reference's own oneDAL build cannot run in this image.  The initial centres are rows
+floor(j N / k) of the WHOLE table, so every GPU count solves the same problem and `final_cost`
+must agree across N.  `--workload C2|C4|C5` runs BASELINE.json's other configurations.
 """
 from __future__ import annotations
 
@@ -291,8 +295,9 @@ def run_ours(args, rank, local_rank, world):
              3: "assign_pair_h16_kernel<BN, 0, 3> (tcgen05 cta_group::2, kind::f16, three products)",
              4: "assign_pair_ss_kernel (tcgen05 cta_group::2, TF32 + BF16 corrections)",
              5: "assign_tc2_kernel (tcgen05, 3xTF32, resident X)", 6: "assign_tc_kernel (tcgen05, 3xTF32, streaming)",
-             7: "recheck_kernel (FP64, CUDA cores)", 8: "assign_h16w_kernel (tcgen05 cta_group::2, kind::f16, d > 256)",
-             9: "fused_assign_accumulate (tcgen05 distances + FP64 accumulation in one read of X)"}
+             7: "recheck_kernel (FP64, CUDA cores)",
+             8: "assign_pair_h16_kernel<BN, 2, 1>, 256 < d <= 512 (coarse pass of the cascade: tcgen05 cta_group::2, kind::f16, one "
+                "product; the undecided rows go through the streaming 3xTF32 kernel, inside assign_phase_ms)"}
     if variant != 0 and acc_ms > main_ms:
         kern, kern_ms = "segment_sums_kernel (per-cluster FP64 sums and cost; second read of X)", acc_ms
     else:
@@ -302,7 +307,7 @@ def run_ours(args, rank, local_rank, world):
         peak_source = f"hbm_gbs of {peaks['source']} MEASURED_PEAKS.json"
     else:
         achieved, unit = flops_per_launch / (kern_ms * 1e-3) / 1e12, "TFLOP/s"
-        if variant == 1:
+        if variant in (1, 8):
             # one FP16 product per score: the ceiling is the dense FP16/BF16 rate itself
             peak, peak_source = peaks["bf16_sustained"], (f"bf16_tflops_sustained of {peaks['source']} MEASURED_PEAKS.json "
                                                           "(FP16 and BF16 MMAs run at the same rate); kernel timed inside a long step")
@@ -323,7 +328,7 @@ def run_ours(args, rank, local_rank, world):
                 "step_frac_of_tf32_proxy_burst": step_tflops_gpu / tf32_burst,
                 "step_gbytes_per_s_per_gpu": step_gbs_gpu,
                 "step_frac_of_hbm": step_gbs_gpu / peaks["hbm_gbs"]}
-    if variant == 1:
+    if variant in (1, 8):
         roofline["coarse_undecided_fraction"] = prof["coarse_undecided_rows"] / args.steps / n_local
     t32 = tf32_measured(achieved)
     if t32:
