@@ -241,6 +241,10 @@ JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cTruncateTable
     if (kmb200_table_truncate(reinterpret_cast<kmb200_table *>(addr), rows) != 0) throw_runtime(env, kmb200_last_error());
 }
 
+JNIEXPORT jlong JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cTableRows(JNIEnvPtr, jobject, jlong addr) {
+    return kmb200_table_rows(reinterpret_cast<kmb200_table *>(addr));
+}
+
 JNIEXPORT void JNICALL Java_org_apache_spark_ml_util_OneDAL_00024_cFreeDataMemory(JNIEnvPtr, jobject, jlong addr) {
     kmb200_table_free(reinterpret_cast<kmb200_table *>(addr));
 }

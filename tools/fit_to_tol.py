@@ -21,11 +21,11 @@ init = np.ascontiguousarray(np.vstack([t.read_rows(int(i), 1) for i in idx]).ast
 out = np.empty((k, d))
 cost, it = C.c_double(), C.c_int32()
 t0 = time.perf_counter()
-_lib.check(m.lib().kmb200_fit(t.handle, None, init.ctypes.data_as(C.c_void_p), k, d, 1e-4, 300,
+_lib.check(m.lib().kmb200_fit(t.handle, None, init.ctypes.data_as(C.c_void_p), k, d, 1e-4, int(os.environ.get("MAXIT", 300)),
                               out.ctypes.data_as(C.c_void_p), C.byref(cost), C.byref(it)))
 wall = time.perf_counter() - t0
 p = _lib.profile()
-print(json.dumps({"workload": f"{rows}x{d} k={k} tol=1e-4 maxIter=300", "iterations": it.value, "cost": cost.value,
+print(json.dumps({"workload": f"{rows}x{d} k={k} tol=1e-4 maxIter=" + os.environ.get("MAXIT", "300"), "iterations": it.value, "cost": cost.value,
                   "wall_s": wall, "device_ms_per_iteration": p["total_ms"] / max(it.value, 1),
                   "rechecked_rows_total": p["rechecked_rows"], "full_rechecks_total": p["full_rechecks"],
                   "empty_cluster_events": p["empty_cluster_events"],
