@@ -2,6 +2,7 @@
 what one of 8 GPUs holds of the headline config), through the C ABI.  Launch order per iteration on the default path:
 coarse one-product pass, gather, three-product fast pass, gather, full-bookkeeping pass, re-check, bucketing, accumulate."""
 import ctypes as C
+import os
 import sys
 
 import numpy as np
@@ -15,6 +16,10 @@ d = int(sys.argv[2]) if len(sys.argv) > 2 else 256
 k = int(sys.argv[3]) if len(sys.argv) > 3 else 1000
 iters = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 _lib.check(m.lib().kmb200_set_device(0))
+for opt in os.environ.get("KMB_OPTIONS", "").split(","):     # e.g. KMB_OPTIONS=fused=2,cascade=0
+    if opt:
+        name, val = opt.split("=")
+        _lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
 centres = np.random.default_rng(42).uniform(-10, 10, (k, d)).astype(np.float32)
 t = m.Table(n, d)
 t.fill_blobs(centres, seed=42)
