@@ -123,7 +123,8 @@ def make_config(args, world):
             "parallelism": f"rows sharded over {world} GPU(s), 1 NCCL all-reduce / iteration",
             "l2": "inputs (rows_per_gpu*d*4 bytes) far larger than the 126 MB L2; no flush needed",
             "init": "rows floor(j*N/k) of the whole table (the same centres for every GPU count)",
-            "tol": "disabled (exactly K iterations)"}
+            "tol": "disabled (exactly K iterations)",
+            "data": f"Gaussian blobs, sigma = 1, k_true = k centres ~ U(-{args.centre_range:g}, {args.centre_range:g})^d"}
 
 
 def cpu_baseline(d, k, rows_full, sample_rows=0, which=None):
@@ -215,7 +216,7 @@ def run_ours(args, rank, local_rank, world):
     row0, row1 = shard_bounds(rows, world)[rank]
     n_local = row1 - row0
     rng = np.random.default_rng(42)
-    centres = rng.uniform(-10, 10, (k, d)).astype(np.float32)
+    centres = rng.uniform(-args.centre_range, args.centre_range, (k, d)).astype(np.float32)
     table = m.Table(n_local, d)
     table.fill_blobs(centres, seed=42, row_offset=row0)
 
@@ -446,6 +447,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override the total row count (debugging)")
+    ap.add_argument("--centre-range", type=float, default=10.0,
+                    help="blob centres ~ U(-R, R)^d with unit noise: 10 = BASELINE's well-separated blobs, 1 = heavy overlap")
     ap.add_argument("--e2e-rows", type=int, default=0)
     ap.add_argument("--cpu-sample-rows", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")

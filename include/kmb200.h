@@ -179,7 +179,7 @@ int kmb200_get_profile(kmb200_profile *out);
  * (rows of the coarse pass's copy as a fraction of the table, default 0.3), "stage_mb" (device
  * staging buffer of the columnar / sparse / FP64 uploads, default 256), "dbg_products" (1 = the
  * score dump of kmb200_debug_scores shows the coarse pass),
- * "ss", "bf16_corr", "cluster", "kernel", "fused", "rb_cap" (older kernels), and the diagnostics
+ * "cluster", "kernel", "fused", "rb_cap" (fallback kernels), and the diagnostics
  * "knockout" / "role_prof" (timing experiments; results are invalid with knockout != 0). */
 int kmb200_set_option(const char *name, double value);
 

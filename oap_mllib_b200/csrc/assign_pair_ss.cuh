@@ -1,5 +1,5 @@
-// CTA-pair assign kernel, "SS" variant (ld <= 256, BN >= 32): the production path for the headline shape.
-// Same result as assign_pair_kernel<BN, true> (TF32 main product + BF16 correction products), but the
+// CTA-pair assign kernel, "SS" variant (ld <= 256, BN >= 32): the fallback of the FP16-split kernel ("h16" = 0).
+// TF32 main product + BF16 correction products; the
 // main product reads its A operand STRAIGHT FROM THE RESIDENT X TILE in shared memory
 // (tcgen05.mma ... kind::tf32 with a shared-memory A descriptor: the tensor core drops the low 13
 // mantissa bits of x itself), so the transform warps only produce the correction operand
@@ -8,10 +8,10 @@
 // buffers of the A operand instead of four: the commit -> transform -> arrive loop crosses the CTA
 // pair twice (~2500 cycles) and with 4 buffers it, not the tensor pipe, set the pace.
 #pragma once
-// (derived from assign_pair.cuh; see the header comment below for what differs)
+// (derived from the round-1 kernel that kept the whole A operand in TMEM, since removed)
 #include <cuda_bf16.h>
 
-#include "assign_pair.cuh"
+#include "assign_tc.cuh"
 
 namespace kmb {
 

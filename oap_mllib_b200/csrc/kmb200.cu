@@ -20,7 +20,6 @@
 #include "../../include/kmb200.h"
 #include "assign_tc.cuh"
 #include "assign_tc2.cuh"
-#include "assign_pair.cuh"
 #include "assign_pair_ss.cuh"
 #include "assign_pair_h16.cuh"
 #include "fused_smallk.cuh"
@@ -79,7 +78,6 @@ static int g_force_simt = 0;
 static int g_knockout = 0;
 static int g_kernel = 2;   // 2 = X-resident / multicast kernel where it applies (ld <= 256), 1 = first-generation kernel
 static int g_fused = 1;    // 1 = one-pass CUDA-core kernel when k*ld is small (HBM-bound regime)
-static int g_ss = 1;       // pair kernel: 1 = main product reads X from shared memory (SS), corrections only in TMEM
 static int g_h16 = 1;      // 1 = FP16-split pair kernel (assign_pair_h16.cuh) where it applies, 0 = TF32 + BF16 corrections
 static int g_two_level = 1;  // FP16-split kernel: 1 = fast bookkeeping over all rows + full bookkeeping over the near-tie rows
                              //   (tables of >= kTwoLevelMinRows rows), 2 = always, 0 = never
@@ -89,7 +87,6 @@ static int g_dbg_products = 3;   // kmb200_debug_scores: 1 = dump the coarse one
 static int g_cascade = 1;    // FP16-split kernel: 1 = coarse one-product pass first (needs the two-level scheme), 0 = off
 static double g_cand1_frac = 0.3;   // rows of the coarse pass's copy, as a fraction of the table ("cand1_frac")
 static int g_rb_cap = 4;   // experiments: cap on the B-ring group slots of the pair kernel
-static int g_corr = 1;     // pair kernel: 1 = BF16 correction MMAs (2 pass-equivalents), 0 = TF32 corrections (3 passes)
 static int g_cluster = 2;  // 2 = CTA pairs (tcgen05 cta_group::2, centroid tiles split across the pair), 1 = single CTAs
 static void env_overrides() {
     static bool done = false;
@@ -97,7 +94,6 @@ static void env_overrides() {
     done = true;
     if (const char *e = getenv("KMB200_KERNEL")) g_kernel = atoi(e) == 1 ? 1 : 2;
     if (const char *e = getenv("KMB200_CLUSTER")) g_cluster = atoi(e) == 1 ? 1 : 2;
-    if (const char *e = getenv("KMB200_BF16_CORR")) g_corr = atoi(e) != 0;
     if (const char *e = getenv("KMB200_H16")) g_h16 = atoi(e) != 0;
 }
 static long long *g_role_prof = nullptr;  // device buffer, allocated by option "role_prof"
@@ -867,20 +863,15 @@ static int launch_assign2_bn(kmb200_table *t) {
     return 0;
 }
 
-template <int BN, int V>   // V: 0 = TF32 corrections (3 passes), 1 = BF16 corrections, A in TMEM, 2 = BF16 corrections, main A from smem
+template <int BN, bool DUMP>   // DUMP: plus the score dump used by kmb200_debug_scores
 static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
-    constexpr bool BF16C = V != 0;   // V == 3: V == 2 plus the score dump used by kmb200_debug_scores
     Workspace &w = t->ws;
-    using Cfg = std::conditional_t<(V >= 2), PairSsCfg<BN>, PairCfg<BN>>;
-    auto kernel = [] {
-        if constexpr (V == 2) return assign_pair_ss_kernel<BN, false>;
-        else if constexpr (V == 3) return assign_pair_ss_kernel<BN, true>;
-        else return assign_pair_kernel<BN, BF16C>;
-    }();
+    using Cfg = PairSsCfg<BN>;
+    auto kernel = assign_pair_ss_kernel<BN, DUMP>;
     static bool attr_set[64] = {false};
     const int kc = t->ld / kChunkK;
     int rb = std::min(Cfg::group_slots(kc), g_rb_cap);
-    if (V >= 2 && rb == 3) rb = 2;   // the SS kernel's completion ring has period 4: 2 or 4 group slots
+    if (rb == 3) rb = 2;   // the kernel's completion ring has period 4: 2 or 4 group slots
     *applicable = rb >= 2;
     if (rb < 2) return 0;
     const int smem = Cfg::smem_bytes(kc, rb);
@@ -902,7 +893,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     p.num_k_chunks = kc;
     p.stages = rb;
     p.passes = 3;
-    p.eps = score_eps(t->ld, BF16C);
+    p.eps = score_eps(t->ld, true);
     p.dbg_scores = w.dbg_scores;
     p.kpad = w.kpad;
     p.knockout = g_knockout;
@@ -910,7 +901,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     const int pairs = std::min((p.num_row_tiles + 1) / 2, t->num_sms / 2);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(pairs * 2));
-    cfg.blockDim = dim3(V >= 2 ? kPairSsThreads : kPairThreads);
+    cfg.blockDim = dim3(kPairSsThreads);
     cfg.dynamicSmemBytes = (size_t)smem;
     cfg.stream = t->stream;
     cudaLaunchAttribute attr[1];
@@ -920,8 +911,7 @@ static int launch_assign_pair_bn(kmb200_table *t, bool *applicable) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    CU_TRY(cudaLaunchKernelEx(&cfg, kernel, w.tm_x, w.tm_bhi_half,
-                              BF16C ? w.tm_bcorr_half : w.tm_blo_half, p));
+    CU_TRY(cudaLaunchKernelEx(&cfg, kernel, w.tm_x, w.tm_bhi_half, w.tm_bcorr_half, p));
     KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches++;
     return 0;
@@ -1235,9 +1225,7 @@ static int launch_assign_h16_wide(kmb200_table *t, bool *done) {
 static int launch_assign_pair(kmb200_table *t, bool *applicable) {
     switch (t->ws.bn) {
 #define KMB_PAIR(BN_) \
-    return !g_corr ? launch_assign_pair_bn<BN_, 0>(t, applicable) \
-                   : !g_ss ? launch_assign_pair_bn<BN_, 1>(t, applicable) \
-                   : t->ws.dbg_scores ? launch_assign_pair_bn<BN_, 3>(t, applicable) : launch_assign_pair_bn<BN_, 2>(t, applicable)
+    return t->ws.dbg_scores ? launch_assign_pair_bn<BN_, true>(t, applicable) : launch_assign_pair_bn<BN_, false>(t, applicable)
         case 32: KMB_PAIR(32);
         case 64: KMB_PAIR(64);
         case 128: KMB_PAIR(128);
@@ -2143,8 +2131,6 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         g_kernel = (int)value;
     } else if (!strcmp(name, "fused")) {
         g_fused = value != 0;
-    } else if (!strcmp(name, "ss")) {
-        g_ss = value != 0;
     } else if (!strcmp(name, "stage_mb")) {
         if (value < 1.0 / 1024 || value > 4096) return fail(KMB200_ERR_ARG, "stage_mb must be in [1/1024, 4096]");
         g_stage_bytes = (size_t)(value * 1048576.0);
@@ -2163,8 +2149,6 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         g_h16 = value != 0;
     } else if (!strcmp(name, "rb_cap")) {
         g_rb_cap = (int)value;
-    } else if (!strcmp(name, "bf16_corr")) {
-        g_corr = value != 0;
     } else if (!strcmp(name, "cluster")) {
         if (value != 1 && value != 2) return fail(KMB200_ERR_ARG, "cluster must be 1 or 2");
         env_overrides();

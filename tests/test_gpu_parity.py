@@ -274,8 +274,6 @@ def test_force_simt_path_agrees(m):
     {"kernel": 1},                        # first-generation streaming kernel (the only one for d > 256)
     {"cluster": 1},                       # single-CTA resident-X kernel
     {"h16": 0},                           # CTA pairs, TF32 main product from shared memory + BF16 corrections
-    {"h16": 0, "bf16_corr": 0},           # CTA pairs, plain 3xTF32
-    {"h16": 0, "ss": 0},                  # CTA pairs, BF16 corrections, A operand entirely in TMEM
     {"fused": 0},                         # tensor-core path even where the one-pass small-k kernel applies
     {"two_level": 2, "cascade": 2},       # coarse one-product pass + fast pass + full bookkeeping over the near-tie rows, forced on small tables and shapes
     {"two_level": 2},                     # ... the coarse pass only where the shape makes it worth its while
@@ -294,7 +292,7 @@ def test_every_kernel_variant_keeps_parity(m, options):
             X, _, _ = ko.gaussian_blobs(n, d, k, seed=n + k)
             check_fit_parity(m, X, ko.row_init_centers(X, k), tol=1e-4, max_iter=5)
     finally:
-        for name, val in {"kernel": 2, "cluster": 2, "bf16_corr": 1, "ss": 1, "fused": 1, "h16": 1, "two_level": 1,
+        for name, val in {"kernel": 2, "cluster": 2, "fused": 1, "h16": 1, "two_level": 1,
                           "cand_cap": 0, "cascade": 1, "cand1_frac": 0.3}.items():
             m._lib.check(m.lib().kmb200_set_option(name.encode(), float(val)))
 

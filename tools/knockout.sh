@@ -1,7 +1,7 @@
 #!/bin/bash
 # Timing experiments for the assign kernel (results are invalid with knockout != 0): which role limits it?
 ROWS=${ROWS:-20000000}
-OPTS=${OPTS:-"passes=3 passes=1 knockout=1 knockout=2 knockout=4 knockout=7"}
+OPTS=${OPTS:-"knockout=0 knockout=4 knockout=64 knockout=2 knockout=128"}   # 4 no epilogue work, 64 TMEM loads only, 2 no transform stores, 128 stores of zeros
 for opt in $OPTS; do
   echo "== $opt"
   timeout -k 5 120 python bench.py --rows $ROWS --steps 3 --warmup 3 --no-e2e --no-cpu --option $opt --option role_prof=1 2>&1 | grep -E "role_prof|^\{" | python -c "
