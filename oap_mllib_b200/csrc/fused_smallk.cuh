@@ -39,6 +39,7 @@ fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent
                     int64_t n, int k, float eps, int32_t *__restrict__ labels, double *__restrict__ cta_part,
                     unsigned long long *__restrict__ recheck_counter) {
     extern __shared__ __align__(16) uint8_t fsm[];
+    __shared__ int s_sort[kFusedWarps][72];   // per warp: [0..32] label counts / offsets, [40..71] rows in label order
     constexpr int STRIDE = LD + 4;   // floats per tile row (16-byte aligned, spreads the banks)
     const int k2 = k;
     float *c32 = reinterpret_cast<float *>(fsm);                 // [k2][LD]
@@ -129,35 +130,70 @@ fused_smallk_kernel(const float *__restrict__ X, const double *__restrict__ cent
         }
         // ---- 4. label store (coalesced)
         if (lane < nrows) labels[row0 + lane] = bidx;
-        // ---- 5. accumulate: lanes own columns; rows with the same label are summed in registers first, so the
-        //         shared-memory partial of a cluster is updated once per batch, not once per row
-        unsigned remaining = nrows == 32 ? 0xffffffffu : ((1u << nrows) - 1u);
-        while (remaining) {
-            const int r0 = __ffs(remaining) - 1;
-            const int l = __shfl_sync(0xffffffffu, bidx, r0);
-            unsigned grp = __ballot_sync(0xffffffffu, bidx == l) & remaining;
-            remaining &= ~grp;
-            double *dst = mypart + (size_t)l * LD;
-            if (lane == 0) mypart[(size_t)k * LD + l] += (double)__popc(grp);
-            // lanes own columns: column sums in FP64, direct-form cost (x - c)^2 in FP32 per group of <= 32 rows
-            const float c0 = c32[(size_t)l * LD + lane];
-            const float c1 = LD > 32 ? c32[(size_t)l * LD + 32 + lane] : 0.f;
+        // ---- 5. accumulate: lanes own columns.  The 32 rows of the batch are first ordered by label (a counting sort
+        //         inside the warp: __match_any_sync gives a row's rank among the rows of its label, a 32-entry shared-
+        //         memory histogram and one warp scan give the labels' offsets), then walked in that order by a fully
+        //         unrolled loop: the running FP64 sum of a column stays in a register while the label does not change
+        //         and goes to the shared-memory partial once per (label, batch).  No data-dependent loop control: the
+        //         only branch is the warp-uniform "label changed" test.  (Round 1 looped over the distinct labels with
+        //         ballot / ffs loops: about 1000 of the 1860 instructions of a batch.)
+        {
+            int *sc = s_sort[w], *sp = s_sort[w] + 40;
+            const int key = lane < nrows ? bidx : 32;           // rows beyond the table sort last
+            const unsigned peers = __match_any_sync(0xffffffffu, key);
+            const int lower = __popc(peers & ((1u << lane) - 1u));
+            sc[lane] = 0;
+            __syncwarp();
+            if (lower == 0 && key < 32) sc[key] = __popc(peers);   // one lane per distinct label
+            __syncwarp();
+            const int cnt = sc[lane];                             // rows of label `lane` in this batch
+            int inc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int up = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += up;
+            }
+            __syncwarp();
+            sc[lane] = inc - cnt;                                 // first sorted position of label `lane`
+            if (lane == 0) sc[32] = nrows;
+            __syncwarp();
+            sp[sc[key] + lower] = lane | (key << 8);
+            if (lane < k && cnt > 0) mypart[(size_t)k * LD + lane] += (double)cnt;
+            __syncwarp();
+            const int mine = sp[lane];                            // the row at sorted position `lane`, and its label
+            int lprev = -1;
             double s0 = 0.0, s1 = 0.0;
-            float q0 = 0.f, q1 = 0.f;
-            while (grp) {
-                const int r = __ffs(grp) - 1;
-                grp &= grp - 1;
-                const float v0 = tile[r * STRIDE + lane];
+            float q0 = 0.f, q1 = 0.f, c0 = 0.f, c1 = 0.f;
+#pragma unroll
+            for (int r = 0; r < 32; ++r) {
+                const int e = __shfl_sync(0xffffffffu, mine, r);
+                const int pr = e & 0xff, lr = e >> 8;
+                if (lr != lprev) {                                // warp-uniform
+                    if (lprev >= 0) {
+                        double *dst = mypart + (size_t)lprev * LD;
+                        dst[lane] += s0;
+                        if (LD > 32) dst[32 + lane] += s1;
+                    }
+                    lprev = lr;
+                    if (lr >= 32) { lprev = -1; break; }          // only rows beyond the table follow
+                    s0 = s1 = 0.0;
+                    c0 = c32[(size_t)lr * LD + lane];
+                    if (LD > 32) c1 = c32[(size_t)lr * LD + 32 + lane];
+                }
+                const float v0 = tile[pr * STRIDE + lane];
                 s0 += (double)v0;
                 q0 = fmaf(v0 - c0, v0 - c0, q0);
                 if (LD > 32) {
-                    const float v1 = tile[r * STRIDE + 32 + lane];
+                    const float v1 = tile[pr * STRIDE + 32 + lane];
                     s1 += (double)v1;
                     q1 = fmaf(v1 - c1, v1 - c1, q1);
                 }
             }
-            dst[lane] += s0;
-            if (LD > 32) dst[32 + lane] += s1;
+            if (lprev >= 0) {
+                double *dst = mypart + (size_t)lprev * LD;
+                dst[lane] += s0;
+                if (LD > 32) dst[32 + lane] += s1;
+            }
             cost += (double)q0 + (double)q1;
         }
         __syncwarp();
