@@ -734,9 +734,9 @@ static int ws_prepare_impl(kmb200_table *t, int k) {
     KM_TRY(dmalloc(&w.red, (size_t)k * ld + k + 1));
     KM_TRY(dmalloc(&w.costj, (size_t)k));
     KM_TRY(dmalloc(&w.flags, 4));
-    w.fused_ctas = t->num_sms * 2;   // 2 CTAs of 256 threads fit one SM (registers)
+    w.fused_ctas = t->num_sms * 3;   // partials for up to 3 CTAs of 256 threads per SM (the MMA variant; the CUDA-core kernel runs 2)
     KM_TRY(dmalloc(&w.fused_part, (size_t)w.fused_ctas * ((size_t)k * ld + k + 1)));
-    KM_TRY(dmalloc(&w.fused_stage, 1024 + 32));
+    KM_TRY(dmalloc(&w.fused_stage, 1024 + 32 + 2048));
     CU_TRY(cudaMallocHost(reinterpret_cast<void **>(&w.host), sizeof(Workspace::Host)));
     KM_TRY(make_map(&w.tm_x, t->X, (uint64_t)t->rows, ld, kTileM));
     KM_TRY(make_map(&w.tm_bhi, w.bhi, (uint64_t)w.kpad, ld, (uint32_t)w.bn));
@@ -1273,7 +1273,7 @@ static int launch_fused_inst(kmb200_table *t, float eps) {
         attr_set[t->device & 63] = true;
     }
     auto *counter = reinterpret_cast<unsigned long long *>(w.flag_count);
-    fused_smallk_kernel<LD, KP><<<w.fused_ctas, kFusedWarps * 32, fused_smem_bytes(w.k, LD), t->stream>>>(
+    fused_smallk_kernel<LD, KP><<<t->num_sms * 2, kFusedWarps * 32, fused_smem_bytes(w.k, LD), t->stream>>>(
         t->X, w.cent, w.cstats, t->rows, w.k, eps, w.labels, w.fused_part, counter);
     KM_TRY(post_launch(__LINE__));
     return 0;
@@ -1286,6 +1286,28 @@ static int launch_fused(kmb200_table *t) {
     g_prof.assign_variant = 0;
     const int k = w.k, ld = t->ld, kp = fused_kp(k);
     CU_TRY(cudaMemsetAsync(w.flag_count, 0, 4 * sizeof(int32_t), t->stream));
+    if (ld == 32 && k <= 16 && g_fused == 1) {
+        // k <= 16, ld = 32 (C5): the distances as warp-level FP16-split MMAs (fused_mma_kernel)
+        static bool attr_set[64] = {false};
+        if (!attr_set[t->device & 63]) {
+            CU_TRY(cudaFuncSetAttribute(fused_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+            attr_set[t->device & 63] = true;
+        }
+        static_assert(sizeof(FusedMmaPrep) <= (1024 + 32 + 2048) * sizeof(float), "staging buffer");
+        FusedMmaPrep *prep = reinterpret_cast<FusedMmaPrep *>(w.fused_stage);
+        fused_mma_prepare_kernel<<<1, 256, 0, t->stream>>>(w.cent, k, t->xabs, prep);
+        KM_TRY(post_launch(__LINE__));
+        const float eps_mma = (float)(g_eps_scale * ldexp(3.0 * 32 / 16.0 + 32.0, -24));   // as the tcgen05 FP16-split kernel
+        auto *counter = reinterpret_cast<unsigned long long *>(w.flag_count);
+        fused_mma_kernel<<<t->num_sms * 3, kFusedWarps * 32, fused_mma_smem_bytes(k), t->stream>>>(
+            t->X, t->xnorm, w.cent, prep, t->rows, k, eps_mma, w.labels, w.fused_part, counter);
+        KM_TRY(post_launch(__LINE__));
+        const int psize1 = k * ld + k + 1;
+        fused_reduce_kernel<<<(psize1 + 255) / 256, 256, 0, t->stream>>>(w.fused_part, t->num_sms * 3, psize1, w.red);
+        KM_TRY(post_launch(__LINE__));
+        g_prof.kernel_launches += 3;
+        return 0;
+    }
     const float eps = (float)(g_eps_scale * ldexp((double)ld + 4.0, -24));   // FP32 FMA chain of ld terms
     float *stage_c = w.fused_stage, *stage_n = w.fused_stage + 1024;
     fused_prepare_kernel<<<1, 256, 0, t->stream>>>(w.cent, k, kp, ld, stage_c, stage_n);
@@ -1297,7 +1319,7 @@ static int launch_fused(kmb200_table *t) {
     else rc = kp == 8 ? launch_fused_inst<64, 8>(t, eps) : launch_fused_inst<64, 16>(t, eps);
     KM_TRY(rc);
     const int psize1 = k * ld + k + 1;
-    fused_reduce_kernel<<<(psize1 + 255) / 256, 256, 0, t->stream>>>(w.fused_part, w.fused_ctas, psize1, w.red);
+    fused_reduce_kernel<<<(psize1 + 255) / 256, 256, 0, t->stream>>>(w.fused_part, t->num_sms * 2, psize1, w.red);
     KM_TRY(post_launch(__LINE__));
     g_prof.kernel_launches += 3;
     return 0;
@@ -2130,7 +2152,7 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         env_overrides();
         g_kernel = (int)value;
     } else if (!strcmp(name, "fused")) {
-        g_fused = value != 0;
+        g_fused = value == 2 ? 2 : value != 0;   // 2 = the CUDA-core kernel also where the MMA variant applies (tests)
     } else if (!strcmp(name, "stage_mb")) {
         if (value < 1.0 / 1024 || value > 4096) return fail(KMB200_ERR_ARG, "stage_mb must be in [1/1024, 4096]");
         g_stage_bytes = (size_t)(value * 1048576.0);

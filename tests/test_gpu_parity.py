@@ -275,6 +275,7 @@ def test_force_simt_path_agrees(m):
     {"cluster": 1},                       # single-CTA resident-X kernel
     {"h16": 0},                           # CTA pairs, TF32 main product from shared memory + BF16 corrections
     {"fused": 0},                         # tensor-core path even where the one-pass small-k kernel applies
+    {"fused": 2},                         # one-pass small-k kernel with CUDA-core distances where the MMA variant applies
     {"two_level": 2, "cascade": 2},       # coarse one-product pass + fast pass + full bookkeeping over the near-tie rows, forced on small tables and shapes
     {"two_level": 2},                     # ... the coarse pass only where the shape makes it worth its while
     {"two_level": 2, "cascade": 0},       # ... without the coarse pass
