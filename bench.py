@@ -19,7 +19,8 @@ fused argmin / segmented-sum loop over a thread pool, the FP64 oracle itself) on
 each timed for one iteration on a bounded row sample and extrapolated linearly in N -- the
 reference's own oneDAL build cannot run in this image.  The initial centres are rows
 floor(j N / k) of the WHOLE table, so every GPU count solves the same problem and `final_cost`
-must agree across N.  `--workload C2|C4|C5` runs BASELINE.json's other configurations.
+must agree across N.  `--workload C2|C4|C5` runs BASELINE.json's other configurations; `--workload PCA` the PCA
+path over C3's table (bench_pca.py: its own metric, same contract).
 """
 from __future__ import annotations
 
@@ -445,7 +446,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS) + ["PCA"])
     ap.add_argument("--rows", type=int, default=0, help="override the total row count (debugging)")
     ap.add_argument("--centre-range", type=float, default=10.0,
                     help="blob centres ~ U(-R, R)^d with unit noise: 10 = BASELINE's well-separated blobs, 1 = heavy overlap")
@@ -460,7 +461,14 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
-    if args.impl == "reference":
+    if args.workload == "PCA":   # the PCA path under the same contract: bench_pca.py
+        import bench_pca
+        me = sys.modules[__name__]
+        if args.impl == "reference":
+            bench_pca.run_reference(args, rank, world, me)
+        else:
+            bench_pca.run_ours(args, rank, local_rank, world, me)
+    elif args.impl == "reference":
         run_reference(args, rank, world)
     else:
         run_ours(args, rank, local_rank, world)

@@ -241,6 +241,31 @@ int kmb200_init_sample(kmb200_table *table, int32_t seed, int32_t step, int32_t 
 int32_t kmb200_xorshift_next_int(int64_t seed);
 double kmb200_xorshift_next_double(int64_t seed, int32_t skip);
 
+/* ---- PCA -------------------------------------------------------------------------
+ * Replaces the body of Java_org_apache_spark_ml_feature_PCADALImpl_cPCATrainDAL (mllib-dal/src/main/native/
+ * PCADALImpl.cpp:38-190): oneDAL's pca::Distributed<step1Local / step2Master, double, svdDense> over the executors'
+ * tables with an all-gather of the partial results in between.  Here: one pass of column statistics, the Gram matrix of
+ * the resident FP32 table on the tensor cores (FP16-split products, FP64 partial sums), one all-reduce of d x d doubles,
+ * and the eigen-decomposition on the host -- the same eigenvalues (sigma^2 / (N - 1)) and principal axes.
+ *   center != 0: the column means are subtracted on the device (what PCADALImpl.scala:100-106 `normalizeData` does with
+ *                two JVM passes before the table is built); center == 0: the table is taken as it is, which is what the
+ *                reference's native code does with the rows it is given (it flags them "already normalised", :50-51).
+ *   pca_train  : eigenvalues[d] descending; eigenvectors[d x d] row-major, ONE PRINCIPAL AXIS PER ROW like the
+ *                reference's result table (PCADALImpl.scala:108-127 copies the first k rows into the columns of pc).
+ *                The sign of an axis is not defined by the reference (LAPACK's choice; IntelPCASuite.scala:75-84
+ *                compares absolute values): here the entry of largest magnitude is positive.  Collective when comm is
+ *                given; every rank receives the result.
+ *   pca_gram   : the (centred) Gram matrix sum_i (x_i - mean)(x_i - mean)^T [d x d], the means [d] (zeros when
+ *                center == 0) and the global row count -- tests and callers that want the covariance itself.
+ *   sym_eig    : the host eigen-solver alone (symmetric n x n row-major in; eigenvalues descending, eigenvectors as rows);
+ *                needs no device.
+ * d is not limited; rows per GPU as for every table.  Profile of a PCA call (kmb200_get_profile): accumulate_ms = the
+ * column-statistics pass, assign_ms = the Gram kernels, allreduce_ms, total_ms = first kernel to the last copy (device
+ * side), finalize_ms = the eigen-solver on the host (wall clock). */
+int kmb200_pca_train(kmb200_table *table, kmb200_comm *comm, int32_t center, double *eigenvalues, double *eigenvectors);
+int kmb200_pca_gram(kmb200_table *table, kmb200_comm *comm, int32_t center, double *gram, double *mean, int64_t *n_total);
+int kmb200_sym_eig(const double *a, int32_t n, double *eigenvalues, double *eigenvectors);
+
 /* Diagnostics (no reference counterpart): copies `bytes` bytes, starting `offset` bytes in, of one of the device
  * arrays the last fit / assign on this table left behind ("labels", "flag_list", "flag_count", "cand_list",
  * "labels_c", "cand1_list", "labels_c1", "xc", "xc1") to host memory.  Used by tools/repro_check.py. */

@@ -11,5 +11,7 @@ from ._lib import Kmb200Error, lib, library_path  # noqa: F401
 from .kmeans import (KMeans, KMeansDALImpl, KMeansModel, KMeansResult, KMeansSummary,  # noqa: F401
                      OneCCL, OneDAL, Table)
 
-__all__ = ["KMeans", "KMeansDALImpl", "KMeansModel", "KMeansResult", "KMeansSummary", "OneCCL",
+from .pca import PCA, PCADALImpl, PCAModel, PCAResult  # noqa: F401
+
+__all__ = ["PCA", "PCADALImpl", "PCAModel", "PCAResult", "KMeans", "KMeansDALImpl", "KMeansModel", "KMeansResult", "KMeansSummary", "OneCCL",
            "OneDAL", "Table", "Kmb200Error", "lib", "library_path"]

@@ -66,6 +66,9 @@ SIGNATURES = {
                                     C.POINTER(C.c_int64)]),
     "kmb200_xorshift_next_int": (C.c_int32, [C.c_int64]),
     "kmb200_xorshift_next_double": (C.c_double, [C.c_int64, C.c_int32]),
+    "kmb200_pca_train": (C.c_int, [_P, _P, C.c_int32, _P, _P]),
+    "kmb200_pca_gram": (C.c_int, [_P, _P, C.c_int32, _P, _P, _P]),
+    "kmb200_sym_eig": (C.c_int, [_P, C.c_int32, _P, _P]),
     "kmb200_debug_dump": (C.c_int, [_P, C.c_char_p, C.c_size_t, _P, C.c_size_t]),
     "kmb200_last_error": (C.c_char_p, []),
     "kmb200_version": (C.c_char_p, []),

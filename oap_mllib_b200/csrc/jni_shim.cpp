@@ -470,4 +470,56 @@ JNIEXPORT jlongArray JNICALL Java_org_apache_spark_ml_clustering_KMeansDALImpl_c
     return arr;
 }
 
+// ---------------------------------------------------------------- PCADALImpl
+// Same name and signature as the reference (native/PCADALImpl.cpp:38-42; javah/org_apache_spark_ml_feature_PCADALImpl.h).
+// pNumTabData is the kmb200_table handle.  On rank 0, result.pcNumericTable / result.explainedVarianceNumericTable
+// receive handles of a d x d table (one principal axis per row) and a 1 x d table (eigenvalues), read with cGetCenters
+// where the reference reads HomogenNumericTable.getDoubleArray (PCADALImpl.scala:108-136) and freed with cFreeCenters.
+// Like the reference's native code it takes the rows as they are (PCADALImpl.scala:37 has centred them on the JVM);
+// cPCATrainDALCentered subtracts the column means on the device instead, so that `normalizeData` can go.
+static jlong pca_train_jni(JNIEnvPtr env, jlong pNumTabData, jobject resultObj, bool center) {
+    kmb200_table *table = reinterpret_cast<kmb200_table *>(pNumTabData);
+    if (!table || !resultObj) {
+        throw_runtime(env, "null table handle or result object");
+        return 0;
+    }
+    const int d = kmb200_table_cols(table);
+    Centers *axes = new Centers{d, d, std::vector<double>((size_t)d * d)};
+    Centers *ev = new Centers{1, d, std::vector<double>((size_t)d)};
+    if (kmb200_pca_train(table, g_comm, center ? 1 : 0, ev->v.data(), axes->v.data()) != 0) {
+        delete axes;
+        delete ev;
+        throw_runtime(env, kmb200_last_error());
+        return 0;
+    }
+    if (g_rank != 0) {
+        delete axes;
+        delete ev;
+        return 0;
+    }
+    auto cls_of = slot<jclass (*)(JNIEnvPtr, jobject)>(env, kJniGetObjectClass);
+    auto fid = slot<jfieldID (*)(JNIEnvPtr, jclass, const char *, const char *)>(env, kJniGetFieldID);
+    auto setl = slot<void (*)(JNIEnvPtr, jobject, jfieldID, jlong)>(env, kJniSetLongField);
+    jclass clazz = cls_of(env, resultObj);
+    setl(env, resultObj, fid(env, clazz, "pcNumericTable", "J"), reinterpret_cast<jlong>(axes));
+    setl(env, resultObj, fid(env, clazz, "explainedVarianceNumericTable", "J"), reinterpret_cast<jlong>(ev));
+    return 0;
+}
+JNIEXPORT jlong JNICALL Java_org_apache_spark_ml_feature_PCADALImpl_cPCATrainDAL(JNIEnvPtr env, jobject, jlong pNumTabData, jint k,
+                                                                                 jint executor_num, jint executor_cores,
+                                                                                 jobject resultObj) {
+    (void)k;
+    (void)executor_num;
+    (void)executor_cores;
+    return pca_train_jni(env, pNumTabData, resultObj, false);
+}
+JNIEXPORT jlong JNICALL Java_org_apache_spark_ml_feature_PCADALImpl_cPCATrainDALCentered(JNIEnvPtr env, jobject, jlong pNumTabData,
+                                                                                         jint k, jint executor_num,
+                                                                                         jint executor_cores, jobject resultObj) {
+    (void)k;
+    (void)executor_num;
+    (void)executor_cores;
+    return pca_train_jni(env, pNumTabData, resultObj, true);
+}
+
 }  // extern "C"

@@ -2007,6 +2007,8 @@ extern "C" int kmb200_init_sample(kmb200_table *t, int32_t seed, int32_t step, i
     return rc;
 }
 
+#include "pca_host.inl"
+
 // Test hook: the raw tensor-core scores ||c_j||^2 - 2 x.c_j (FP32) of every row against every padded
 // centre column, so tests can measure the 3xTF32 error against FP64 and validate the near-tie bound.
 extern "C" int kmb200_debug_scores(kmb200_table *t, const double *centers, int32_t k, int32_t d, float *scores_host,
@@ -2177,6 +2179,16 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         g_cluster = (int)value;
     } else if (!strcmp(name, "knockout")) {
         g_knockout = (int)value;  // timing experiments only: results are invalid when non-zero
+    } else if (!strcmp(name, "pca_flush_rows")) {
+        if (!(value >= 32 && value <= 1048576)) return fail(KMB200_ERR_ARG, "pca_flush_rows must be in [32, 2^20]");
+        g_pca_flush_rows = (int)value;
+    } else if (!strcmp(name, "pca_promote")) {
+        if (!(value >= 1 && value <= 4096)) return fail(KMB200_ERR_ARG, "pca_promote must be in [1, 4096]");
+        g_pca_promote = (int)value;
+    } else if (!strcmp(name, "pca_knockout")) {
+        g_pca_knockout = (int)value;
+    } else if (!strcmp(name, "pca_desc_swap")) {
+        g_pca_desc_swap = value != 0;
     } else {
         return fail(KMB200_ERR_ARG, "unknown option '%s'", name);
     }
