@@ -1,7 +1,7 @@
 """`bench.py --workload PCA`: the PCA path under bench.py's contract.
 
-A "step" is one fit of ALL d principal components over the resident table: column statistics pass, Gram matrix on the
-tensor cores (gram_pair_kernel), one all-reduce of d x d doubles, eigen-decomposition on the host -- one call of
+A "step" is one fit of ALL d principal components over the resident table: the column statistics kept with the table by
+its appends, Gram matrix on the tensor cores (gram_pair_kernel), one all-reduce of d x d doubles, eigen-decomposition on the host -- one call of
 kmb200_pca_train, what Java_org_apache_spark_ml_feature_PCADALImpl_cPCATrainDAL does in the reference
 (mllib-dal/src/main/native/PCADALImpl.cpp:38-190).  The table is C3's (100M x 256 FP32, synthetic blobs): BASELINE.json
 quotes no PCA configuration, so `vs_baseline` is null and the metric is this file's own: `pca_fits_per_sec`.
@@ -182,9 +182,9 @@ def run_ours(args, rank, local_rank, world, B):
                 "executed_frac_of_fp16_sustained": 2.0 * flops_per_launch / (gram_ms * 1e-3) / 1e12 / peaks["bf16_sustained"],
                 "why_hbm": "2 n d^2 flops at the FP16 rate take less time than 4 n d bytes at HBM bandwidth for d = 256; the kernel executes "
                            "two FP16 products per term (FP64-faithful split), see executed_tflops",
-                "stats_pass_gbytes_per_s": bytes_per_launch / (phase["accumulate_ms"] * 1e-3) / 1e9,
-                "step_gbytes_per_s_per_gpu": 2.0 * bytes_per_launch / (ms_per_step * 1e-3) / 1e9,
-                "step_note": "a fit reads the table twice (statistics pass, Gram pass)"}
+                "step_gbytes_per_s_per_gpu": bytes_per_launch / (ms_per_step * 1e-3) / 1e9,
+                "step_note": "a fit reads the table once: the column sums / maxima it needs first are kept with the table by its appends "
+                             "(3 small kernels per appended batch; one extra pass only when rows were overwritten out of order)"}
     launches = int(sum(p["kernel_launches"] for p in profs))
     checksum = float(ev.sum())
 

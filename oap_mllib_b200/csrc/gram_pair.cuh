@@ -32,8 +32,8 @@
 // with its own MMA-issuing warp, its own four flush warps and segment boundaries half a segment apart -- while one half
 // is being drained (TMEM reads run at 64 B / cycle: about 2000 cycles per drain) the tensor pipe works on the other.
 //
-// Warp roles (608 threads): 0-7 flush (warp & 3 = TMEM lane quarter, warp >> 2 = column half), 8-15 transform, 16 TMA
-// producer, 17 / 18 MMA issuers of half 0 / 1 (leader CTA).  Barriers: every ring is a plain full / free pair whose
+// Warp roles (608 threads): 0-7 flush (warp & 3 = TMEM lane quarter, warp >> 2 = column half), 8-15 transform (two
+// groups of four; sixteen warps ran slower), 16 TMA producer, 17 / 18 MMA issuers of half 0 / 1 (leader CTA).  Barriers: every ring is a plain full / free pair whose
 // waiters wait for EVERY use in order (see the parity rule in assign_pair_h16.cuh):
 //   land_full[LS] (tx) / land_free[LS] (the 4 transform warps of the stage's group)           per CTA
 //   hl_full[HS] (leader: 4 local + 4 remote transform warps; both issuers wait) / hl_free[HS] (both issuers' multicast commits)
@@ -45,16 +45,17 @@
 
 namespace kmb {
 
-constexpr int kGramThreads = 608;
-constexpr int kGramRows = 32;                       // rows per stage (two K = 16 steps)
+constexpr int kGramThreads = 608;   // 19 warps: 8 flush, 8 transform, producer, 2 issuers
 constexpr int kGramStrip = 128;                     // columns per CTA
-constexpr int kGramLandBytes = kGramRows * 128;     // one [32 x 32 floats] box
-constexpr int kGramSubBytes = kGramRows * 128;      // one [32 x 64 halves] sub-tile
-constexpr int kGramOpBytes = 2 * kGramSubBytes;     // H (or L) of one strip and stage
-// Landing / operand ring depths (diagonal panels: one strip per stage; off-diagonal: two).  Both EVEN: the two transform
-// groups take the even / the odd stages, and a ring slot must always be consumed by the same group (parity rule).
-template <bool SAME> struct GramRings { static constexpr int LS = SAME ? 6 : 4, HS = SAME ? 4 : 2; };
-constexpr int kGramMaxBars = 2 * 6 + 2 * 4 + 4;
+// Rows per stage R (R / 16 K-steps): 64 on the diagonal panels (one strip per stage), 32 off the diagonal (two strips).
+// Every stage costs a fixed ~1000 cycles of hand-offs in the transform warps (proxy fence, cluster-scope arrive) and a
+// wait + commit in each issuer, so the rows per stage are what amortises them (measured with the knock-outs of
+// tools/pca_check.py: at R = 32 the barrier skeleton alone, without any load, conversion or MMA, ran 40 % as long as the
+// whole kernel).  Landing / operand ring depths are EVEN: the two transform groups take the even / the odd stages, and
+// a ring slot must always be consumed by the same group (parity rule).
+// (p.ls, p.hs; defaults gram_default_rings)
+constexpr int kGramMaxRing = 8;
+constexpr int kGramMaxBars = 4 * kGramMaxRing + 4;
 
 struct GramParams {
     const float *scale;     // [ld2] s_c     (ld2 = ld rounded up to 256: entries beyond ld are 1 / 0)
@@ -62,17 +63,25 @@ struct GramParams {
     double *partial;        // [pairs][256 n][256 m]
     int32_t n_rows;         // rows of the table
     int32_t stages_total;   // ceil(n_rows / 32)
+    int32_t ls, hs;         // landing / operand ring depths (even, <= 8)
     int32_t flush_stages;   // stages per level-1 segment
     int32_t promote_segs;   // level-1 segments per level-3 promotion
     int32_t colA0, colB0;   // first column of the A / B panel (multiples of 256)
     int32_t desc_swap;      // debugging: exchange LBO and SBO in the operand descriptors
+    long long *prof;        // optional cycle counters of pair 0's roles (diagnostics), else nullptr
     int32_t knockout;       // timing experiments (results invalid): 1 = no MMAs, 2 = no conversion, 4 = no level-2 / level-3 work, 8 = no TMA
 };
 
-static inline int gram_smem_bytes(bool same) {
+static inline int gram_smem_bytes(bool same, int rows, int ls, int hs) {
     const int strips = same ? 1 : 2;
-    const int ls = same ? GramRings<true>::LS : GramRings<false>::LS, hs = same ? GramRings<true>::HS : GramRings<false>::HS;
-    return 1024 + strips * (ls * 4 * kGramLandBytes + hs * 2 * kGramOpBytes) + kGramMaxBars * 8 + 16 + 2 * 2 * kGramStrip * 4;
+    return 1024 + strips * (ls + hs) * 4 * rows * 128 + kGramMaxBars * 8 + 16 + 2 * 2 * kGramStrip * 4;
+}
+// Default ring depths.  The landing ring needs few slots (the producer waits for a free slot 80 % of the time); the
+// operand ring is what lets the issuer of one column half run ahead while the other waits for its accumulator.
+static inline void gram_default_rings(bool same, int rows, int *ls, int *hs) {
+    if (!same) { *ls = 2; *hs = 4; }
+    else if (rows == 64) { *ls = 2; *hs = 4; }
+    else { *ls = 4; *hs = 8; }
 }
 
 // MN-major operand, 128-byte swizzle (see the header): start address, LBO, SBO in 16-byte units
@@ -95,6 +104,35 @@ __device__ __forceinline__ void mma_f16_ss_pair(uint32_t tmem_d, uint64_t desc_a
         : "memory");
 }
 
+// Eight consecutive columns of one row: FP32 (TMA-landed, swizzled) -> y = x s + o -> FP16 pair (h, l).  CHECK: the row
+// may lie past the end of the table (TMA zero-filled it; with centring y would be the offset, not 0).
+template <bool SAME, bool CHECK>
+__device__ __forceinline__ void gram_convert8(const uint8_t *src, int q, int rr, const float (&sc)[8], const float (&of)[8], bool valid,
+                                              uint4 &hv, uint4 &lv) {
+    const float4 v0 = *reinterpret_cast<const float4 *>(src + (((2 * q) ^ rr) << 4));
+    const float4 v1 = *reinterpret_cast<const float4 *>(src + (((2 * q + 1) ^ rr) << 4));
+    const float x[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    uint32_t hw[4], lw[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float y0 = fmaf(x[2 * j], sc[2 * j], of[2 * j]), y1 = fmaf(x[2 * j + 1], sc[2 * j + 1], of[2 * j + 1]);
+        if (CHECK) {
+            y0 = valid ? y0 : 0.f;
+            y1 = valid ? y1 : 0.f;
+        }
+        const __half2 a = __floats2half2_rn(y0, y1);
+        const float2 af = __half22float2(a);
+        // the residuals are exact; diagonal panels store 2 l (exact too): H^T H + H^T (2 L) is half of G^ + G^^T's
+        // asymmetric part, and gram_reduce_kernel averages entry (i, j) with (j, i) -- two products instead of three
+        const float l2 = SAME ? 2.f : 1.f;
+        const __half2 b = __floats2half2_rn(l2 * (y0 - af.x), l2 * (y1 - af.y));
+        hw[j] = *reinterpret_cast<const uint32_t *>(&a);
+        lw[j] = *reinterpret_cast<const uint32_t *>(&b);
+    }
+    hv = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+    lv = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+}
+
 // Level-1 segments of column half h: the first one of half 1 is half as long, so the two halves are never drained at
 // the same time.  Stage g of nst ends a segment when it is the last one, or the f0 + i fs -th.
 __device__ __forceinline__ int gram_first_segment(int h, int fs) { return (h == 1 && fs >= 2) ? fs / 2 : fs; }
@@ -102,11 +140,15 @@ __device__ __forceinline__ bool gram_segment_ends(int g, int nst, int f0, int fs
     return g + 1 == nst || (g + 1 >= f0 && (g + 1 - f0) % fs == 0);
 }
 
-template <bool SAME>
+template <bool SAME, int R>
 __global__ void __launch_bounds__(kGramThreads, 1)
 gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
     constexpr int STRIPS = SAME ? 1 : 2;
-    constexpr int kGramLS = GramRings<SAME>::LS, kGramHS = GramRings<SAME>::HS;
+    const int kGramLS = p.ls, kGramHS = p.hs;
+    constexpr int kGramRows = R;
+    constexpr int kGramLandBytes = R * 128;            // one [R x 32 floats] box
+    constexpr int kGramSubBytes = R * 128;             // one [R x 64 halves] sub-tile
+    constexpr int kGramOpBytes = 2 * kGramSubBytes;    // H (or L) of one strip and stage
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -164,9 +206,13 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
     if (warp == 16) {
         // ================================ TMA producer ================================
         const uint64_t evict_first = 0x12F0000000000000ull;
+        const bool prof = p.prof != nullptr && blockIdx.x == 0;
+        long long t_wait = 0, t0 = clock64();
         for (int g = 0; g < nst; ++g) {
             const uint32_t s = g % kGramLS, ph = (g / kGramLS) & 1;
+            const long long tm = prof ? clock64() : 0;
             mbar_wait_parked(&land_free[s], ph ^ 1);
+            if (prof) t_wait += clock64() - tm;
             if (elect_one()) {
                 if (p.knockout & 8) {
                     mbar_arrive(&land_full[s]);
@@ -185,6 +231,10 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
             }
             __syncwarp();
         }
+        if (prof && lane == 0) {
+            p.prof[0] = clock64() - t0;   // producer: total, waiting for a free landing slot
+            p.prof[1] = t_wait;
+        }
     } else if (warp >= 17) {
         // ================================ MMA issuers =================================
         // warp 17 + h: column half h (N = 128: sub-tile h of both CTAs' B strips), level-1 accumulator at columns 128 h
@@ -196,10 +246,15 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
             const uint32_t d_tmem = tmem_base + h * 128;
             uint32_t seg = 0;
             bool seg_start = true;
+            const bool prof = p.prof != nullptr && blockIdx.x == 0;
+            long long t_acc = 0, t_full = 0, t0 = clock64();
             for (int g = 0; g < nst; ++g) {
                 const uint32_t s = g % kGramHS, ph = (g / kGramHS) & 1;
+                long long tm = prof ? clock64() : 0;
                 if (seg_start && seg >= 1) mbar_wait(&acc_empty[h], (seg - 1) & 1);
+                if (prof) { const long long t = clock64(); t_acc += t - tm; tm = t; }
                 mbar_wait(&hl_full[s], ph);
+                if (prof) t_full += clock64() - tm;
                 tc_fence_after();
                 const bool seg_end = gram_segment_ends(g, nst, F0, FS);
                 if (elect_one()) {
@@ -221,12 +276,17 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
                 seg_start = seg_end;
                 if (seg_end) ++seg;
             }
+            if (prof && lane == 0) {
+                p.prof[4 + 4 * h] = clock64() - t0;   // issuer h: total, waiting for its accumulator, waiting for operands
+                p.prof[5 + 4 * h] = t_acc;
+                p.prof[6 + 4 * h] = t_full;
+            }
         }
     } else if (warp >= 8) {
         // ================================ transform ===================================
         // Two groups of four warps: group (tw >> 2) converts the stages of that parity, so a warp has two stage times
         // for the latency chain wait -> LDS -> convert -> wait -> STS -> fence -> (remote) arrive.  Warp: box tw & 3 (32
-        // columns of the strip), all 32 rows in four steps of eight; lane: row lane & 7, 8-column group lane >> 3.  A
+        // columns of the strip), all R rows in steps of eight; lane: row lane & 7, 8-column group lane >> 3.  A
         // quarter warp (one column group, eight rows) reads 16-byte chunks (2q) ^ row and writes chunk
         // ((box & 1) * 4 + q) ^ row of eight different rows: eight different bank groups both ways.
         const int tw = warp - 8;
@@ -241,71 +301,80 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
                 of[s][j] = col_s[STRIPS * kGramStrip + s * kGramStrip + box * 32 + q * 8 + j];
             }
         const uint32_t sub = box >> 1, chunk = (box & 1) * 4 + q;
+        const bool prof = p.prof != nullptr && blockIdx.x < 2 && box == 0;
+        long long t_land = 0, t_free = 0, t_fence = 0, t0 = clock64();
         for (int g = grp; g < nst; g += 2) {
             const uint32_t ls = g % kGramLS, lph = (g / kGramLS) & 1, hs = g % kGramHS;
+            const int rows_left = p.n_rows - (st0 + g) * kGramRows;   // rows of this stage inside the table
+            const bool full = rows_left >= kGramRows;
+            long long tm = prof ? clock64() : 0;
             mbar_wait_parked(&land_full[ls], lph);
+            if (prof) t_land += clock64() - tm;
 #pragma unroll
             for (int s = 0; s < STRIPS; ++s) {
-                uint4 hv[4], lv[4];
 #pragma unroll
-                for (int it = 0; it < ((p.knockout & 2) ? 0 : 4); ++it) {
-                    const int row = it * 8 + rr;
-                    const uint8_t *src = land + ((ls * STRIPS + s) * 4 + box) * kGramLandBytes + row * 128;
-                    const float4 v0 = *reinterpret_cast<const float4 *>(src + (((2 * q) ^ rr) << 4));
-                    const float4 v1 = *reinterpret_cast<const float4 *>(src + (((2 * q + 1) ^ rr) << 4));
-                    const bool valid = (st0 + g) * kGramRows + row < p.n_rows;   // rows past the table contribute nothing
-                    const float x[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-                    uint32_t hw[4], lw[4];
+                for (int pass = 0; pass < R / 32; ++pass) {
+                    uint4 hv[4], lv[4];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const float y0 = valid ? fmaf(x[2 * j], sc[s][2 * j], of[s][2 * j]) : 0.f;
-                        const float y1 = valid ? fmaf(x[2 * j + 1], sc[s][2 * j + 1], of[s][2 * j + 1]) : 0.f;
-                        const __half2 a = __floats2half2_rn(y0, y1);
-                        const float2 af = __half22float2(a);
-                        // the residuals are exact; diagonal panels store 2 l (exact too): H^T H + H^T (2 L) is half of
-                        // G^ + G^^T's asymmetric part, and gram_reduce_kernel averages entry (i, j) with (j, i) -- two
-                        // products instead of three
-                        const float l2 = SAME ? 2.f : 1.f;
-                        const __half2 b = __floats2half2_rn(l2 * (y0 - af.x), l2 * (y1 - af.y));
-                        hw[j] = *reinterpret_cast<const uint32_t *>(&a);
-                        lw[j] = *reinterpret_cast<const uint32_t *>(&b);
+                    for (int it = 0; it < ((p.knockout & 2) ? 0 : 4); ++it) {
+                        const int row = pass * 32 + it * 8 + rr;
+                        const uint8_t *src = land + ((ls * STRIPS + s) * 4 + box) * kGramLandBytes + row * 128;
+                        if (full) gram_convert8<SAME, false>(src, q, rr, sc[s], of[s], true, hv[it], lv[it]);
+                        else gram_convert8<SAME, true>(src, q, rr, sc[s], of[s], row < rows_left, hv[it], lv[it]);
                     }
-                    hv[it] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-                    lv[it] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-                }
-                if (s == STRIPS - 1) {
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&land_free[ls]);   // the stage's tiles are in registers
-                }
-                // the MMAs that read the previous contents of this operand slot have completed
-                if (s == 0 && g >= kGramHS) mbar_wait_parked(&hl_free[hs], ((g / kGramHS) - 1) & 1);
+                    if (s == STRIPS - 1 && pass == R / 32 - 1) {
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&land_free[ls]);   // the stage's tiles are in registers
+                    }
+                    // the MMAs that read the previous contents of this operand slot have completed
+                    if (s == 0 && pass == 0 && g >= kGramHS) {
+                        tm = prof ? clock64() : 0;
+                        mbar_wait_parked(&hl_free[hs], ((g / kGramHS) - 1) & 1);
+                        if (prof) t_free += clock64() - tm;
+                    }
 #pragma unroll
-                for (int it = 0; it < 4; ++it) {
-                    const int row = it * 8 + rr;
-                    uint8_t *dst = ops + (hs * STRIPS + s) * 2 * kGramOpBytes + sub * kGramSubBytes + row * 128 + ((chunk ^ rr) << 4);
-                    *reinterpret_cast<uint4 *>(dst) = hv[it];
-                    *reinterpret_cast<uint4 *>(dst + kGramOpBytes) = lv[it];
+                    for (int it = 0; it < 4; ++it) {
+                        const int row = pass * 32 + it * 8 + rr;
+                        uint8_t *dst = ops + (hs * STRIPS + s) * 2 * kGramOpBytes + sub * kGramSubBytes + row * 128 + ((chunk ^ rr) << 4);
+                        *reinterpret_cast<uint4 *>(dst) = hv[it];
+                        *reinterpret_cast<uint4 *>(dst + kGramOpBytes) = lv[it];
+                    }
                 }
             }
+            tm = prof ? clock64() : 0;
             fence_proxy_async();   // generic-proxy stores -> visible to the tensor core's reads
             __syncwarp();
             if (lane == 0) {
                 if (leader) mbar_arrive(&hl_full[hs]);
-                else mbar_arrive_remote(&hl_full[hs], 0);
+                else mbar_arrive_remote_cta(&hl_full[hs], 0);
             }
+            if (prof) t_fence += clock64() - tm;
+        }
+        if (prof && lane == 0) {
+            long long *o = p.prof + 16 + 8 * blockIdx.x + 4 * grp;   // transform (CTA, group): total, landing wait, operand-slot wait, fence + arrive
+            o[0] = clock64() - t0;
+            o[1] = t_land;
+            o[2] = t_free;
+            o[3] = t_fence;
         }
     } else {
         // ================================ flush =======================================
         // warp & 3: TMEM lane quarter (output rows m), warp >> 2: column half.  TMEM column c of half h is output column
         // (c >> 6) * 128 + 64 h + (c & 63) of the panel (columns 0-63 come from CTA 0's sub-tile h, 64-127 from CTA 1's).
+        // (Tried and slower: all eight warps draining whichever half completes next, level 1 read first and released at
+        // once -- the drains of the two halves then queue behind each other; 16-column pieces for a 72-register budget.)
         const int qd = warp & 3, h = warp >> 2;
         const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
         const int F0 = gram_first_segment(h, FS);
         const int nseg = nst <= F0 ? 1 : 1 + (nst - F0 + FS - 1) / FS;
         double *P = p.partial + (size_t)pair * 65536 + (int)rank * 128 + qd * 32 + lane;
         const uint32_t l1 = tmem_base + lane_addr + h * 128, l2 = l1 + 256;
+        const bool prof = p.prof != nullptr && blockIdx.x == 0 && qd == 0;
+        long long t_wait = 0, t0 = clock64();
         for (int seg = 0; seg < nseg; ++seg) {
+            const long long tm = prof ? clock64() : 0;
             mbar_wait_parked(&acc_full[h], seg & 1);
+            if (prof) t_wait += clock64() - tm;
             tc_fence_after();
             const bool promote = (seg + 1) % p.promote_segs == 0 || seg + 1 == nseg;
             const bool fresh = seg % p.promote_segs == 0;   // level 2 was cleared (or never written)
@@ -345,6 +414,10 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
             }
             tmem_wait_st();
         }
+        if (prof && lane == 0) {
+            p.prof[12 + 2 * h] = clock64() - t0;   // flush warps of half h: total, waiting for a complete accumulator
+            p.prof[13 + 2 * h] = t_wait;
+        }
     }
     // teardown: every MMA has completed (the flush warps waited for the last acc_full) before TMEM goes away
     tc_fence_before();
@@ -369,12 +442,20 @@ __global__ void __launch_bounds__(256) colstats_kernel(const float *__restrict__
         double s[4] = {0.0, 0.0, 0.0, 0.0};
         float m[4] = {0.f, 0.f, 0.f, 0.f};
         if (rl < RL) {
-            for (int64_t r = r0 + rl; r < r1; r += RL) {
-                const float4 v = __ldg(reinterpret_cast<const float4 *>(X + r * ld) + g0 + g);
+            auto add = [&](const float4 v) {
                 s[0] += v.x; s[1] += v.y; s[2] += v.z; s[3] += v.w;
                 m[0] = fmaxf(m[0], fabsf(v.x)); m[1] = fmaxf(m[1], fabsf(v.y));
                 m[2] = fmaxf(m[2], fabsf(v.z)); m[3] = fmaxf(m[3], fabsf(v.w));
+            };
+            int64_t r = r0 + rl;
+            for (; r + 7 * (int64_t)RL < r1; r += 8 * (int64_t)RL) {   // eight independent loads in flight per thread
+                float4 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = __ldcs(reinterpret_cast<const float4 *>(X + (r + u * (int64_t)RL) * ld) + g0 + g);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) add(v[u]);
             }
+            for (; r < r1; r += RL) add(__ldcs(reinterpret_cast<const float4 *>(X + r * ld) + g0 + g));
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -427,6 +508,13 @@ __global__ void __launch_bounds__(256) colstats_reduce_kernel(const double *__re
         omax[c] = b;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) osum[ld] = (double)n;
+}
+// running statistics (+)= one batch's (kmb200_table::colsum / colmax); sums [ld + 1] with the row count last
+__global__ void colstats_merge_kernel(const double *__restrict__ tsum, const float *__restrict__ tmax, int ld, int reset,
+                                      double *__restrict__ colsum, float *__restrict__ colmax) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c <= ld) colsum[c] = (reset ? 0.0 : colsum[c]) + tsum[c];
+    if (c < ld) colmax[c] = fmaxf(reset ? 0.f : colmax[c], tmax[c]);
 }
 // Per column, from the GLOBAL sums / maxima: mu = centre ? float(sum / N) : 0; s = 2^(13 - floor(log2(max|x| + |mu|)));
 // scale = s, offs = -mu s, inv = 1 / s (double), mean_used = mu (double).  Columns [ld, ld2) get scale 1, offset 0.

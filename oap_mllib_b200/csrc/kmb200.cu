@@ -23,6 +23,7 @@
 #include "assign_pair_ss.cuh"
 #include "assign_pair_h16.cuh"
 #include "fused_smallk.cuh"
+#include "gram_pair.cuh"
 #include "kernels_misc.cuh"
 
 using namespace kmb;
@@ -229,7 +230,27 @@ struct EventPool {
     }
 };
 
+// Buffers of the PCA path (pca_host.inl), allocated on a table's first PCA call and kept with it: allocation and
+// release per call cost more than the kernels on a table of a few million rows.
+struct PcaWs {
+    int pairs = 0;
+    double *gsum = nullptr, *inv = nullptr, *mean_used = nullptr, *partial = nullptr, *G = nullptr;
+    float *gmax = nullptr, *scale = nullptr, *offs = nullptr;
+    long long *prof = nullptr;
+    double *host = nullptr;   // pinned: [ld * ld] Gram matrix, [ld + 1] sums, [ld] means
+    cudaEvent_t ev[5] = {};
+    ~PcaWs() {
+        void *ptrs[] = {gsum, inv, mean_used, partial, G, gmax, scale, offs, prof};
+        for (void *q : ptrs)
+            if (q) cudaFree(q);
+        if (host) cudaFreeHost(host);
+        for (auto e : ev)
+            if (e) cudaEventDestroy(e);
+    }
+};
+
 struct kmb200_table {
+    PcaWs *pca = nullptr;
     int device = 0;
     int64_t rows = 0;       // logical rows (kmb200_table_truncate may lower it)
     int64_t capacity = 0;   // rows allocated at creation
@@ -239,6 +260,15 @@ struct kmb200_table {
     float *xabs = nullptr;   // [1] max |x_ij| over everything ever appended (scale of the FP16 split)
     void *stage = nullptr;
     size_t stage_bytes = 0;
+    // Running column statistics of rows [0, stats_rows) (PCA: sums for the centring, max |x| for the column scales),
+    // kept up to date by every append that continues where the last one ended (launch_rownorm); anything else --
+    // a gap, an overwrite, a truncation below stats_rows -- clears stats_ok and the PCA call recomputes them in one pass.
+    double *colsum = nullptr;      // [ld + 1] column sums, then the row count
+    float *colmax = nullptr;       // [ld]
+    double *cs_psum = nullptr, *cs_tsum = nullptr;   // scratch: per-block partials [4 * num_sms][ld], one batch's sums [ld + 1]
+    float *cs_pmax = nullptr, *cs_tmax = nullptr;
+    int64_t stats_rows = 0;
+    bool stats_ok = false;
     double *init_cost = nullptr;   // [rows] k-means|| initialisation: cost of every row to the nearest centre chosen so far
     double *init_tmp = nullptr;    // [rows + 1024] scratch of those passes
     cudaStream_t stream = nullptr;
@@ -385,9 +415,13 @@ extern "C" int kmb200_table_free(kmb200_table *t) {
     cudaSetDevice(t->device);
     cudaStreamSynchronize(t->stream);
     ws_free(t->ws);
+    delete t->pca;
     if (t->stage) cudaFree(t->stage);
     if (t->init_cost) cudaFree(t->init_cost);
     if (t->init_tmp) cudaFree(t->init_tmp);
+    void *stats[] = {t->colsum, t->colmax, t->cs_psum, t->cs_tsum, t->cs_pmax, t->cs_tmax};
+    for (void *q : stats)
+        if (q) cudaFree(q);
     cudaFree(t->X);
     cudaFree(t->xnorm);
     cudaFree(t->xabs);
@@ -399,13 +433,46 @@ extern "C" int kmb200_table_free(kmb200_table *t) {
 extern "C" int64_t kmb200_table_rows(const kmb200_table *t) { return t ? t->rows : -1; }
 extern "C" int32_t kmb200_table_cols(const kmb200_table *t) { return t ? t->d : -1; }
 
+// Column statistics of the rows just written (see kmb200_table::colsum).  row0 == 0 starts over.
+static int table_stats_append(kmb200_table *t, int64_t row0, int64_t nrows) {
+    if (nrows <= 0) return 0;
+    const bool reset = row0 == 0;
+    if (reset) {
+        t->stats_rows = 0;
+        t->stats_ok = true;
+    }
+    if (!t->stats_ok) return 0;
+    if (row0 != t->stats_rows) {
+        t->stats_ok = false;
+        return 0;
+    }
+    const int ld = t->ld;
+    if (!t->colsum) {
+        CU_TRY(cudaMalloc(&t->colsum, ((size_t)ld + 1) * sizeof(double)));
+        CU_TRY(cudaMalloc(&t->colmax, (size_t)ld * sizeof(float)));
+        CU_TRY(cudaMalloc(&t->cs_tsum, ((size_t)ld + 1) * sizeof(double)));
+        CU_TRY(cudaMalloc(&t->cs_tmax, (size_t)ld * sizeof(float)));
+        CU_TRY(cudaMalloc(&t->cs_psum, (size_t)t->num_sms * 4 * ld * sizeof(double)));
+        CU_TRY(cudaMalloc(&t->cs_pmax, (size_t)t->num_sms * 4 * ld * sizeof(float)));
+    }
+    const int blocks = (int)std::min<int64_t>((int64_t)t->num_sms * 4, std::max<int64_t>(1, nrows / 64));
+    colstats_kernel<<<blocks, 256, 0, t->stream>>>(t->X + (size_t)row0 * ld, nrows, ld, t->cs_psum, t->cs_pmax);
+    KM_TRY(post_launch(__LINE__));
+    colstats_reduce_kernel<<<(ld + 7) / 8, 256, 0, t->stream>>>(t->cs_psum, t->cs_pmax, blocks, ld, nrows, t->cs_tsum, t->cs_tmax);
+    KM_TRY(post_launch(__LINE__));
+    colstats_merge_kernel<<<(ld + 256) / 256, 256, 0, t->stream>>>(t->cs_tsum, t->cs_tmax, ld, reset ? 1 : 0, t->colsum, t->colmax);
+    KM_TRY(post_launch(__LINE__));
+    t->stats_rows = row0 + nrows;
+    return 0;
+}
+
 static int launch_rownorm(kmb200_table *t, int64_t row0, int64_t nrows) {
     const int64_t warps = (nrows + 3) / 4;
     int blocks = (int)std::min<int64_t>((warps * 32 + 255) / 256, (int64_t)t->num_sms * 16);
     if (blocks < 1) blocks = 1;
     rownorm_kernel<<<blocks, 256, 0, t->stream>>>(t->X, t->xnorm, t->xabs, row0, nrows, t->ld);
     KM_TRY(post_launch(__LINE__));
-    return 0;
+    return table_stats_append(t, row0, nrows);
 }
 
 template <typename T>
@@ -582,6 +649,7 @@ extern "C" int kmb200_table_truncate(kmb200_table *t, int64_t rows) {
     if (t->init_tmp) cudaFree(t->init_tmp);
     t->init_cost = t->init_tmp = nullptr;
     t->rows = rows;
+    if (rows != t->stats_rows) t->stats_ok = false;
     return 0;
 }
 
@@ -2185,6 +2253,14 @@ extern "C" int kmb200_set_option(const char *name, double value) {
     } else if (!strcmp(name, "pca_promote")) {
         if (!(value >= 1 && value <= 4096)) return fail(KMB200_ERR_ARG, "pca_promote must be in [1, 4096]");
         g_pca_promote = (int)value;
+    } else if (!strcmp(name, "pca_ls") || !strcmp(name, "pca_hs")) {
+        const int v = (int)value;
+        if (v < 0 || v > kGramMaxRing || (v & 1)) return fail(KMB200_ERR_ARG, "%s must be even and at most %d", name, kGramMaxRing);
+        (name[4] == 'l' ? g_pca_ls : g_pca_hs) = v;
+    } else if (!strcmp(name, "pca_role_prof")) {
+        g_pca_role_prof = value != 0;
+    } else if (!strcmp(name, "pca_rows")) {
+        g_pca_rows = value == 32 ? 32 : 64;
     } else if (!strcmp(name, "pca_knockout")) {
         g_pca_knockout = (int)value;
     } else if (!strcmp(name, "pca_desc_swap")) {

@@ -212,6 +212,19 @@ __device__ __forceinline__ void mbar_arrive_remote_relaxed(uint64_t *bar, uint32
         "r"(rank)
         : "memory");
 }
+// Arrive on the barrier at the same offset in CTA `rank`, with mbarrier.arrive's DEFAULT semantics (release at CTA
+// scope): the hand-off of shared-memory operands written by this CTA's threads (each followed by fence.proxy.async) to a
+// cta_group::2 MMA issued by the peer -- the MMA reads THIS CTA's shared memory through this SM's own tensor core, so
+// nothing has to become visible to the peer's threads.  The cluster-scope release below costs ~2000 cycles after a
+// burst of shared-memory stores (measured in gram_pair_kernel); this form a few hundred.
+__device__ __forceinline__ void mbar_arrive_remote_cta(uint64_t *bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}" ::"r"(smem_u32(bar)),
+        "r"(rank)
+        : "memory");
+}
 // arrive on the barrier at the same offset in CTA `rank` of the cluster
 __device__ __forceinline__ void mbar_arrive_remote(uint64_t *bar, uint32_t rank) {
     asm volatile(

@@ -19,4 +19,4 @@ def test_two_gpus_match_two_rank_oracle(built_lib):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     sys.stdout.write(r.stdout[-4000:])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert r.stdout.count(" OK") == 7
+    assert r.stdout.count(" OK") == 10    # 7 K-means cases + 3 PCA cases

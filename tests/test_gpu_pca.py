@@ -141,6 +141,37 @@ def test_results_are_bit_reproducible(m):
         table.release()
 
 
+def test_column_statistics_follow_the_appends(m):
+    """The column sums / maxima the centring and the column scales need are kept with the table by appends that continue
+    where the last one ended; an overwrite in the middle makes the PCA call recompute them (three more kernels)."""
+    from oap_mllib_b200 import pca
+
+    def gram_matches(table, X):
+        g, mean, n = pca.gram(table, True)
+        g_ref, mean_ref, _ = po.centred_gram([X], True)
+        assert n == X.shape[0] and np.allclose(mean, mean_ref, rtol=0, atol=1e-12 * np.abs(mean_ref).max())
+        assert (np.abs(g - g_ref) / np.sqrt(np.outer(np.diag(g_ref), np.diag(g_ref)))).max() <= GRAM_TOL
+        return m._lib.profile()["kernel_launches"]
+
+    X = decaying_table(50_000, 40, seed=13, shift=20.0)
+    t = m.Table(60_000, 40)                   # sized for more rows than arrive, truncated below (OneDAL.scala:150-160 does the same)
+    try:
+        t.append(0, X[:20_000])
+        t.append(20_000, X[20_000:])
+        t.truncate(50_000)
+        kept = gram_matches(t, X)
+        X2 = X.copy()
+        X2[1000:2000] = X2[1000:2000] * 3.0 + 7.0
+        t.append(1000, X2[1000:2000])          # out of order: the running statistics are dropped ...
+        assert gram_matches(t, X2) == kept + 3     # ... and recomputed by the call
+        assert gram_matches(t, X2) == kept         # (and then kept again)
+        t.append(0, X[:30_000])                # a new upload from row 0 starts them over
+        t.append(30_000, X[30_000:])
+        assert gram_matches(t, X) == kept
+    finally:
+        t.release()
+
+
 def test_pcadalimpl_mirror_and_model(m):
     """PCADALImpl.train -> MLlibPCAModel: pc is d x k with one component per column, explainedVariance sums below 1."""
     X = decaying_table(20_000, 30, seed=2)

@@ -96,3 +96,62 @@ def test_two_ranks_gloo_equal_single_rank_oracle():
         np.testing.assert_allclose(C, want_c, rtol=1e-12)
         assert abs(cost - want_cost) <= 1e-10 * want_cost
     np.testing.assert_array_equal(out[0][3], out[1][3])          # bit-identical centres on both ranks
+
+
+def _pca_worker(rank, world, port, q):
+    """The PCA protocol of csrc/pca_host.inl on two gloo ranks: all-reduce of [column sums | row count] (sum) and of the
+    column maxima (max), a shared FP32-rounded mean, the local Gram matrix of the rows centred with it, one all-reduce of
+    d x d doubles, and the exact correction  G - N ybar ybar^T  with ybar = sum / N - mean_f32."""
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from oap_mllib_b200 import sharding
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        n, d = 5003, 12
+        rng = np.random.default_rng(8)
+        X = (rng.standard_normal((n, d)) * np.linspace(5, 0.2, d) + rng.uniform(-30, 30, d)).astype(np.float32)
+        r0, r1 = sharding.shard_bounds(n, world)[rank]
+        mine = X[r0:r1].astype(np.float64)
+        stats = torch.from_numpy(np.concatenate([mine.sum(axis=0), [float(r1 - r0)]]))
+        dist.all_reduce(stats)
+        mx = torch.from_numpy(np.abs(mine).max(axis=0))
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        s1, ntot = stats.numpy()[:d], stats.numpy()[d]
+        mean_f = (s1 / ntot).astype(np.float32).astype(np.float64)      # what the kernel subtracts
+        y = mine - mean_f
+        g = torch.from_numpy(y.T @ y)
+        dist.all_reduce(g)
+        ybar = s1 / ntot - mean_f
+        q.put((rank, g.numpy() - ntot * np.outer(ybar, ybar), int(ntot), mx.numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_gloo_pca_partials_equal_the_oracle():
+    import torch.multiprocessing as mp
+    from oracle import pca_oracle as po
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_pca_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    n, d = 5003, 12
+    rng = np.random.default_rng(8)
+    X = (rng.standard_normal((n, d)) * np.linspace(5, 0.2, d) + rng.uniform(-30, 30, d)).astype(np.float32)
+    g_ref, _, n_ref = po.centred_gram([X[:2501], X[2501:]], True)
+    for rank, g, ntot, mx in out:
+        assert ntot == n_ref == n
+        np.testing.assert_allclose(g, g_ref, rtol=1e-10, atol=1e-9 * np.abs(g_ref).max())
+        np.testing.assert_array_equal(mx, np.abs(X.astype(np.float64)).max(axis=0))
+    np.testing.assert_array_equal(out[0][1], out[1][1])      # the same matrix on both ranks
+    ev, axes = po.eig_desc(out[0][1])
+    ev_ref, axes_ref = po.pca_svd_dense([X[:2501], X[2501:]])
+    np.testing.assert_allclose(ev / (n - 1), ev_ref, rtol=1e-9)
+    np.testing.assert_allclose(axes[:4], axes_ref[:4], atol=1e-8)

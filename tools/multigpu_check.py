@@ -58,6 +58,30 @@ def main():
         else:
             assert model is None
         dist.barrier()
+    # ---- PCA (section 8 row f4): every rank's shard in its own table, PCADALImpl.train collectively (one all-reduce of the
+    # column statistics, one of the d x d Gram matrix), rank 0 against the oracle's distributed route (one QR factor per rank)
+    from oracle import pca_oracle as po
+    for n, d, kk in [(50001, 96, 8), (300000, 256, 16), (20000, 300, 5)]:
+        rng = np.random.default_rng(n + d)
+        basis = np.linalg.qr(rng.standard_normal((d, d)))[0]
+        X = ((rng.standard_normal((n, d)) * (10.0 * 0.93 ** np.arange(d) + 0.05)) @ basis + rng.uniform(-5, 5, d)).astype(np.float32)
+        bounds = shard_bounds(n, world)
+        r0, r1 = bounds[rank]
+        ident = [m.OneCCL.getUniqueId() if rank == 0 else None]
+        dist.broadcast_object_list(ident, src=0)
+        model = m.PCADALImpl(kk, world, 1).train(X[r0:r1], rank=rank, unique_id=ident[0])
+        if rank == 0:
+            ev, axes = po.pca_svd_dense([X[a:b] for a, b in bounds])
+            pc, expl = po.model(ev, axes, kk)
+            e_pc, e_ex = np.abs(model.pc - pc).max(), np.abs(model.explainedVariance - expl).max()
+            ok = e_pc <= 1e-6 and e_ex <= 1e-6
+            print(f"[multigpu] pca n={n} d={d} k={kk} world={world}: component err {e_pc:.2e} explained-variance err {e_ex:.2e} "
+                  f"{'OK' if ok else 'FAIL'}", flush=True)
+            if not ok:
+                failures.append(("pca", n, d, kk))
+        else:
+            assert model is None
+        dist.barrier()
     dist.destroy_process_group()
     if failures:
         sys.exit(1)

@@ -76,14 +76,31 @@ def main():
             print(f"[pca] big {n} x {d} flush {flush}: {dt * 1e3:.1f} ms per call; max rel diff to flush=128: "
                   f"{(np.abs(g - g_ref) / np.sqrt(np.outer(np.diag(g_ref), np.diag(g_ref)))).max():.3e}", flush=True)
         if args.knock:
-            for flush in (128, 16384):
-                for ko in (0, 1, 2, 4, 8, 1 | 4, 2 | 8, 1 | 2 | 4 | 8):
+            def opt(name, v):
+                _lib.check(lib.kmb200_set_option(name.encode(), float(v)))
+            for rows_per_stage, ls, hs in [(64, 2, 4), (64, 4, 2), (32, 4, 8)]:
+                for flush in (128, 256, 512, 16384):
+                    opt("pca_rows", rows_per_stage), opt("pca_ls", ls), opt("pca_hs", hs), opt("pca_flush_rows", flush)
+                    pca.gram(t, True)
+                    pca.gram(t, True)
+                    print(f"[pca] timing rows/stage {rows_per_stage} rings {ls}/{hs} flush {flush}: gram {_lib.profile()['assign_ms']:.2f} ms", flush=True)
+            opt("pca_role_prof", 1)
+            for rows_per_stage, ls, hs in [(64, 2, 4), (32, 4, 8)]:
+                opt("pca_rows", rows_per_stage), opt("pca_ls", ls), opt("pca_hs", hs), opt("pca_flush_rows", 256)
+                print(f"[pca] role profile, rows/stage {rows_per_stage}, rings {ls}/{hs}, flush 256:", flush=True)
+                pca.gram(t, True)
+            opt("pca_role_prof", 0), opt("pca_ls", 0), opt("pca_hs", 0), opt("pca_rows", 64)
+        if args.knock and False:
+            for rows_per_stage, flush, ko in [(64, 128, 0), (64, 128, 1), (64, 128, 2), (64, 128, 4), (64, 128, 8), (64, 128, 15), (64, 16384, 0),
+                                              (64, 256, 0), (32, 128, 0), (32, 16384, 0)]:
+                if True:
+                    _lib.check(lib.kmb200_set_option(b"pca_rows", float(rows_per_stage)))
                     _lib.check(lib.kmb200_set_option(b"pca_flush_rows", float(flush)))
                     _lib.check(lib.kmb200_set_option(b"pca_knockout", float(ko)))
                     pca.gram(t, True)
                     pca.gram(t, True)
                     pr = _lib.profile()
-                    print(f"[pca] knock flush {flush} knockout {ko}: gram {pr['assign_ms']:.2f} ms, stats {pr['accumulate_ms']:.2f} ms", flush=True)
+                    print(f"[pca] knock rows/stage {rows_per_stage} flush {flush} knockout {ko}: gram {pr['assign_ms']:.2f} ms, stats {pr['accumulate_ms']:.2f} ms", flush=True)
             _lib.check(lib.kmb200_set_option(b"pca_knockout", 0.0))
         t.release()
 
