@@ -180,7 +180,11 @@ int kmb200_get_profile(kmb200_profile *out);
  * staging buffer of the columnar / sparse / FP64 uploads, default 256), "dbg_products" (1 = the
  * score dump of kmb200_debug_scores shows the coarse pass),
  * "cluster", "kernel", "fused", "rb_cap" (fallback kernels), and the diagnostics
- * "knockout" / "role_prof" (timing experiments; results are invalid with knockout != 0). */
+ * "knockout" / "role_prof" (timing experiments; results are invalid with knockout != 0).
+ * PCA: "pca_flush_rows" (rows a tensor-core FP32 accumulator holds before it is added into the next level, default 256:
+ * its truncating adds cost 4e-9 of a diagonal entry per row), "pca_promote" (such segments per promotion to FP64,
+ * default 16), "pca_rows" (rows per stage on the diagonal panels, 64 or 32), "pca_ls" / "pca_hs" (landing / operand
+ * ring depths, even, 0 = default), and the diagnostics "pca_role_prof", "pca_knockout", "pca_desc_swap". */
 int kmb200_set_option(const char *name, double value);
 
 /* ---- cluster sizes without any device allocation ------------------------------------------------
