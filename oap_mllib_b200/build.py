@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libkmeans_b200.so")
-SOURCES = ["kmb200.cu", "jni_shim.cpp"]
+SOURCES = ["kmb200.cu", "jni_shim.cpp", "sym_eig.cpp"]
 DEPS = ["assign_tc.cuh", "assign_tc2.cuh", "assign_pair_ss.cuh", "assign_pair_h16.cuh", "fused_smallk.cuh", "gram_pair.cuh", "sym_eig.h", "pca_host.inl", "kernels_misc.cuh", "ptx_sm100.cuh", "jni_min.h", "../../include/kmb200.h"]
 
 
