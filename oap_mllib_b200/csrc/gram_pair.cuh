@@ -389,7 +389,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
                     __syncwarp();
                     if (lane == 0) {
                         if (leader) mbar_arrive(&acc_empty[h]);
-                        else mbar_arrive_remote(&acc_empty[h], 0);
+                        else mbar_arrive_remote_relaxed(&acc_empty[h], 0);   // (TMEM reads: ordered by the tcgen05 fence, no memory to publish)
                     }
                 }
 #pragma unroll

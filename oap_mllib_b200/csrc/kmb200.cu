@@ -442,11 +442,13 @@ static int table_stats_append(kmb200_table *t, int64_t row0, int64_t nrows) {
         t->stats_ok = true;
     }
     if (!t->stats_ok) return 0;
-    if (row0 != t->stats_rows) {
+    const int ld = t->ld;
+    // out of order -> recompute at the PCA call; so do appends of a few rows at a time (three launches per append
+    // would cost more than the one pass they save)
+    if (row0 != t->stats_rows || (!reset && (size_t)nrows * ld * sizeof(float) < (size_t)64 * 1024)) {
         t->stats_ok = false;
         return 0;
     }
-    const int ld = t->ld;
     if (!t->colsum) {
         CU_TRY(cudaMalloc(&t->colsum, ((size_t)ld + 1) * sizeof(double)));
         CU_TRY(cudaMalloc(&t->colmax, (size_t)ld * sizeof(float)));
