@@ -67,6 +67,7 @@ struct GramParams {
     int32_t flush_stages;   // stages per level-1 segment
     int32_t promote_segs;   // level-1 segments per level-3 promotion
     int32_t colA0, colB0;   // first column of the A / B panel (multiples of 256)
+    int32_t split;          // d <= 128 (diagonal panel only): the two CTAs of a pair take DIFFERENT stages, see the kernel
     int32_t desc_swap;      // debugging: exchange LBO and SBO in the operand descriptors
     long long *prof;        // optional cycle counters of pair 0's roles (diagnostics), else nullptr
     int32_t knockout;       // timing experiments (results invalid): 1 = no MMAs, 2 = no conversion, 4 = no level-2 / level-3 work, 8 = no TMA
@@ -171,7 +172,12 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
     const int st1 = (int)((long long)p.stages_total * (pair + 1) / pairs);
     const int nst = st1 - st0;
     const int FS = p.flush_stages;
-    const int colA = p.colA0 + (int)rank * kGramStrip, colB = p.colB0 + (int)rank * kGramStrip;
+    // p.split (tables of at most 128 columns): with one strip the second CTA of a pair would only see padding.  Instead
+    // both CTAs take columns [0, 128) of DIFFERENT stages (2 g and 2 g + 1).  The pair's MMA then produces
+    // [A0^T B0 | A0^T B1] in CTA 0's lanes and [A1^T B0 | A1^T B1] in CTA 1's: the blocks on the diagonal are the two
+    // stages' Gram matrices, the cross blocks are never read -- twice the rows per unit of tensor work.
+    const int split = SAME ? p.split : 0;
+    const int colA = p.colA0 + (split ? 0 : (int)rank * kGramStrip), colB = p.colB0 + (int)rank * kGramStrip;
 
     if (threadIdx.x < STRIPS * kGramStrip) {
         const int s = threadIdx.x / kGramStrip, c = threadIdx.x % kGramStrip;
@@ -219,7 +225,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
                 } else {
                     mbar_arrive_expect_tx(&land_full[s], STRIPS * 4 * kGramLandBytes);
                     uint8_t *dst = land + s * STRIPS * 4 * kGramLandBytes;
-                    const int row = (st0 + g) * kGramRows;
+                    const int row = (split ? 2 * (st0 + g) + (int)rank : st0 + g) * kGramRows;
 #pragma unroll
                     for (int b = 0; b < 4; ++b) tma_load_2d_hint(&tm_x, &land_full[s], dst + b * kGramLandBytes, colA + 32 * b, row, evict_first);
                     if constexpr (!SAME) {
@@ -305,7 +311,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
         long long t_land = 0, t_free = 0, t_fence = 0, t0 = clock64();
         for (int g = grp; g < nst; g += 2) {
             const uint32_t ls = g % kGramLS, lph = (g / kGramLS) & 1, hs = g % kGramHS;
-            const int rows_left = p.n_rows - (st0 + g) * kGramRows;   // rows of this stage inside the table
+            const int rows_left = p.n_rows - (split ? 2 * (st0 + g) + (int)rank : st0 + g) * kGramRows;   // rows of this stage inside the table
             const bool full = rows_left >= kGramRows;
             long long tm = prof ? clock64() : 0;
             mbar_wait_parked(&land_full[ls], lph);
@@ -379,12 +385,21 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
             const bool promote = (seg + 1) % p.promote_segs == 0 || seg + 1 == nseg;
             const bool fresh = seg % p.promote_segs == 0;   // level 2 was cleared (or never written)
 #pragma unroll 1
-            for (int ch = (p.knockout & 4) ? 3 : 0; ch < 4; ++ch) {
+            const int ch0 = (p.knockout & 4) ? 3 : split ? 2 * (int)rank : 0, ch1 = split ? 2 * (int)rank + 2 : 4;
+            if ((p.knockout & 4) && ch0 >= ch1) {   // (knock-out, nothing to read: release only)
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if (leader) mbar_arrive(&acc_empty[h]);
+                    else mbar_arrive_remote_relaxed(&acc_empty[h], 0);
+                }
+            }
+            for (int ch = ch0; ch < ch1; ++ch) {
                 uint32_t a[32], b[32];
                 tmem_ld32(l1 + ch * 32, a);
                 if (!fresh) tmem_ld32(l2 + ch * 32, b);
                 tmem_wait_ld();
-                if (ch == 3) {   // level 1 has been read: the MMAs of the next segment may overwrite it
+                if (ch == ch1 - 1) {   // level 1 has been read: the MMAs of the next segment may overwrite it
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) {
@@ -543,21 +558,26 @@ __global__ void pca_prep_kernel(const double *__restrict__ gsum, const float *__
 }
 // G[i][j] (i in the A panel, j in the B panel) = inv_i inv_j * sum over pairs of P[pair][j][i]; written into the full
 // [ld x ld] matrix (and mirrored, so that the panel pairs above the diagonal fill the whole matrix).  Fixed order.
+// split: the pair's two stages left their sums in the blocks (0, 0) and (1, 1) of P (see the kernel).
 __global__ void gram_reduce_kernel(const double *__restrict__ partial, int pairs, const double *__restrict__ inv, int ld, int colA0,
-                                   int colB0, double *__restrict__ G) {
+                                   int colB0, int split, double *__restrict__ G) {
     const int m = blockIdx.x * blockDim.x + threadIdx.x;   // 0..255: lanes contiguous in P
     const int nn = blockIdx.y;                             // 0..255
     const int i = colA0 + m, j = colB0 + nn;
     if (m >= 256 || i >= ld || j >= ld) return;
-    double a = 0.0;
-    for (int q = 0; q < pairs; ++q) a += partial[(size_t)q * 65536 + (size_t)nn * 256 + m];
-    a *= inv[i] * inv[j];
+    auto entry = [&](int r, int c) {   // sum over the pairs of P[c][r] (and of the second stage's block)
+        double a = 0.0;
+        for (int q = 0; q < pairs; ++q) {
+            a += partial[(size_t)q * 65536 + (size_t)c * 256 + r];
+            if (split) a += partial[(size_t)q * 65536 + (size_t)(128 + c) * 256 + 128 + r];
+        }
+        return a * (inv[i] * inv[j]);
+    };
+    const double a = entry(m, nn);
     if (colA0 == colB0) {
-        // diagonal panel: entry (i, j) and (j, i) of the product differ only in the order of the FP32 additions: average
-        double b = 0.0;
-        for (int q = 0; q < pairs; ++q) b += partial[(size_t)q * 65536 + (size_t)m * 256 + nn];
-        b *= inv[i] * inv[j];
-        G[(size_t)i * ld + j] = 0.5 * (a + b);
+        // diagonal panel: entry (i, j) and (j, i) of the product differ only in the order of the FP32 additions (and, with
+        // two products, A = H^T (2 L) + H^T H is only half of the sum): average
+        G[(size_t)i * ld + j] = 0.5 * (a + entry(nn, m));
     } else {
         G[(size_t)i * ld + j] = a;
         G[(size_t)j * ld + i] = a;

@@ -2261,6 +2261,8 @@ extern "C" int kmb200_set_option(const char *name, double value) {
         (name[4] == 'l' ? g_pca_ls : g_pca_hs) = v;
     } else if (!strcmp(name, "pca_role_prof")) {
         g_pca_role_prof = value != 0;
+    } else if (!strcmp(name, "pca_split")) {
+        g_pca_split = value != 0;
     } else if (!strcmp(name, "pca_rows")) {
         g_pca_rows = value == 32 ? 32 : 64;
     } else if (!strcmp(name, "pca_knockout")) {

@@ -12,6 +12,7 @@
 static int g_pca_flush_rows = 256;   // rows a level-1 (tensor core, FP32) accumulator holds ("pca_flush_rows")
 static int g_pca_promote = 16;        // level-1 segments per promotion of the level-2 sums to FP64 ("pca_promote")
 static int g_pca_desc_swap = 0;       // debugging ("pca_desc_swap")
+static int g_pca_split = 1;           // d <= 128: the CTAs of a pair take different stages ("pca_split")
 static int g_pca_rows = 64;           // rows per stage on the diagonal panels, 64 or 32 ("pca_rows")
 static int g_pca_ls = 0, g_pca_hs = 0;   // ring depths ("pca_ls", "pca_hs"; 0 = default, even, <= 8)
 static int g_pca_role_prof = 0;       // diagnostics ("pca_role_prof"): print pair 0's role cycle counters to stderr
@@ -27,7 +28,8 @@ static int pca_gram(kmb200_table *t, kmb200_comm *comm, int center, std::vector<
     const int world = comm ? comm->world : 1;
     cudaStream_t st = t->stream;
     const int Rd = g_pca_rows == 32 ? 32 : 64;   // rows per stage on the diagonal panels
-    const int64_t min_stages = (n + Rd - 1) / Rd;
+    const int split = (g_pca_split && ld <= 128) ? 1 : 0;
+    const int64_t min_stages = (n + Rd * (1 + split) - 1) / (Rd * (1 + split));
     const int pairs = (int)std::max<int64_t>(1, std::min<int64_t>(min_stages, t->num_sms / 2));
     if (t->pca && t->pca->pairs < pairs) {   // (the table was longer when they were sized)
         delete t->pca;
@@ -115,7 +117,8 @@ static int pca_gram(kmb200_table *t, kmb200_comm *comm, int center, std::vector<
             size_t cfg_smem = 0;
             p.colA0 = I * 256;
             p.colB0 = J * 256;
-            p.stages_total = (int32_t)((n + R - 1) / R);
+            p.split = split;
+            p.stages_total = (int32_t)((n + R * (1 + split) - 1) / (R * (1 + split)));
             p.flush_stages = std::max(1, g_pca_flush_rows / R);
             int ls = 0, hs = 0;
             gram_default_rings(I == J, R, &ls, &hs);
@@ -157,7 +160,7 @@ static int pca_gram(kmb200_table *t, kmb200_comm *comm, int center, std::vector<
                         fprintf(stderr, "[gram roles] transform cta %d group %d: total %lld wait-landing %lld wait-operand-slot %lld fence+arrive %lld\n", c, g,
                                 h[16 + 8 * c + 4 * g], h[17 + 8 * c + 4 * g], h[18 + 8 * c + 4 * g], h[19 + 8 * c + 4 * g]);
             }
-            gram_reduce_kernel<<<dim3(1, 256), 256, 0, st>>>(partial, pairs, inv, ld, p.colA0, p.colB0, G);
+            gram_reduce_kernel<<<dim3(1, 256), 256, 0, st>>>(partial, pairs, inv, ld, p.colA0, p.colB0, split, G);
             KM_TRY(post_launch(__LINE__));
             g_prof.kernel_launches += 2;
         }
