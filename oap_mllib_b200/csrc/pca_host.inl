@@ -119,7 +119,8 @@ static int pca_gram(kmb200_table *t, kmb200_comm *comm, int center, std::vector<
             p.colB0 = J * 256;
             p.split = split;
             p.stages_total = (int32_t)((n + R * (1 + split) - 1) / (R * (1 + split)));
-            p.flush_stages = std::max(1, g_pca_flush_rows / R);
+            // (three products off the diagonal panels: 3/2 of the adds per row, so 2/3 of the rows per segment)
+            p.flush_stages = std::max(1, (I == J ? g_pca_flush_rows : g_pca_flush_rows * 2 / 3) / R);
             int ls = 0, hs = 0;
             gram_default_rings(I == J, R, &ls, &hs);
             if (g_pca_ls > 0) ls = g_pca_ls;

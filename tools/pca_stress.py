@@ -81,7 +81,9 @@ def main():
         sc[sc == 0] = 1.0
         err = float((np.abs(g - g_ref) / sc).max())
         worst = max(worst, err)
-        if not (err <= 2e-6 and cnt == n):
+        # (without centring, a column whose mean dwarfs its spread has the SAME split residual in every row: the 2^-22
+        #  terms then add up instead of averaging out)
+        if not (err <= (2e-6 if center else 4e-6) and cnt == n):
             print(f"[pca stress] shape {n} x {dd} center={center}: error {err:.3e}", flush=True)
             sys.exit(1)
         done += 1
