@@ -448,6 +448,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS) + ["PCA"])
     ap.add_argument("--rows", type=int, default=0, help="override the total row count (debugging)")
+    ap.add_argument("--pca-d", type=int, default=0, help="--workload PCA: columns of the table (default 256; other shapes are not the bench line)")
     ap.add_argument("--centre-range", type=float, default=10.0,
                     help="blob centres ~ U(-R, R)^d with unit noise: 10 = BASELINE's well-separated blobs, 1 = heavy overlap")
     ap.add_argument("--e2e-rows", type=int, default=0)

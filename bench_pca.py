@@ -27,7 +27,9 @@ DESC = "PCA synthetic dense 100Mx256 fp32 (C3's table), all 256 components, colu
 
 
 def config(args, world, rows):
-    return {"workload": DESC, "rows_total": rows, "rows_per_gpu": rows // world, "d": D, "k": D,
+    d = getattr(args, "pca_d", 0) or D
+    desc = DESC if (d == D and rows == ROWS) else f"PCA synthetic dense {rows}x{d} fp32 (NOT the bench configuration), all {d} components"
+    return {"workload": desc, "rows_total": rows, "rows_per_gpu": rows // world, "d": d, "k": d,
             "parallelism": f"rows sharded over {world} GPU(s), one NCCL all-reduce of the column statistics and one of the d x d Gram matrix per fit",
             "l2": "inputs (rows_per_gpu*d*4 bytes) far larger than the 126 MB L2; no flush needed",
             "data": f"Gaussian blobs, sigma = 1, 1000 centres ~ U(-{args.centre_range:g}, {args.centre_range:g})^d"}
@@ -101,7 +103,7 @@ def run_ours(args, rank, local_rank, world, B):
     from oap_mllib_b200 import _lib
     from oap_mllib_b200.sharding import shard_bounds
     rows = args.rows or ROWS
-    d = D
+    d = getattr(args, "pca_d", 0) or D
     torch.cuda.set_device(local_rank)
     _lib.check(m.lib().kmb200_set_device(local_rank))
     for opt in args.option:
@@ -178,8 +180,8 @@ def run_ours(args, rank, local_rank, world, B):
                 "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_flops_per_launch": flops_per_launch,
                 "kernel_ms_per_launch": gram_ms,
                 "algorithmic_tflops": flops_per_launch / (gram_ms * 1e-3) / 1e12,
-                "executed_tflops": 2.0 * flops_per_launch / (gram_ms * 1e-3) / 1e12,
-                "executed_frac_of_fp16_sustained": 2.0 * flops_per_launch / (gram_ms * 1e-3) / 1e12 / peaks["bf16_sustained"],
+                "executed_tflops": 2.0 * flops_per_launch / (gram_ms * 1e-3) / 1e12 if d == 256 else None,
+                "executed_frac_of_fp16_sustained": 2.0 * flops_per_launch / (gram_ms * 1e-3) / 1e12 / peaks["bf16_sustained"] if d == 256 else None,
                 "why_hbm": "2 n d^2 flops at the FP16 rate take less time than 4 n d bytes at HBM bandwidth for d = 256; the kernel executes "
                            "two FP16 products per term (FP64-faithful split), see executed_tflops",
                 "step_gbytes_per_s_per_gpu": bytes_per_launch / (ms_per_step * 1e-3) / 1e9,
