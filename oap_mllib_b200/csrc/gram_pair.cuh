@@ -67,7 +67,8 @@ struct GramParams {
     int32_t flush_stages;   // stages per level-1 segment
     int32_t promote_segs;   // level-1 segments per level-3 promotion
     int32_t colA0, colB0;   // first column of the A / B panel (multiples of 256)
-    int32_t split;          // d <= 128 (diagonal panel only): the two CTAs of a pair take DIFFERENT stages, see the kernel
+    int32_t split;          // diagonal panel of a narrow table: 1 (d <= 128) = the two CTAs of a pair take DIFFERENT stages,
+                            // 2 (d <= 64) = and each CTA two of them, side by side in its strip; see the kernel
     int32_t desc_swap;      // debugging: exchange LBO and SBO in the operand descriptors
     long long *prof;        // optional cycle counters of pair 0's roles (diagnostics), else nullptr
     int32_t knockout;       // timing experiments (results invalid): 1 = no MMAs, 2 = no conversion, 4 = no level-2 / level-3 work, 8 = no TMA
@@ -175,8 +176,12 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
     // p.split (tables of at most 128 columns): with one strip the second CTA of a pair would only see padding.  Instead
     // both CTAs take columns [0, 128) of DIFFERENT stages (2 g and 2 g + 1).  The pair's MMA then produces
     // [A0^T B0 | A0^T B1] in CTA 0's lanes and [A1^T B0 | A1^T B1] in CTA 1's: the blocks on the diagonal are the two
-    // stages' Gram matrices, the cross blocks are never read -- twice the rows per unit of tensor work.
+    // stages' Gram matrices, the cross blocks are never read -- twice the rows per unit of tensor work.  split == 2
+    // (at most 64 columns): each CTA also puts TWO stages side by side in its strip (sub-tile s = columns [0, 64) of its
+    // stage s), four stages per pair; the useful blocks are then the four 64 x 64 ones on the diagonal.
     const int split = SAME ? p.split : 0;
+    const int PS = 1 << split, CS = split == 2 ? 2 : 1;   // stages per pair and step, stages per CTA and step
+    auto stage_of = [&](int g, int sub) { return (st0 + g) * PS + (split ? (int)rank * CS : 0) + sub; };
     const int colA = p.colA0 + (split ? 0 : (int)rank * kGramStrip), colB = p.colB0 + (int)rank * kGramStrip;
 
     if (threadIdx.x < STRIPS * kGramStrip) {
@@ -225,9 +230,12 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
                 } else {
                     mbar_arrive_expect_tx(&land_full[s], STRIPS * 4 * kGramLandBytes);
                     uint8_t *dst = land + s * STRIPS * 4 * kGramLandBytes;
-                    const int row = (split ? 2 * (st0 + g) + (int)rank : st0 + g) * kGramRows;
+                    const int row = stage_of(g, 0) * kGramRows;
 #pragma unroll
-                    for (int b = 0; b < 4; ++b) tma_load_2d_hint(&tm_x, &land_full[s], dst + b * kGramLandBytes, colA + 32 * b, row, evict_first);
+                    for (int b = 0; b < 4; ++b) {
+                        if (split == 2) tma_load_2d_hint(&tm_x, &land_full[s], dst + b * kGramLandBytes, colA + 32 * (b & 1), stage_of(g, b >> 1) * kGramRows, evict_first);
+                        else tma_load_2d_hint(&tm_x, &land_full[s], dst + b * kGramLandBytes, colA + 32 * b, row, evict_first);
+                    }
                     if constexpr (!SAME) {
 #pragma unroll
                         for (int b = 0; b < 4; ++b)
@@ -303,15 +311,16 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
         for (int s = 0; s < STRIPS; ++s)
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                sc[s][j] = col_s[s * kGramStrip + box * 32 + q * 8 + j];
-                of[s][j] = col_s[STRIPS * kGramStrip + s * kGramStrip + box * 32 + q * 8 + j];
+                const int cpos = (split == 2 ? (box & 1) : box) * 32 + q * 8 + j;   // column of the strip this value belongs to
+                sc[s][j] = col_s[s * kGramStrip + cpos];
+                of[s][j] = col_s[STRIPS * kGramStrip + s * kGramStrip + cpos];
             }
         const uint32_t sub = box >> 1, chunk = (box & 1) * 4 + q;
         const bool prof = p.prof != nullptr && blockIdx.x < 2 && box == 0;
         long long t_land = 0, t_free = 0, t_fence = 0, t0 = clock64();
         for (int g = grp; g < nst; g += 2) {
             const uint32_t ls = g % kGramLS, lph = (g / kGramLS) & 1, hs = g % kGramHS;
-            const int rows_left = p.n_rows - (split ? 2 * (st0 + g) + (int)rank : st0 + g) * kGramRows;   // rows of this stage inside the table
+            const int rows_left = p.n_rows - stage_of(g, split == 2 ? box >> 1 : 0) * kGramRows;   // rows of this warp's stage inside the table
             const bool full = rows_left >= kGramRows;
             long long tm = prof ? clock64() : 0;
             mbar_wait_parked(&land_full[ls], lph);
@@ -384,9 +393,11 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
             tc_fence_after();
             const bool promote = (seg + 1) % p.promote_segs == 0 || seg + 1 == nseg;
             const bool fresh = seg % p.promote_segs == 0;   // level 2 was cleared (or never written)
-#pragma unroll 1
-            const int ch0 = (p.knockout & 4) ? 3 : split ? 2 * (int)rank : 0, ch1 = split ? 2 * (int)rank + 2 : 4;
-            if ((p.knockout & 4) && ch0 >= ch1) {   // (knock-out, nothing to read: release only)
+            // split: only the diagonal blocks are read (columns from this CTA's own B; split == 2: and only by the lane
+            // half whose rows belong to column half h)
+            const bool useful = split != 2 || (qd >> 1) == h;
+            const int ch0 = (p.knockout & 4) ? 3 : split ? 2 * (int)rank : 0, ch1 = !useful ? 0 : split ? 2 * (int)rank + 2 : 4;
+            if (ch0 >= ch1) {   // nothing to read: release only
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
@@ -394,6 +405,7 @@ gram_pair_kernel(const __grid_constant__ CUtensorMap tm_x, const GramParams p) {
                     else mbar_arrive_remote_relaxed(&acc_empty[h], 0);
                 }
             }
+#pragma unroll 1
             for (int ch = ch0; ch < ch1; ++ch) {
                 uint32_t a[32], b[32];
                 tmem_ld32(l1 + ch * 32, a);
@@ -558,7 +570,7 @@ __global__ void pca_prep_kernel(const double *__restrict__ gsum, const float *__
 }
 // G[i][j] (i in the A panel, j in the B panel) = inv_i inv_j * sum over pairs of P[pair][j][i]; written into the full
 // [ld x ld] matrix (and mirrored, so that the panel pairs above the diagonal fill the whole matrix).  Fixed order.
-// split: the pair's two stages left their sums in the blocks (0, 0) and (1, 1) of P (see the kernel).
+// split: the pair's two (four) stages left their sums in the 128 x 128 (64 x 64) blocks on the diagonal of P (see the kernel).
 __global__ void gram_reduce_kernel(const double *__restrict__ partial, int pairs, const double *__restrict__ inv, int ld, int colA0,
                                    int colB0, int split, double *__restrict__ G) {
     const int m = blockIdx.x * blockDim.x + threadIdx.x;   // 0..255: lanes contiguous in P
@@ -569,7 +581,9 @@ __global__ void gram_reduce_kernel(const double *__restrict__ partial, int pairs
         double a = 0.0;
         for (int q = 0; q < pairs; ++q) {
             a += partial[(size_t)q * 65536 + (size_t)c * 256 + r];
-            if (split) a += partial[(size_t)q * 65536 + (size_t)(128 + c) * 256 + 128 + r];
+            if (split == 1) a += partial[(size_t)q * 65536 + (size_t)(128 + c) * 256 + 128 + r];
+            if (split == 2)
+                for (int b = 1; b < 4; ++b) a += partial[(size_t)q * 65536 + (size_t)(64 * b + c) * 256 + 64 * b + r];
         }
         return a * (inv[i] * inv[j]);
     };

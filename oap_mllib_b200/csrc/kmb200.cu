@@ -2262,7 +2262,7 @@ extern "C" int kmb200_set_option(const char *name, double value) {
     } else if (!strcmp(name, "pca_role_prof")) {
         g_pca_role_prof = value != 0;
     } else if (!strcmp(name, "pca_split")) {
-        g_pca_split = value != 0;
+        g_pca_split = value < 0 ? 0 : value > 2 ? 2 : (int)value;
     } else if (!strcmp(name, "pca_rows")) {
         g_pca_rows = value == 32 ? 32 : 64;
     } else if (!strcmp(name, "pca_knockout")) {

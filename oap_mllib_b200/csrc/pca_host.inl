@@ -12,7 +12,8 @@
 static int g_pca_flush_rows = 256;   // rows a level-1 (tensor core, FP32) accumulator holds ("pca_flush_rows")
 static int g_pca_promote = 16;        // level-1 segments per promotion of the level-2 sums to FP64 ("pca_promote")
 static int g_pca_desc_swap = 0;       // debugging ("pca_desc_swap")
-static int g_pca_split = 1;           // d <= 128: the CTAs of a pair take different stages ("pca_split")
+static int g_pca_split = 2;           // narrow tables: 0 = off, 1 = the CTAs of a pair take different stages (d <= 128), 2 = and two
+                                      // stages per CTA for d <= 64 ("pca_split")
 static int g_pca_rows = 64;           // rows per stage on the diagonal panels, 64 or 32 ("pca_rows")
 static int g_pca_ls = 0, g_pca_hs = 0;   // ring depths ("pca_ls", "pca_hs"; 0 = default, even, <= 8)
 static int g_pca_role_prof = 0;       // diagnostics ("pca_role_prof"): print pair 0's role cycle counters to stderr
@@ -28,8 +29,8 @@ static int pca_gram(kmb200_table *t, kmb200_comm *comm, int center, std::vector<
     const int world = comm ? comm->world : 1;
     cudaStream_t st = t->stream;
     const int Rd = g_pca_rows == 32 ? 32 : 64;   // rows per stage on the diagonal panels
-    const int split = (g_pca_split && ld <= 128) ? 1 : 0;
-    const int64_t min_stages = (n + Rd * (1 + split) - 1) / (Rd * (1 + split));
+    const int split = !g_pca_split ? 0 : ld <= 64 ? std::min(g_pca_split, 2) : ld <= 128 ? 1 : 0;   // stages per pair and step: 1 << split
+    const int64_t min_stages = (n + (Rd << split) - 1) / (Rd << split);
     const int pairs = (int)std::max<int64_t>(1, std::min<int64_t>(min_stages, t->num_sms / 2));
     if (t->pca && t->pca->pairs < pairs) {   // (the table was longer when they were sized)
         delete t->pca;
@@ -118,7 +119,7 @@ static int pca_gram(kmb200_table *t, kmb200_comm *comm, int center, std::vector<
             p.colA0 = I * 256;
             p.colB0 = J * 256;
             p.split = split;
-            p.stages_total = (int32_t)((n + R * (1 + split) - 1) / (R * (1 + split)));
+            p.stages_total = (int32_t)((n + ((int64_t)R << split) - 1) / ((int64_t)R << split));
             // (three products off the diagonal panels: 3/2 of the adds per row, so 2/3 of the rows per segment)
             p.flush_stages = std::max(1, (I == J ? g_pca_flush_rows : g_pca_flush_rows * 2 / 3) / R);
             int ls = 0, hs = 0;

@@ -104,17 +104,17 @@ def test_long_table_accumulation(m, center):
     check_against_oracle(m, [X[:70_001], X[70_001:70_002], X[70_002:]], center=center)
 
 
-@pytest.mark.parametrize("n,d", [(100_000, 128), (70_001, 64), (50_000, 33)])
+@pytest.mark.parametrize("n,d", [(100_000, 128), (70_001, 64), (50_000, 33), (90_003, 32), (60_000, 7)])
 def test_narrow_tables_with_and_without_the_row_split(m, n, d):
-    """d <= 128: the two CTAs of a pair take different stages (default) or, with "pca_split" = 0, the same stage with the
-    second CTA on padding columns; both against the oracle, odd and even numbers of stages."""
+    """d <= 128: the two CTAs of a pair take different stages; d <= 64: and two stages each, side by side in the strip
+    (default, "pca_split" = 2); with 1 / 0 only the first / neither.  All against the oracle, ragged numbers of stages."""
     X = decaying_table(n, d, seed=n)
     try:
-        for split in (1.0, 0.0):
+        for split in (2.0, 1.0, 0.0):
             m._lib.check(m.lib().kmb200_set_option(b"pca_split", split))
             check_against_oracle(m, [X])
     finally:
-        m._lib.check(m.lib().kmb200_set_option(b"pca_split", 1.0))
+        m._lib.check(m.lib().kmb200_set_option(b"pca_split", 2.0))
 
 
 def test_column_scales_spread_over_30_orders(m):
