@@ -307,6 +307,21 @@ def _jni_rank(rank, world, lib_path, q_id, q_out):
             and np.allclose(got, want_c, rtol=1e-5, atol=1e-5)
     else:
         ok = ok and out == 0
+    # the PCA native on the same tables and communicator (section 8 row f4): the result fields are set on rank 0 only
+    from oracle import pca_oracle as po
+    pca = fn(h, "Java_org_apache_spark_ml_feature_PCADALImpl_cPCATrainDALCentered", C.c_int64,
+             [P, P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, P])
+    pres = vm.new(object())
+    ok = ok and pca(vm.env, None, table, 3, world, 1, pres) == 0 and not vm.thrown
+    if rank == 0:
+        f = vm.fields[pres]
+        axes = vm.objs[get_cent(vm.env, None, f["pcNumericTable"])].reshape(d, d)
+        ev = vm.objs[get_cent(vm.env, None, f["explainedVarianceNumericTable"])]
+        X32 = X.astype(np.float32)
+        ev_ref, axes_ref = po.pca_svd_dense([X32[(n * r) // world:(n * (r + 1)) // world] for r in range(world)])
+        ok = ok and np.abs(ev - ev_ref).max() <= 2e-6 * ev_ref[0] and np.abs(axes[:3] - axes_ref[:3]).max() <= 1e-6
+    else:
+        ok = ok and pres not in vm.fields
     cleanup(vm.env, None)
     q_out.put((rank, bool(ok), vm.thrown))
 
@@ -314,7 +329,7 @@ def _jni_rank(rank, world, lib_path, q_id, q_out):
 @pytest.mark.gpu
 def test_jni_two_executors_rendezvous_and_fit(built_lib):
     """Two executor processes, one GPU each: c_setDevice, c_getUniqueId on rank 0 (the bytes travel to rank 1 the way
-    the Spark closure would carry them), c_init(size = 2), the collective compute native, c_cleanup."""
+    the Spark closure would carry them), c_init(size = 2), the collective compute natives (K-means, then PCA), c_cleanup."""
     import multiprocessing as mp
 
     import oap_mllib_b200 as m
