@@ -8,7 +8,8 @@
 //   (diagonal panels: A = H^T (2 L) + H^T H and G^ = (A + A^T) / 2 -- two products)
 //
 // One CTA pair (tcgen05 cta_group::2) owns a 256-column panel pair (A columns [colA0, colA0 + 256) x B columns
-// [colB0, colB0 + 256)) and a contiguous range of 32-row stages; M = 256 output rows are split over the pair (CTA r:
+// [colB0, colB0 + 256)) and a contiguous range of R-row stages (R = 64 on the diagonal, 32 off it); M = 256 output rows
+// are split over the pair (CTA r:
 // A columns colA0 + 128 r ...), and so are the N = 256 output columns of the B operand (CTA r supplies B columns
 // colB0 + 128 r ... from its own shared memory).  On the diagonal (colA0 == colB0) A and B are the SAME shared-memory
 // image, so every CTA reads only its own 128-column strip of X and the table is read from HBM once.
@@ -16,14 +17,14 @@
 // Both operands are "MN-major": the contraction index is the table ROW, and a row-major [rows][columns] tile has the
 // M / N index contiguous.  That is exactly the image a transform warp gets by converting the TMA-landed FP32 tile in
 // place -- no transpose anywhere:
-//   landing tile   [32 rows][32 floats], 128-byte swizzle (TMA)           4 per strip and stage
-//   operand tiles  H, L: [2 sub-tiles][32 rows][64 halves], 128-byte swizzle:  canonical MN-major SW128 layout
-//                  ((8,8,2),(8,k)) : ((1,8,LBO),(64,SBO)) halves with LBO = 4096 B (next 64 columns), SBO = 1024 B
+//   landing tile   [R rows][32 floats], 128-byte swizzle (TMA)           4 per strip and stage
+//   operand tiles  H, L: [2 sub-tiles][R rows][64 halves], 128-byte swizzle:  canonical MN-major SW128 layout
+//                  ((8,8,2),(8,k)) : ((1,8,LBO),(64,SBO)) halves with LBO = 128 R bytes (next 64 columns), SBO = 1024 B
 //                  (next 8 rows); a K = 16 step advances the start address by 2048 B.
 //
 // Accumulation in three levels.  The tensor core adds into FP32 and TRUNCATES: measured on this kernel, the diagonal of G
 // comes out low by 6e-9 of itself per accumulated row (1.5e-6 after 256 rows, 1.5e-5 after 2048), so
-//   level 1  a TMEM accumulator only ever holds `flush_stages * 32` rows (default 128);
+//   level 1  a TMEM accumulator only ever holds `flush_stages * R` rows (default 256; 160 with three products);
 //   level 2  the flush warps then add it (FP32, round to nearest: no drift) into a second TMEM array;
 //   level 3  every `promote_segs` segments that one is added into this pair's FP64 partial in global memory
 //            (P[n][m], 256 x 256, lanes contiguous; no other writer: plain read-modify-write) and cleared.
@@ -33,8 +34,8 @@
 // is being drained (TMEM reads run at 64 B / cycle: about 2000 cycles per drain) the tensor pipe works on the other.
 //
 // Warp roles (608 threads): 0-7 flush (warp & 3 = TMEM lane quarter, warp >> 2 = column half), 8-15 transform (two
-// groups of four; sixteen warps ran slower), 16 TMA producer, 17 / 18 MMA issuers of half 0 / 1 (leader CTA).  Barriers: every ring is a plain full / free pair whose
-// waiters wait for EVERY use in order (see the parity rule in assign_pair_h16.cuh):
+// groups of four; sixteen warps ran slower), 16 TMA producer, 17 / 18 MMA issuers of half 0 / 1 (leader CTA).  Barriers:
+// every ring is a plain full / free pair whose waiters wait for EVERY use in order (see the parity rule in assign_pair_h16.cuh):
 //   land_full[LS] (tx) / land_free[LS] (the 4 transform warps of the stage's group)           per CTA
 //   hl_full[HS] (leader: 4 local + 4 remote transform warps; both issuers wait) / hl_free[HS] (both issuers' multicast commits)
 //   acc_full[half] (multicast commit) / acc_empty[half] (leader: 4 local + 4 remote flush warps)
