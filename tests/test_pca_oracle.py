@@ -9,10 +9,14 @@ import pytest
 
 from oracle import pca_oracle as po
 
-FIXTURE = np.array([[0.0, 1.0, 0.0, 7.0, 0.0], [2.0, 0.0, 3.0, 4.0, 5.0], [4.0, 0.0, 0.0, 6.0, 7.0]])
-SPARK_PROJECTION = np.array([[1.6485728230883807, -4.013282700516296], [-4.645104331781534, -1.1167972663619026],
-                             [-6.428880535676489, -5.337951427775355]])
-SPARK_EXPLAINED = np.array([0.7943932532230531, 0.20560674677694699])
+import json
+import os
+
+with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pca_fixture.json")) as _f:
+    _FX = json.load(_f)
+FIXTURE = np.array(_FX["rows"])
+SPARK_PROJECTION = np.array(_FX["spark_projection_first_two_axes"])
+SPARK_EXPLAINED = np.array(_FX["spark_explained_variance_first_two"])
 
 
 @pytest.mark.parametrize("route", ["svd_dense", "gram"])
