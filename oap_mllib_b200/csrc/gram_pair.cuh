@@ -53,8 +53,8 @@ constexpr int kGramStrip = 128;                     // columns per CTA
 // wait + commit in each issuer, so the rows per stage are what amortises them (measured with the knock-outs of
 // tools/pca_check.py: at R = 32 the barrier skeleton alone, without any load, conversion or MMA, ran 40 % as long as the
 // whole kernel).  Landing / operand ring depths are EVEN: the two transform groups take the even / the odd stages, and
-// a ring slot must always be consumed by the same group (parity rule).
-// (p.ls, p.hs; defaults gram_default_rings)
+// a ring slot must always be consumed by the same group (parity rule); they are launch parameters (p.ls, p.hs;
+// defaults: gram_default_rings).
 constexpr int kGramMaxRing = 8;
 constexpr int kGramMaxBars = 4 * kGramMaxRing + 4;
 
@@ -63,7 +63,7 @@ struct GramParams {
     const float *offs;      // [ld2] -mu_c s_c
     double *partial;        // [pairs][256 n][256 m]
     int32_t n_rows;         // rows of the table
-    int32_t stages_total;   // ceil(n_rows / 32)
+    int32_t stages_total;   // steps over all pairs: ceil(n_rows / (R << split))
     int32_t ls, hs;         // landing / operand ring depths (even, <= 8)
     int32_t flush_stages;   // stages per level-1 segment
     int32_t promote_segs;   // level-1 segments per level-3 promotion
