@@ -44,7 +44,13 @@ def test_jni_symbols_exported(built_lib):
               "Java_org_apache_spark_ml_util_OneCCL_00024_c_1cleanup",
               "Java_org_apache_spark_ml_util_OneCCL_00024_isRoot",
               "Java_org_apache_spark_ml_util_OneCCL_00024_rankID",
-              "Java_org_apache_spark_ml_util_OneCCL_00024_setEnv"]:
+              "Java_org_apache_spark_ml_util_OneCCL_00024_setEnv",
+              "Java_org_apache_spark_ml_util_OneCCL_00024_c_1setDevice",
+              "Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansDALAssign",
+              "Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansInitCosts",
+              "Java_org_apache_spark_ml_clustering_KMeansDALImpl_cKMeansInitSample",
+              "Java_org_apache_spark_ml_feature_PCADALImpl_cPCATrainDAL",            # native/javah/org_apache_spark_ml_feature_PCADALImpl.h
+              "Java_org_apache_spark_ml_feature_PCADALImpl_cPCATrainDALCentered"]:
         assert hasattr(handle, n), n
 
 
@@ -56,6 +62,8 @@ def test_no_cpu_fallback_without_gpu(built_lib):
         m.Table(8, 3)
     with pytest.raises(m.Kmb200Error):
         m.KMeans(k=2).fit(np.zeros((4, 2)))
+    with pytest.raises(m.Kmb200Error):
+        m.PCA(k=1).fit(np.zeros((4, 2)))
     assert m.OneDAL.cCheckPlatformCompatibility() is False
 
 
