@@ -26,6 +26,7 @@
 namespace kmb {
 
 constexpr int kPairH16Threads = 640;
+constexpr uint32_t kTransformSleepNs = 128;   // between polls of the transform warps' wait for the A columns (a tile of slack)
 
 template <int BN>
 struct PairH16Cfg {
@@ -235,7 +236,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 const bool resident = rtn > 0 && i < RES;
                 if (!resident && tile >= (uint32_t)NG) {
                     const uint32_t q = tile - NG;
-                    mbar_wait_parked(&tile_done[q & 7], (q >> 3) & 1);
+                    mbar_wait_backoff(&tile_done[q & 7], (q >> 3) & 1, kTransformSleepNs);   // (the ring gives this warp NG tiles of slack)
                 }
                 if (!resident && elect_one()) {
                     uint8_t *st = bs + g * group_bytes;
@@ -263,7 +264,7 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
             for (int kc = 0; kc < KC; ++kc) {
                 const uint32_t wg = kc & 1, j = xj[wg]++;
                 const uint32_t s = wg * XSW + j % XSW, ph = (j / XSW) & 1;
-                mbar_wait_parked(&xempty[s], ph ^ 1);
+                mbar_wait_backoff(&xempty[s], ph ^ 1, kTransformSleepNs);   // (XSW slots of slack)
                 if (elect_one()) {
                     mbar_arrive_expect_tx(&xfull[s], kXStageBytes);
                     tma_load_2d(&tm_x, &xfull[s], xs + s * kXStageBytes, kc * kChunkK, rt * kTileM);
@@ -434,9 +435,9 @@ assign_pair_h16_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_co
                 const uint32_t abuf = ADB ? (rtn & 1) : 0;
                 if (prof) { const long long t = clock64(); t_x += t - t_mark; t_mark = t; }
                 if (ADB) {
-                    if (rtn >= 2) mbar_wait_parked(&a_free[abuf * 2 + 1], ((rtn >> 1) - 1) & 1);
+                    if (rtn >= 2) mbar_wait_backoff(&a_free[abuf * 2 + 1], ((rtn >> 1) - 1) & 1, kTransformSleepNs);
                 } else if (rtn > 0) {
-                    mbar_wait_parked(&a_free[(kc >> 1) < C64a ? 0 : 1], (rtn - 1) & 1);
+                    mbar_wait_backoff(&a_free[(kc >> 1) < C64a ? 0 : 1], (rtn - 1) & 1, kTransformSleepNs);
                 }
                 tc_fence_after();
                 if (prof) {
